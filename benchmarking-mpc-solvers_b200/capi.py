@@ -1,0 +1,379 @@
+"""ctypes binding of libmpcb200.so — the repo's own user of the C ABI in include/mpc_b200.h.
+
+There is no CPU fallback: if the library is missing, cannot be loaded, or no CUDA device is present, the calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libmpcb200.so")
+
+MPC_OK, MPC_EINVAL, MPC_ECUDA, MPC_ENCCL, MPC_ENOMEM, MPC_ESTATE = 0, -1, -2, -3, -4, -5
+AGENT_MPPI, AGENT_CEM = 0, 1
+ENV_PENDULUM, ENV_CARTPOLE, ENV_ACROBOT = 0, 1, 2
+F64, F32 = 0, 1
+NOISE_TENSOR, NOISE_PHILOX = 0, 1
+COMM_ID_BYTES = 128
+MAX_ENV_PARAMS = 24
+
+DTYPES = {"f64": F64, "float64": F64, "fp64": F64, "f32": F32, "float32": F32, "fp32": F32}
+NOISES = {"tensor": NOISE_TENSOR, "numpy": NOISE_TENSOR, "philox": NOISE_PHILOX}
+
+# every symbol include/mpc_b200.h declares
+SYMBOLS = [
+    "mpc_create", "mpc_destroy", "mpc_last_error", "mpc_abi_version", "mpc_set_noise", "mpc_fill_noise",
+    "mpc_philox_noise", "mpc_mppi_solve", "mpc_mppi_get_costs", "mpc_cem_begin", "mpc_cem_iterate", "mpc_cem_end",
+    "mpc_cem_solve", "mpc_cem_get_rewards", "mpc_cem_get_elites", "mpc_cem_get_std", "mpc_simulate", "mpc_model_step",
+    "mpc_comm_create_id", "mpc_comm_init", "mpc_mppi_rollout_partial", "mpc_mppi_apply_partials", "mpc_upload_inputs", "mpc_solve_enqueue", "mpc_download_outputs",
+    "mpc_timer_start", "mpc_timer_stop", "mpc_sync", "mpc_set_profiling", "mpc_get_rollout_ms", "mpc_launch_count", "mpc_get_geometry", "mpc_measure_fma_peak",
+    "mpc_flush_l2",
+]
+
+
+class MpcConfig(C.Structure):
+    _fields_ = [
+        ("struct_size", C.c_uint32), ("agent", C.c_int32), ("env", C.c_int32), ("dtype", C.c_int32),
+        ("noise", C.c_int32), ("device", C.c_int32), ("K", C.c_int32), ("H", C.c_int32), ("batch", C.c_int32),
+        ("rank", C.c_int32), ("world", C.c_int32), ("max_iter", C.c_int32), ("n_elite", C.c_int32),
+        ("resample", C.c_int32),
+        ("lam", C.c_double), ("sigma", C.c_double), ("epsilon", C.c_double), ("alpha", C.c_double),
+        ("bounds_low", C.c_double), ("bounds_high", C.c_double), ("seed", C.c_uint64),
+        ("env_params", C.c_double * MAX_ENV_PARAMS),
+    ]
+
+
+class MpcError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("libmpcb200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+_dp = C.POINTER(C.c_double)
+
+
+def load():
+    """Load libmpcb200.so.  Raises if it has not been built — there is deliberately no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("%s is missing: build it with `python %s` (nvcc, sm_100a). "
+                           "This package has no CPU or PyTorch fallback." % (LIB_PATH, os.path.join(HERE, "build.py")))
+    L = C.CDLL(LIB_PATH)
+    hp = C.c_void_p
+    L.mpc_create.argtypes = [C.POINTER(MpcConfig), C.POINTER(hp)]
+    L.mpc_destroy.argtypes = [hp]
+    L.mpc_last_error.argtypes = [hp]
+    L.mpc_last_error.restype = C.c_char_p
+    L.mpc_abi_version.argtypes = []
+    L.mpc_set_noise.argtypes = [hp, _dp]
+    L.mpc_fill_noise.argtypes = [hp]
+    L.mpc_philox_noise.argtypes = [hp, C.c_uint64, _dp]
+    L.mpc_mppi_solve.argtypes = [hp, _dp, _dp, _dp, _dp, _dp, _dp, _dp]
+    L.mpc_mppi_get_costs.argtypes = [hp, _dp]
+    L.mpc_cem_begin.argtypes = [hp, _dp, _dp, _dp]
+    L.mpc_cem_iterate.argtypes = [hp, _dp, C.POINTER(C.c_int32)]
+    L.mpc_cem_end.argtypes = [hp, _dp, _dp, _dp, _dp]
+    L.mpc_cem_solve.argtypes = [hp, _dp, _dp, _dp, _dp, _dp, _dp, _dp, C.POINTER(C.c_int32)]
+    L.mpc_cem_get_rewards.argtypes = [hp, C.c_int32, _dp]
+    L.mpc_cem_get_elites.argtypes = [hp, C.c_int32, C.POINTER(C.c_int32)]
+    L.mpc_cem_get_std.argtypes = [hp, _dp]
+    L.mpc_simulate.argtypes = [hp, _dp, _dp, _dp, _dp, _dp]
+    L.mpc_model_step.argtypes = [hp, C.c_int32, _dp, _dp, _dp, _dp, _dp]
+    L.mpc_comm_create_id.argtypes = [C.c_void_p]
+    L.mpc_comm_init.argtypes = [hp, C.c_void_p]
+    L.mpc_mppi_rollout_partial.argtypes = [hp, _dp, _dp, _dp, _dp]
+    L.mpc_mppi_apply_partials.argtypes = [hp, _dp, _dp, _dp, _dp, _dp]
+    L.mpc_upload_inputs.argtypes = [hp, _dp, _dp, _dp]
+    L.mpc_solve_enqueue.argtypes = [hp]
+    L.mpc_download_outputs.argtypes = [hp, _dp, _dp, _dp, _dp]
+    L.mpc_timer_start.argtypes = [hp]
+    L.mpc_timer_stop.argtypes = [hp, C.POINTER(C.c_float)]
+    L.mpc_sync.argtypes = [hp]
+    L.mpc_set_profiling.argtypes = [hp, C.c_int32]
+    L.mpc_get_rollout_ms.argtypes = [hp, C.POINTER(C.c_float)]
+    L.mpc_launch_count.argtypes = [hp]
+    L.mpc_launch_count.restype = C.c_int64
+    L.mpc_get_geometry.argtypes = [hp, C.POINTER(C.c_int32)]
+    L.mpc_measure_fma_peak.argtypes = [C.c_int32, C.c_int32, _dp]
+    L.mpc_flush_l2.argtypes = [hp]
+    _lib = L
+    return L
+
+
+def _in(a, shape=None):
+    """float64 C-contiguous view/copy + pointer (None -> NULL)."""
+    if a is None:
+        return None, None
+    arr = np.ascontiguousarray(a, dtype=np.float64)
+    if shape is not None and arr.size != int(np.prod(shape)):
+        raise ValueError("expected %s elements, got array of shape %s" % (shape, arr.shape))
+    return arr, arr.ctypes.data_as(_dp)
+
+
+def _out(shape):
+    arr = np.empty(shape, dtype=np.float64)
+    return arr, arr.ctypes.data_as(_dp)
+
+
+class Solver:
+    """Thin object wrapper around one mpc_handle."""
+
+    def __init__(self, agent, env, env_params, K, H, *, dtype="f64", noise="tensor", lam=1.0, sigma=1.0,
+                 max_iter=1, n_elite=1, epsilon=0.0, alpha=0.0, bounds=(-1.0, 1.0), batch=1, device=0, rank=0,
+                 world=1, seed=0, resample=False):
+        self._h = None
+        L = load()
+        cfg = MpcConfig()
+        cfg.struct_size = C.sizeof(MpcConfig)
+        cfg.agent = AGENT_MPPI if str(agent).upper() == "MPPI" else AGENT_CEM
+        cfg.env = int(env)
+        cfg.dtype = DTYPES[dtype] if isinstance(dtype, str) else int(dtype)
+        cfg.noise = NOISES[noise] if isinstance(noise, str) else int(noise)
+        cfg.device, cfg.K, cfg.H, cfg.batch = int(device), int(K), int(H), int(batch)
+        cfg.rank, cfg.world = int(rank), int(world)
+        cfg.max_iter, cfg.n_elite, cfg.resample = int(max_iter), int(n_elite), int(bool(resample))
+        cfg.lam, cfg.sigma, cfg.epsilon, cfg.alpha = float(lam), float(sigma), float(epsilon), float(alpha)
+        cfg.bounds_low, cfg.bounds_high = float(bounds[0]), float(bounds[1])
+        cfg.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+        if len(env_params) > MAX_ENV_PARAMS:
+            raise ValueError("too many env params")
+        for i, v in enumerate(env_params):
+            cfg.env_params[i] = float(v)
+        self.cfg = cfg
+        self.L = L
+        self.K, self.H, self.B = int(K), int(H), int(batch)
+        self.ns = 2 if cfg.env == ENV_PENDULUM else 4
+        self.nz = self.ns + 1
+        self.is_mppi = cfg.agent == AGENT_MPPI
+        self.tensor_noise = cfg.noise == NOISE_TENSOR
+        h = C.c_void_p()
+        rc = L.mpc_create(C.byref(cfg), C.byref(h))
+        if rc != MPC_OK:
+            raise MpcError(rc, (L.mpc_last_error(None) or b"").decode())
+        self._h = h
+        geo = (C.c_int32 * 6)()
+        self._ck(L.mpc_get_geometry(self._h, geo))
+        self.geometry = dict(grid=geo[0], block=geo[1], smem=geo[2], tiles=geo[3], K_local=geo[4], k_begin=geo[5])
+        self.K_local, self.k_begin = geo[4], geo[5]
+
+    # -- plumbing
+    def _ck(self, rc):
+        if rc != MPC_OK:
+            raise MpcError(rc, (self.L.mpc_last_error(self._h) or b"").decode())
+
+    def close(self):
+        if self._h is not None:
+            self.L.mpc_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _gz(self, g_z):
+        """None or an all-zero goal is sent as NULL (zero goal resident on the device)."""
+        if g_z is None:
+            return None, None
+        g = np.asarray(g_z, dtype=np.float64)
+        if not g.any():
+            return None, None
+        return _in(g, (self.B, self.H, self.nz))
+
+    # -- noise
+    def set_noise(self, delta_u):
+        a, p = _in(delta_u, (self.K, self.H))
+        self._ck(self.L.mpc_set_noise(self._h, p))
+
+    def fill_noise(self):
+        self._ck(self.L.mpc_fill_noise(self._h))
+
+    def philox_noise(self, draw=0):
+        out, p = _out((self.K_local, self.H))
+        self._ck(self.L.mpc_philox_noise(self._h, int(draw), p))
+        return out
+
+    # -- MPPI
+    def mppi_solve(self, x, g_z=None, U_in=None, want_traj=True):
+        xa, xp = _in(x, (self.B, self.ns))
+        ga, gp = self._gz(g_z)
+        ua, up = _in(U_in, (self.B, self.H))
+        u0, u0p = _out((self.B,))
+        U, Up = _out((self.B, self.H))
+        if want_traj:
+            xs, xsp = _out((self.B, self.H + 1, self.ns))
+            cost, cp = _out((self.B,))
+        else:
+            xs = cost = xsp = cp = None
+        self._ck(self.L.mpc_mppi_solve(self._h, xp, gp, up, u0p, Up, xsp, cp))
+        return u0, U, xs, cost
+
+    def mppi_costs(self):
+        out, p = _out((self.B, self.K_local))
+        self._ck(self.L.mpc_mppi_get_costs(self._h, p))
+        return out
+
+    # -- CEM
+    def cem_begin(self, x, g_z=None, U_in=None):
+        xa, xp = _in(x, (self.ns,))
+        ga, gp = self._gz(g_z)
+        ua, up = _in(U_in, (self.H,))
+        self._ck(self.L.mpc_cem_begin(self._h, xp, gp, up))
+
+    def cem_iterate(self, z=None):
+        za, zp = _in(z, (self.K, self.H))
+        done = C.c_int32(0)
+        self._ck(self.L.mpc_cem_iterate(self._h, zp, C.byref(done)))
+        return bool(done.value)
+
+    def cem_end(self, want_traj=True):
+        u0, u0p = _out((1,))
+        U, Up = _out((self.H,))
+        if want_traj:
+            xs, xsp = _out((self.H + 1, self.ns))
+            cost, cp = _out((1,))
+        else:
+            xs = cost = xsp = cp = None
+        self._ck(self.L.mpc_cem_end(self._h, u0p, Up, xsp, cp))
+        return u0, U, xs, cost
+
+    def cem_solve(self, x, g_z=None, U_in=None, want_traj=True):
+        xa, xp = _in(x, (self.ns,))
+        ga, gp = self._gz(g_z)
+        ua, up = _in(U_in, (self.H,))
+        u0, u0p = _out((1,))
+        U, Up = _out((self.H,))
+        if want_traj:
+            xs, xsp = _out((self.H + 1, self.ns))
+            cost, cp = _out((1,))
+        else:
+            xs = cost = xsp = cp = None
+        iters = C.c_int32(0)
+        self._ck(self.L.mpc_cem_solve(self._h, xp, gp, up, u0p, Up, xsp, cp, C.byref(iters)))
+        return u0, U, xs, cost, iters.value
+
+    def cem_rewards(self, it):
+        out, p = _out((self.K_local,))
+        self._ck(self.L.mpc_cem_get_rewards(self._h, int(it), p))
+        return out
+
+    def cem_elites(self, it):
+        out = np.empty(self.cfg.n_elite, dtype=np.int32)
+        self._ck(self.L.mpc_cem_get_elites(self._h, int(it), out.ctypes.data_as(C.POINTER(C.c_int32))))
+        return out
+
+    def cem_std(self):
+        out, p = _out((self.H,))
+        self._ck(self.L.mpc_cem_get_std(self._h, p))
+        return out
+
+    # -- nominal rollout / single steps
+    def simulate(self, x, us, g_z=None):
+        xa, xp = _in(x, (self.ns,))
+        ua, up = _in(us, (self.H,))
+        ga, gp = _in(g_z, (self.H, self.nz)) if g_z is not None else (None, None)
+        xs, xsp = _out((self.H + 1, self.ns))
+        cost = C.c_double()
+        self._ck(self.L.mpc_simulate(self._h, xp, up, gp, xsp, C.byref(cost)))
+        return xs, cost.value
+
+    def model_step(self, x, u, g=None):
+        x = np.ascontiguousarray(x, dtype=np.float64).reshape(-1, self.ns)
+        n = x.shape[0]
+        xa, xp = _in(x)
+        ua, up = _in(u, (n,))
+        ga, gp = _in(g, (n, self.nz)) if g is not None else (None, None)
+        cost, cp = _out((n,))
+        xn, xnp = _out((n, self.ns))
+        self._ck(self.L.mpc_model_step(self._h, n, xp, up, gp, cp, xnp))
+        return cost, xn
+
+    # -- multi-GPU
+    @staticmethod
+    def comm_create_id():
+        buf = C.create_string_buffer(COMM_ID_BYTES)
+        rc = load().mpc_comm_create_id(buf)
+        if rc != MPC_OK:
+            raise MpcError(rc, (load().mpc_last_error(None) or b"").decode())
+        return bytes(buf.raw)
+
+    def comm_init(self, id_bytes):
+        buf = C.create_string_buffer(bytes(id_bytes), COMM_ID_BYTES)
+        self._ck(self.L.mpc_comm_init(self._h, buf))
+
+    def mppi_rollout_partial(self, x, g_z=None, U_in=None):
+        xa, xp = _in(x, (self.B, self.ns))
+        ga, gp = self._gz(g_z)
+        ua, up = _in(U_in, (self.B, self.H))
+        rec, rp = _out((self.B, 2 + self.H))
+        self._ck(self.L.mpc_mppi_rollout_partial(self._h, xp, gp, up, rp))
+        return rec
+
+    def mppi_apply_partials(self, recs, want_traj=True):
+        ra, rp = _in(recs, (self.cfg.world, self.B, 2 + self.H))
+        u0, u0p = _out((self.B,))
+        U, Up = _out((self.B, self.H))
+        if want_traj:
+            xs, xsp = _out((self.B, self.H + 1, self.ns))
+            cost, cp = _out((self.B,))
+        else:
+            xs = cost = xsp = cp = None
+        self._ck(self.L.mpc_mppi_apply_partials(self._h, rp, u0p, Up, xsp, cp))
+        return u0, U, xs, cost
+
+    # -- measurement
+    def upload_inputs(self, x, g_z=None, U_in=None):
+        xa, xp = _in(x, (self.B, self.ns))
+        ga, gp = self._gz(g_z)
+        ua, up = _in(U_in, (self.B, self.H))
+        self._ck(self.L.mpc_upload_inputs(self._h, xp, gp, up))
+
+    def solve_enqueue(self):
+        self._ck(self.L.mpc_solve_enqueue(self._h))
+
+    def download_outputs(self):
+        u0, u0p = _out((self.B,))
+        U, Up = _out((self.B, self.H))
+        xs, xsp = _out((self.B, self.H + 1, self.ns))
+        cost, cp = _out((self.B,))
+        self._ck(self.L.mpc_download_outputs(self._h, u0p, Up, xsp, cp))
+        return u0, U, xs, cost
+
+    def timer_start(self):
+        self._ck(self.L.mpc_timer_start(self._h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._ck(self.L.mpc_timer_stop(self._h, C.byref(ms)))
+        return ms.value
+
+    def set_profiling(self, on=True):
+        self._ck(self.L.mpc_set_profiling(self._h, int(bool(on))))
+
+    def rollout_ms(self):
+        ms = C.c_float()
+        self._ck(self.L.mpc_get_rollout_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def sync(self):
+        self._ck(self.L.mpc_sync(self._h))
+
+    def flush_l2(self):
+        self._ck(self.L.mpc_flush_l2(self._h))
+
+    @property
+    def launch_count(self):
+        return int(self.L.mpc_launch_count(self._h))
+
+
+def measure_fma_peak(device=0, dtype="f32"):
+    out = C.c_double()
+    rc = load().mpc_measure_fma_peak(int(device), DTYPES[dtype], C.byref(out))
+    if rc != MPC_OK:
+        raise MpcError(rc, (load().mpc_last_error(None) or b"").decode())
+    return out.value

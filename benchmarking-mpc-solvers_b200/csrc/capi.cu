@@ -1,0 +1,938 @@
+// capi.cu — the C ABI declared in include/mpc_b200.h: handle, buffers, staging, launch sequencing, NCCL exchange.
+// No torch types, no CPU fallback: every entry point either runs the CUDA path or returns an error.
+#include "../../include/mpc_b200.h"
+#include "kernels.cuh"
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+
+using namespace mpc;
+
+// ---------------------------------------------------------------------------------------------- NCCL (lazy dlopen)
+// Only the five entry points the exchange needs; resolved on first use so that single-GPU users never load NCCL.
+namespace {
+typedef struct ncclComm *ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+typedef int ncclResult_t;
+enum { ncclFloat64 = 8 };
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+} g_nccl;
+
+bool nccl_load(std::string *err) {
+    if (g_nccl.ok) return true;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *n : names) {
+        g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (g_nccl.lib) break;
+    }
+    if (!g_nccl.lib) {
+        *err = std::string("cannot load libnccl: ") + dlerror();
+        return false;
+    }
+#define LOADSYM(field, name)                                              \
+    g_nccl.field = (decltype(g_nccl.field))dlsym(g_nccl.lib, name);       \
+    if (!g_nccl.field) {                                                  \
+        *err = std::string("libnccl lacks ") + name;                      \
+        return false;                                                     \
+    }
+    LOADSYM(GetUniqueId, "ncclGetUniqueId");
+    LOADSYM(CommInitRank, "ncclCommInitRank");
+    LOADSYM(AllGather, "ncclAllGather");
+    LOADSYM(CommDestroy, "ncclCommDestroy");
+    LOADSYM(GetErrorString, "ncclGetErrorString");
+#undef LOADSYM
+    g_nccl.ok = true;
+    return true;
+}
+thread_local std::string g_create_error;
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------- handle
+struct mpc_handle {
+    mpc_config cfg;
+    EnvParamsHost ep;
+    Geometry g;
+    int ns, nz;
+    int num_sms;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evr0 = nullptr, evr1 = nullptr;
+    bool profiling = false;
+    // device
+    void *d_noise = nullptr;      // R [Bn][H][Kpad]          (MPPI tensor / CEM z of the current iteration)
+    double *d_in = nullptr;       // x0 [B][ns] | g_z [B][H][nz] | U [B][H]
+    double *d_S = nullptr;        // [B][Kpad]
+    double *d_part = nullptr;     // [B][max_parts][2+H]
+    double *d_rank_part = nullptr;  // [world][B][2+H]
+    double *d_out = nullptr;      // [B][out_stride] (+1)
+    double *d_scratch = nullptr;  // staging for uploads: max(K_local*H, misc)
+    size_t scratch_elems = 0;
+    // CEM
+    double *d_sd = nullptr, *d_R = nullptr;
+    unsigned long long *d_keys = nullptr;
+    int *d_elite = nullptr, *d_sel = nullptr;
+    int cem_iter = 0;
+    bool cem_open = false;
+    // host (pinned)
+    double *h_in = nullptr, *h_out = nullptr;
+    size_t in_elems = 0, out_elems = 0, out_stride = 0;
+    float *d_flush = nullptr;
+    size_t flush_elems = 0;
+    // state
+    bool noise_ready = false;
+    bool g_zero_on_device = false;
+    uint64_t solves = 0;
+    int64_t launches = 0;
+    int last_iters = 0;
+    ncclComm_t comm = nullptr;
+    std::string err;
+};
+
+static int fail(mpc_handle *h, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (h)
+        h->err = buf;
+    else
+        g_create_error = buf;
+    return code;
+}
+
+#define CU(h, call)                                                                                       \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess) return fail(h, MPC_ECUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                                           __FILE__, __LINE__);                                           \
+    } while (0)
+
+// Fold the reference models' parameters into the constants envs.cuh consumes — in float64 and in the reference's
+// own association order, so the float64 path differs from numpy only by FMA contraction and libm ulps.
+static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
+    memset(out, 0, sizeof *out);
+    out->env = env;
+    double *c = out->c;
+    if (env == MPC_ENV_PENDULUM) {  // pendulum_model.py:14-21,28-38
+        const double g = p[0], m = p[1], l = p[2];
+        c[0] = -3 * g / (2 * l);
+        c[1] = 3. / (m * (l * l));
+        c[2] = p[3];
+        c[3] = p[4];
+        c[4] = p[5];
+        c[5] = p[6]; c[6] = p[7]; c[7] = p[8];
+    } else if (env == MPC_ENV_CARTPOLE) {  // cartpole_swingup_model.py:25-33,63-85
+        const double g = p[0], m_c = p[1], m_p = p[2], l = p[3], b = p[6];
+        const double total_m = m_p + m_c, m_p_l = m_p * l;
+        c[0] = 1.0 / p[7];
+        c[1] = p[4];
+        c[2] = p[5];
+        c[3] = b;
+        c[4] = -2 * m_p_l;
+        c[5] = 3 * m_p * g;
+        c[6] = 4 * b;
+        c[7] = 4 * total_m;
+        c[8] = 3 * m_p;
+        c[9] = -3 * m_p_l;
+        c[10] = 6 * total_m * g;
+        c[11] = 4 * l * total_m;
+        c[12] = 3 * m_p_l;
+        for (int i = 0; i < 5; ++i) c[13 + i] = -p[8 + i];
+    } else if (env == MPC_ENV_ACROBOT) {  // acrobot_model.py:100-132
+        const double m1 = p[1], m2 = p[2], l1 = p[3], lc1 = p[4], lc2 = p[5], I1 = p[6], I2 = p[7], g = p[8];
+        c[0] = p[0];
+        c[1] = m1 * (lc1 * lc1) + m2 * ((l1 * l1) + (lc2 * lc2)) + I1 + I2;
+        c[2] = 2 * m2 * l1 * lc2;
+        c[3] = m2 * (lc2 * lc2) + I2;
+        c[4] = m2 * l1 * lc2;
+        c[5] = (m1 * lc1 + m2 * l1) * g;
+        c[6] = m2 * lc2 * g;
+        c[7] = p[9];
+        c[8] = p[10];
+        for (int i = 0; i < 5; ++i) c[9 + i] = p[11 + i];
+    } else {
+        return -1;
+    }
+    return 0;
+}
+
+namespace mpc {
+int mppi_rollout_occupancy(int dtype, int noise, int env, int H);  // kernels.cu
+}
+
+static size_t off_x(const mpc_handle *) { return 0; }
+static size_t off_gz(const mpc_handle *h) { return (size_t)h->g.B * h->ns; }
+static size_t off_U(const mpc_handle *h) { return off_gz(h) + (size_t)h->g.B * h->g.H * h->nz; }
+
+static MppiArgs mppi_args(const mpc_handle *h, int want_traj) {
+    MppiArgs a;
+    memset(&a, 0, sizeof a);
+    a.g = h->g;
+    a.neg_inv_lam = -(1 / h->cfg.lam);
+    a.pert = h->cfg.lam * (1.0 / (h->cfg.sigma * h->cfg.sigma));
+    a.sigma = h->cfg.sigma;
+    a.lo = h->cfg.bounds_low;
+    a.hi = h->cfg.bounds_high;
+    a.seed = h->cfg.seed;
+    a.draw = h->cfg.resample ? (uint32_t)(h->solves & 0x7fffffffu) : 0u;
+    a.noise_batched = 0;
+    a.want_traj = want_traj;
+    a.world = h->cfg.world;
+    a.rank = h->cfg.rank;
+    return a;
+}
+
+static MppiBuffers mppi_bufs(const mpc_handle *h) {
+    MppiBuffers b;
+    b.noise = h->d_noise;
+    b.x0 = h->d_in + off_x(h);
+    b.g_z = h->d_in + off_gz(h);
+    b.U = h->d_in + off_U(h);
+    b.S = h->d_S;
+    b.part = h->d_part;
+    b.rank_part = h->d_rank_part;
+    b.out = h->d_out;
+    return b;
+}
+
+static CemArgs cem_args(const mpc_handle *h, int iter, int want_traj) {
+    CemArgs a;
+    memset(&a, 0, sizeof a);
+    a.g = h->g;
+    a.sigma = h->cfg.sigma;
+    a.lo = h->cfg.bounds_low;
+    a.hi = h->cfg.bounds_high;
+    a.alpha = h->cfg.alpha;
+    a.epsilon = h->cfg.epsilon;
+    a.n_elite = h->cfg.n_elite;
+    a.iter = iter;
+    a.seed = h->cfg.seed + 0x9E3779B97F4A7C15ull * (h->cfg.resample ? h->solves : 0);
+    a.want_traj = want_traj;
+    return a;
+}
+
+static CemBuffers cem_bufs(const mpc_handle *h) {
+    CemBuffers b;
+    b.z = h->d_noise;
+    b.x0 = h->d_in + off_x(h);
+    b.g_z = h->d_in + off_gz(h);
+    b.mu = h->d_in + off_U(h);
+    b.sd = h->d_sd;
+    b.R = h->d_R;
+    b.keys = h->d_keys;
+    b.elite_idx = h->d_elite;
+    b.sel = h->d_sel;
+    b.out = h->d_out;
+    return b;
+}
+
+extern "C" {
+
+int mpc_abi_version(void) { return MPC_B200_ABI_VERSION; }
+
+const char *mpc_last_error(const mpc_handle *h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int mpc_destroy(mpc_handle *h) {
+    if (!h) return MPC_OK;
+    cudaSetDevice(h->cfg.device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->comm && g_nccl.ok) g_nccl.CommDestroy(h->comm);
+    cudaFree(h->d_noise);
+    cudaFree(h->d_in);
+    cudaFree(h->d_S);
+    cudaFree(h->d_part);
+    cudaFree(h->d_rank_part);
+    cudaFree(h->d_out);
+    cudaFree(h->d_scratch);
+    cudaFree(h->d_sd);
+    cudaFree(h->d_R);
+    cudaFree(h->d_keys);
+    cudaFree(h->d_elite);
+    cudaFree(h->d_sel);
+    cudaFree(h->d_flush);
+    if (h->h_in) cudaFreeHost(h->h_in);
+    if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->evr0) cudaEventDestroy(h->evr0);
+    if (h->evr1) cudaEventDestroy(h->evr1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return MPC_OK;
+}
+
+int mpc_create(const mpc_config *cfg, mpc_handle **out) {
+    if (!cfg || !out) return fail(nullptr, MPC_EINVAL, "null argument");
+    *out = nullptr;
+    if (cfg->struct_size != sizeof(mpc_config))
+        return fail(nullptr, MPC_EINVAL, "mpc_config size mismatch: caller %u, library %zu", cfg->struct_size,
+                    sizeof(mpc_config));
+    if (cfg->env < 0 || cfg->env > 2) return fail(nullptr, MPC_EINVAL, "unknown env %d", cfg->env);
+    if (cfg->agent != MPC_AGENT_MPPI && cfg->agent != MPC_AGENT_CEM)
+        return fail(nullptr, MPC_EINVAL, "unknown agent %d", cfg->agent);
+    if (cfg->dtype != MPC_F64 && cfg->dtype != MPC_F32) return fail(nullptr, MPC_EINVAL, "unknown dtype %d", cfg->dtype);
+    if (cfg->noise != MPC_NOISE_TENSOR && cfg->noise != MPC_NOISE_PHILOX)
+        return fail(nullptr, MPC_EINVAL, "unknown noise mode %d", cfg->noise);
+    if (cfg->K < 1 || cfg->H < 1 || cfg->batch < 1) return fail(nullptr, MPC_EINVAL, "K, H, batch must be >= 1");
+    if (cfg->H > TILE * MAX_EH) return fail(nullptr, MPC_EINVAL, "H = %d exceeds the supported %d", cfg->H, TILE * MAX_EH);
+    if (cfg->world < 1 || cfg->rank < 0 || cfg->rank >= cfg->world)
+        return fail(nullptr, MPC_EINVAL, "bad rank/world %d/%d", cfg->rank, cfg->world);
+    if (cfg->K < cfg->world) return fail(nullptr, MPC_EINVAL, "K = %d smaller than world = %d", cfg->K, cfg->world);
+    if (!(cfg->sigma > 0)) return fail(nullptr, MPC_EINVAL, "std must be > 0");
+    if (cfg->agent == MPC_AGENT_MPPI && !(cfg->lam > 0)) return fail(nullptr, MPC_EINVAL, "lam must be > 0");
+    if (cfg->agent == MPC_AGENT_CEM) {
+        if (cfg->batch != 1) return fail(nullptr, MPC_EINVAL, "CEM supports batch = 1");
+        if (cfg->world != 1) return fail(nullptr, MPC_EINVAL, "CEM is single-GPU in this version");
+        if (cfg->n_elite < 1 || cfg->n_elite > cfg->K)
+            return fail(nullptr, MPC_EINVAL, "n_elite = %d must be in [1, K]", cfg->n_elite);
+        if (cfg->max_iter < 1) return fail(nullptr, MPC_EINVAL, "max_iter must be >= 1");
+    }
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(nullptr, MPC_ECUDA, "no CUDA device (%s); this library has no CPU path",
+                    ce == cudaSuccess ? "device count 0" : cudaGetErrorString(ce));
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, MPC_EINVAL, "device %d of %d", cfg->device, ndev);
+
+    mpc_handle *h = new (std::nothrow) mpc_handle();
+    if (!h) return fail(nullptr, MPC_ENOMEM, "out of host memory");
+    h->cfg = *cfg;
+    if (fold_env_params(cfg->env, cfg->env_params, &h->ep)) {
+        delete h;
+        return fail(nullptr, MPC_EINVAL, "bad env");
+    }
+    h->ns = (cfg->env == MPC_ENV_PENDULUM) ? 2 : 4;
+    h->nz = h->ns + 1;
+
+#define CUC(call)                                                                                    \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) {                                                                     \
+            int rc_ = fail(nullptr, e_ == cudaErrorMemoryAllocation ? MPC_ENOMEM : MPC_ECUDA,        \
+                           "%s: %s", #call, cudaGetErrorString(e_));                                 \
+            mpc_destroy(h);                                                                          \
+            return rc_;                                                                              \
+        }                                                                                            \
+    } while (0)
+
+    CUC(cudaSetDevice(cfg->device));
+    CUC(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, cfg->device));
+    CUC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CUC(cudaEventCreate(&h->ev0));
+    CUC(cudaEventCreate(&h->ev1));
+    CUC(cudaEventCreate(&h->evr0));
+    CUC(cudaEventCreate(&h->evr1));
+
+    // ---- geometry: contiguous K shard, padded to whole tiles, tiles dealt to a one-wave grid ----------------
+    Geometry &g = h->g;
+    const long long K = cfg->K;
+    g.k_begin = (int)(K * cfg->rank / cfg->world);
+    g.K_local = (int)(K * (cfg->rank + 1) / cfg->world) - g.k_begin;
+    g.Kpad = (g.K_local + TILE - 1) / TILE * TILE;
+    g.H = cfg->H;
+    g.B = cfg->batch;
+    g.ns = h->ns;
+    g.tiles_per_solve = g.Kpad / TILE;
+    g.total_tiles = g.B * g.tiles_per_solve;
+    g.smem_rollout = mppi_rollout_smem(cfg->dtype, cfg->H);
+    int max_smem = 0;
+    CUC(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
+    if (cfg->agent == MPC_AGENT_MPPI && g.smem_rollout > (size_t)max_smem) {
+        int rc = fail(nullptr, MPC_EINVAL, "H = %d needs %zu B of shared memory per block (limit %d)", cfg->H,
+                      g.smem_rollout, max_smem);
+        mpc_destroy(h);
+        return rc;
+    }
+    int occ = 1;
+    if (cfg->agent == MPC_AGENT_MPPI) {
+        occ = mppi_rollout_occupancy(cfg->dtype, cfg->noise, cfg->env, cfg->H);
+        if (occ < 1) occ = 1;
+    }
+    const int slots = h->num_sms * occ;
+    g.chunk = (g.total_tiles + slots - 1) / slots;
+    g.grid = (g.total_tiles + g.chunk - 1) / g.chunk;
+    g.max_parts = (g.tiles_per_solve + g.chunk - 1) / g.chunk + 1;
+    if (g.max_parts > g.grid) g.max_parts = g.grid;
+
+    // ---- buffers ------------------------------------------------------------------------------------------
+    const size_t esz = cfg->dtype == MPC_F32 ? 4 : 8;
+    const size_t rec = PART_HDR + g.H;
+    h->out_stride = 2 + g.H + (size_t)(g.H + 1) * h->ns;
+    h->in_elems = off_U(h) + (size_t)g.B * g.H;
+    h->out_elems = (size_t)g.B * h->out_stride + 1;
+    CUC(cudaMalloc(&h->d_in, h->in_elems * sizeof(double)));
+    CUC(cudaMemsetAsync(h->d_in, 0, h->in_elems * sizeof(double), h->stream));  // planned_us = zeros (mppi.py:14)
+    CUC(cudaMalloc(&h->d_out, h->out_elems * sizeof(double)));
+    CUC(cudaMemsetAsync(h->d_out, 0, h->out_elems * sizeof(double), h->stream));
+    CUC(cudaMallocHost(&h->h_in, h->in_elems * sizeof(double)));
+    CUC(cudaMallocHost(&h->h_out, h->out_elems * sizeof(double)));
+    memset(h->h_in, 0, h->in_elems * sizeof(double));
+    h->g_zero_on_device = true;
+    if (cfg->noise == MPC_NOISE_TENSOR) {
+        CUC(cudaMalloc(&h->d_noise, (size_t)g.H * g.Kpad * esz));
+        CUC(cudaMemsetAsync(h->d_noise, 0, (size_t)g.H * g.Kpad * esz, h->stream));
+    }
+    if (cfg->agent == MPC_AGENT_MPPI) {
+        CUC(cudaMalloc(&h->d_S, (size_t)g.B * g.Kpad * sizeof(double)));
+        CUC(cudaMalloc(&h->d_part, (size_t)g.B * g.max_parts * rec * sizeof(double)));
+        CUC(cudaMalloc(&h->d_rank_part, (size_t)cfg->world * g.B * rec * sizeof(double)));
+    } else {
+        CUC(cudaMalloc(&h->d_sd, (size_t)g.H * sizeof(double)));
+        CUC(cudaMalloc(&h->d_R, (size_t)cfg->max_iter * g.Kpad * sizeof(double)));
+        CUC(cudaMalloc(&h->d_keys, (size_t)g.Kpad * sizeof(unsigned long long)));
+        CUC(cudaMalloc(&h->d_elite, (size_t)cfg->max_iter * cfg->n_elite * sizeof(int)));
+        CUC(cudaMalloc(&h->d_sel, 8 * sizeof(int)));
+        CUC(cudaMemsetAsync(h->d_sel, 0, 8 * sizeof(int), h->stream));
+        CUC(cudaMemsetAsync(h->d_R, 0, (size_t)cfg->max_iter * g.Kpad * sizeof(double), h->stream));
+        CUC(cudaMemsetAsync(h->d_elite, 0, (size_t)cfg->max_iter * cfg->n_elite * sizeof(int), h->stream));
+    }
+    CUC(cudaStreamSynchronize(h->stream));
+#undef CUC
+    h->noise_ready = (cfg->noise == MPC_NOISE_PHILOX);
+    *out = h;
+    return MPC_OK;
+}
+
+static int ensure_scratch(mpc_handle *h, size_t elems) {
+    if (h->scratch_elems >= elems) return MPC_OK;
+    if (h->d_scratch) cudaFree(h->d_scratch);
+    h->d_scratch = nullptr;
+    h->scratch_elems = 0;
+    cudaError_t e = cudaMalloc(&h->d_scratch, elems * sizeof(double));
+    if (e != cudaSuccess) return fail(h, MPC_ENOMEM, "cudaMalloc scratch of %zu doubles: %s", elems, cudaGetErrorString(e));
+    h->scratch_elems = elems;
+    return MPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- noise
+int mpc_set_noise(mpc_handle *h, const double *delta_u_KH) {
+    if (!h || !delta_u_KH) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.noise != MPC_NOISE_TENSOR) return fail(h, MPC_ESTATE, "handle is in PHILOX noise mode");
+    CU(h, cudaSetDevice(h->cfg.device));
+    const Geometry &g = h->g;
+    const size_t n = (size_t)g.K_local * g.H;
+    int rc = ensure_scratch(h, n);
+    if (rc) return rc;
+    CU(h, cudaMemcpyAsync(h->d_scratch, delta_u_KH + (size_t)g.k_begin * g.H, n * sizeof(double),
+                          cudaMemcpyHostToDevice, h->stream));
+    CU(h, launch_transpose_noise(h->cfg.dtype, h->d_scratch, h->d_noise, g.K_local, g.Kpad, g.H, h->stream));
+    h->launches++;
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->noise_ready = true;
+    return MPC_OK;
+}
+
+int mpc_fill_noise(mpc_handle *h) {
+    if (!h) return MPC_EINVAL;
+    if (h->cfg.noise != MPC_NOISE_TENSOR) return fail(h, MPC_ESTATE, "handle is in PHILOX noise mode");
+    CU(h, cudaSetDevice(h->cfg.device));
+    const Geometry &g = h->g;
+    CU(h, launch_philox_fill(h->cfg.dtype, h->d_noise, g.K_local, g.k_begin, g.Kpad, g.H, h->cfg.sigma, h->cfg.seed, 0u,
+                             h->stream));
+    h->launches++;
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->noise_ready = true;
+    return MPC_OK;
+}
+
+int mpc_philox_noise(mpc_handle *h, uint64_t draw, double *out) {
+    if (!h || !out) return fail(h, MPC_EINVAL, "null argument");
+    CU(h, cudaSetDevice(h->cfg.device));
+    const Geometry &g = h->g;
+    const size_t n = (size_t)g.K_local * g.H;
+    int rc = ensure_scratch(h, n);
+    if (rc) return rc;
+    const uint32_t stream_bit = (h->cfg.agent == MPC_AGENT_CEM) ? 0x80000000u : 0u;
+    uint64_t seed = h->cfg.seed;
+    if (h->cfg.agent == MPC_AGENT_CEM && h->cfg.resample) seed += 0x9E3779B97F4A7C15ull * (h->solves ? h->solves - 1 : 0);
+    CU(h, launch_philox_materialize(h->d_scratch, g.K_local, g.k_begin, g.H, seed,
+                                    ((uint32_t)draw & 0x7fffffffu) | stream_bit, h->stream));
+    h->launches++;
+    CU(h, cudaMemcpyAsync(out, h->d_scratch, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- staging
+// h_in layout = device layout.  g_z == NULL means a zero goal (what every reference script passes,
+// Experiment.py:81-82): the device copy is zeroed once and not re-sent.
+static int stage_inputs(mpc_handle *h, const double *x, const double *g_z, const double *U_in) {
+    const Geometry &g = h->g;
+    if (!x) return fail(h, MPC_EINVAL, "state pointer is null");
+    memcpy(h->h_in + off_x(h), x, (size_t)g.B * h->ns * sizeof(double));
+    size_t upto = off_gz(h);
+    const size_t gz_elems = (size_t)g.B * g.H * h->nz;
+    if (g_z) {
+        memcpy(h->h_in + off_gz(h), g_z, gz_elems * sizeof(double));
+        h->g_zero_on_device = false;
+        upto = off_U(h);
+    } else if (!h->g_zero_on_device) {
+        memset(h->h_in + off_gz(h), 0, gz_elems * sizeof(double));
+        h->g_zero_on_device = true;
+        upto = off_U(h);
+    }
+    if (U_in) {
+        memcpy(h->h_in + off_U(h), U_in, (size_t)g.B * g.H * sizeof(double));
+        if (upto == off_U(h)) {
+            upto = h->in_elems;
+        } else {
+            CU(h, cudaMemcpyAsync(h->d_in + off_U(h), h->h_in + off_U(h), (size_t)g.B * g.H * sizeof(double),
+                                  cudaMemcpyHostToDevice, h->stream));
+        }
+    }
+    CU(h, cudaMemcpyAsync(h->d_in, h->h_in, upto * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    return MPC_OK;
+}
+
+static int fetch_outputs(mpc_handle *h, int want_traj, double *u0, double *U_out, double *xs_out, double *cost_out) {
+    const Geometry &g = h->g;
+    const size_t per = want_traj ? h->out_stride : (size_t)(1 + g.H);
+    if (g.B == 1) {
+        CU(h, cudaMemcpyAsync(h->h_out, h->d_out, (per + (want_traj ? 1 : 0)) * sizeof(double), cudaMemcpyDeviceToHost,
+                              h->stream));
+    } else if (want_traj) {
+        CU(h, cudaMemcpyAsync(h->h_out, h->d_out, h->out_elems * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    } else {
+        CU(h, cudaMemcpy2DAsync(h->h_out, h->out_stride * sizeof(double), h->d_out, h->out_stride * sizeof(double),
+                                per * sizeof(double), g.B, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CU(h, cudaStreamSynchronize(h->stream));
+    for (int b = 0; b < g.B; ++b) {
+        const double *o = h->h_out + (size_t)b * h->out_stride;
+        if (u0) u0[b] = o[0];
+        if (U_out) memcpy(U_out + (size_t)b * g.H, o + 1, g.H * sizeof(double));
+        if (want_traj) {
+            if (cost_out) cost_out[b] = o[1 + g.H];
+            if (xs_out) memcpy(xs_out + (size_t)b * (g.H + 1) * h->ns, o + 2 + g.H, (size_t)(g.H + 1) * h->ns * sizeof(double));
+        }
+    }
+    return MPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- MPPI
+static int mppi_enqueue(mpc_handle *h, int want_traj) {
+    if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "not an MPPI handle");
+    if (!h->noise_ready) return fail(h, MPC_ESTATE, "noise tensor not set: call mpc_set_noise or mpc_fill_noise first");
+    if (h->cfg.world > 1 && !h->comm) return fail(h, MPC_ESTATE, "world > 1 but mpc_comm_init was not called");
+    const MppiArgs a = mppi_args(h, want_traj);
+    const MppiBuffers b = mppi_bufs(h);
+    if (h->profiling) CU(h, cudaEventRecord(h->evr0, h->stream));
+    CU(h, launch_mppi_rollout(h->cfg.dtype, h->cfg.noise, h->ep, a, b, h->stream));
+    if (h->profiling) CU(h, cudaEventRecord(h->evr1, h->stream));
+    h->launches++;
+    if (h->cfg.world == 1) {
+        CU(h, launch_mppi_finalize(h->cfg.dtype, 0, h->ep, a, b, h->stream));
+        h->launches++;
+    } else {
+        CU(h, launch_mppi_finalize(h->cfg.dtype, 1, h->ep, a, b, h->stream));
+        const size_t cnt = (size_t)h->g.B * (PART_HDR + h->g.H);
+        ncclResult_t r = g_nccl.AllGather(h->d_rank_part + (size_t)h->cfg.rank * cnt, h->d_rank_part, cnt, ncclFloat64,
+                                          h->comm, h->stream);
+        if (r != 0) return fail(h, MPC_ENCCL, "ncclAllGather: %s", g_nccl.GetErrorString(r));
+        CU(h, launch_mppi_finalize(h->cfg.dtype, 2, h->ep, a, b, h->stream));
+        h->launches += 3;
+    }
+    h->solves++;
+    return MPC_OK;
+}
+
+int mpc_mppi_solve(mpc_handle *h, const double *x, const double *g_z, const double *U_in, double *u0, double *U_out,
+                   double *xs_out, double *cost_out) {
+    if (!h) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    const int want_traj = (xs_out || cost_out) ? 1 : 0;
+    int rc = stage_inputs(h, x, g_z, U_in);
+    if (rc) return rc;
+    rc = mppi_enqueue(h, want_traj);
+    if (rc) return rc;
+    return fetch_outputs(h, want_traj, u0, U_out, xs_out, cost_out);
+}
+
+int mpc_mppi_rollout_partial(mpc_handle *h, const double *x, const double *g_z, const double *U_in, double *rec_out) {
+    if (!h || !rec_out) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "not an MPPI handle");
+    if (!h->noise_ready) return fail(h, MPC_ESTATE, "noise tensor not set: call mpc_set_noise or mpc_fill_noise first");
+    CU(h, cudaSetDevice(h->cfg.device));
+    int rc = stage_inputs(h, x, g_z, U_in);
+    if (rc) return rc;
+    const MppiArgs a = mppi_args(h, 0);
+    const MppiBuffers b = mppi_bufs(h);
+    CU(h, launch_mppi_rollout(h->cfg.dtype, h->cfg.noise, h->ep, a, b, h->stream));
+    CU(h, launch_mppi_finalize(h->cfg.dtype, 1, h->ep, a, b, h->stream));
+    h->launches += 2;
+    const size_t cnt = (size_t)h->g.B * (PART_HDR + h->g.H);
+    CU(h, cudaMemcpyAsync(rec_out, h->d_rank_part + (size_t)h->cfg.rank * cnt, cnt * sizeof(double),
+                          cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+int mpc_mppi_apply_partials(mpc_handle *h, const double *recs, double *u0, double *U_out, double *xs_out,
+                            double *cost_out) {
+    if (!h || !recs) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "not an MPPI handle");
+    CU(h, cudaSetDevice(h->cfg.device));
+    const int want_traj = (xs_out || cost_out) ? 1 : 0;
+    const size_t cnt = (size_t)h->cfg.world * h->g.B * (PART_HDR + h->g.H);
+    CU(h, cudaMemcpyAsync(h->d_rank_part, recs, cnt * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CU(h, launch_mppi_finalize(h->cfg.dtype, 2, h->ep, mppi_args(h, want_traj), mppi_bufs(h), h->stream));
+    h->launches++;
+    h->solves++;
+    return fetch_outputs(h, want_traj, u0, U_out, xs_out, cost_out);
+}
+
+int mpc_mppi_get_costs(mpc_handle *h, double *S_out) {
+    if (!h || !S_out) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "not an MPPI handle");
+    CU(h, cudaSetDevice(h->cfg.device));
+    const Geometry &g = h->g;
+    CU(h, cudaMemcpy2DAsync(S_out, (size_t)g.K_local * sizeof(double), h->d_S, (size_t)g.Kpad * sizeof(double),
+                            (size_t)g.K_local * sizeof(double), g.B, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- CEM
+static int cem_enqueue_iter(mpc_handle *h, int iter) {
+    const CemArgs a = cem_args(h, iter, 0);
+    const CemBuffers b = cem_bufs(h);
+    CU(h, launch_cem_rollout(h->cfg.dtype, h->cfg.noise, h->ep, a, b, h->stream));
+    CU(h, launch_cem_select(a, b, h->stream));
+    CU(h, launch_cem_refit(h->cfg.dtype, h->cfg.noise, a, b, h->stream));
+    h->launches += 3;
+    return MPC_OK;
+}
+
+int mpc_cem_begin(mpc_handle *h, const double *x, const double *g_z, const double *U_in) {
+    if (!h) return MPC_EINVAL;
+    if (h->cfg.agent != MPC_AGENT_CEM) return fail(h, MPC_ESTATE, "not a CEM handle");
+    CU(h, cudaSetDevice(h->cfg.device));
+    int rc = stage_inputs(h, x, g_z, U_in);
+    if (rc) return rc;
+    CU(h, launch_cem_reset(cem_args(h, 0, 0), cem_bufs(h), h->stream));
+    h->launches++;
+    h->cem_iter = 0;
+    h->cem_open = true;
+    return MPC_OK;
+}
+
+int mpc_cem_iterate(mpc_handle *h, const double *z_KH, int32_t *done) {
+    if (!h) return MPC_EINVAL;
+    if (!h->cem_open) return fail(h, MPC_ESTATE, "mpc_cem_iterate without mpc_cem_begin");
+    if (h->cem_iter >= h->cfg.max_iter) return fail(h, MPC_ESTATE, "more than max_iter = %d iterations", h->cfg.max_iter);
+    CU(h, cudaSetDevice(h->cfg.device));
+    const Geometry &g = h->g;
+    if (h->cfg.noise == MPC_NOISE_TENSOR) {
+        if (!z_KH) return fail(h, MPC_EINVAL, "TENSOR noise mode needs the standard normals of this iteration");
+        const size_t n = (size_t)g.K_local * g.H;
+        int rc = ensure_scratch(h, n);
+        if (rc) return rc;
+        CU(h, cudaMemcpyAsync(h->d_scratch, z_KH + (size_t)g.k_begin * g.H, n * sizeof(double), cudaMemcpyHostToDevice,
+                              h->stream));
+        CU(h, launch_transpose_noise(h->cfg.dtype, h->d_scratch, h->d_noise, g.K_local, g.Kpad, g.H, h->stream));
+        h->launches++;
+    }
+    int rc = cem_enqueue_iter(h, h->cem_iter);
+    if (rc) return rc;
+    h->cem_iter++;
+    int sel[2] = {0, 0};
+    CU(h, cudaMemcpyAsync(sel, h->d_sel, sizeof sel, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    if (done) *done = sel[0];
+    return MPC_OK;
+}
+
+static int cem_finish(mpc_handle *h, int want_traj, double *u0, double *U_out, double *xs_out, double *cost_out,
+                      int32_t *iters_out) {
+    CU(h, launch_cem_finish(h->cfg.dtype, h->ep, cem_args(h, 0, want_traj), cem_bufs(h), h->stream));
+    h->launches++;
+    CU(h, cudaMemcpyAsync(h->h_out, h->d_out, h->out_elems * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    const Geometry &g = h->g;
+    const double *o = h->h_out;
+    if (u0) u0[0] = o[0];
+    if (U_out) memcpy(U_out, o + 1, g.H * sizeof(double));
+    if (want_traj) {
+        if (cost_out) cost_out[0] = o[1 + g.H];
+        if (xs_out) memcpy(xs_out, o + 2 + g.H, (size_t)(g.H + 1) * h->ns * sizeof(double));
+    }
+    h->last_iters = (int)o[h->out_stride];
+    if (iters_out) *iters_out = h->last_iters;
+    h->cem_open = false;
+    h->solves++;
+    return MPC_OK;
+}
+
+int mpc_cem_end(mpc_handle *h, double *u0, double *U_out, double *xs_out, double *cost_out) {
+    if (!h) return MPC_EINVAL;
+    if (!h->cem_open) return fail(h, MPC_ESTATE, "mpc_cem_end without mpc_cem_begin");
+    CU(h, cudaSetDevice(h->cfg.device));
+    return cem_finish(h, (xs_out || cost_out) ? 1 : 0, u0, U_out, xs_out, cost_out, nullptr);
+}
+
+int mpc_cem_solve(mpc_handle *h, const double *x, const double *g_z, const double *U_in, double *u0, double *U_out,
+                  double *xs_out, double *cost_out, int32_t *iters_out) {
+    if (!h) return MPC_EINVAL;
+    if (h->cfg.agent != MPC_AGENT_CEM) return fail(h, MPC_ESTATE, "not a CEM handle");
+    if (h->cfg.noise != MPC_NOISE_PHILOX)
+        return fail(h, MPC_ESTATE, "mpc_cem_solve needs PHILOX noise; use begin/iterate/end with host noise");
+    int rc = mpc_cem_begin(h, x, g_z, U_in);
+    if (rc) return rc;
+    for (int it = 0; it < h->cfg.max_iter; ++it) {  // later iterations return at once when the done flag is set
+        rc = cem_enqueue_iter(h, it);
+        if (rc) return rc;
+    }
+    h->cem_iter = h->cfg.max_iter;
+    return cem_finish(h, (xs_out || cost_out) ? 1 : 0, u0, U_out, xs_out, cost_out, iters_out);
+}
+
+int mpc_cem_get_rewards(mpc_handle *h, int32_t iter, double *R_out) {
+    if (!h || !R_out) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.agent != MPC_AGENT_CEM) return fail(h, MPC_ESTATE, "not a CEM handle");
+    if (iter < 0 || iter >= h->cfg.max_iter) return fail(h, MPC_EINVAL, "iteration %d out of range", iter);
+    CU(h, cudaSetDevice(h->cfg.device));
+    CU(h, cudaMemcpyAsync(R_out, h->d_R + (size_t)iter * h->g.Kpad, (size_t)h->g.K_local * sizeof(double),
+                          cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+int mpc_cem_get_elites(mpc_handle *h, int32_t iter, int32_t *idx_out) {
+    if (!h || !idx_out) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.agent != MPC_AGENT_CEM) return fail(h, MPC_ESTATE, "not a CEM handle");
+    if (iter < 0 || iter >= h->cfg.max_iter) return fail(h, MPC_EINVAL, "iteration %d out of range", iter);
+    CU(h, cudaSetDevice(h->cfg.device));
+    CU(h, cudaMemcpyAsync(idx_out, h->d_elite + (size_t)iter * h->cfg.n_elite, (size_t)h->cfg.n_elite * sizeof(int),
+                          cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+int mpc_cem_get_std(mpc_handle *h, double *std_out) {
+    if (!h || !std_out) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.agent != MPC_AGENT_CEM) return fail(h, MPC_ESTATE, "not a CEM handle");
+    CU(h, cudaSetDevice(h->cfg.device));
+    CU(h, cudaMemcpyAsync(std_out, h->d_sd, (size_t)h->g.H * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- nominal rollout
+int mpc_simulate(mpc_handle *h, const double *x, const double *us, const double *g_z, double *xs_out, double *cost_out) {
+    if (!h || !x || !us) return fail(h, MPC_EINVAL, "null argument");
+    CU(h, cudaSetDevice(h->cfg.device));
+    const int H = h->g.H, ns = h->ns, nz = h->nz;
+    const size_t n_in = ns + (size_t)H + (size_t)H * nz, n_out = 1 + (size_t)(H + 1) * ns;
+    int rc = ensure_scratch(h, n_in + n_out);
+    if (rc) return rc;
+    std::string tmp((n_in + n_out) * sizeof(double), '\0');
+    double *hb = reinterpret_cast<double *>(&tmp[0]);
+    memcpy(hb, x, ns * sizeof(double));
+    memcpy(hb + ns, us, H * sizeof(double));
+    if (g_z) memcpy(hb + ns + H, g_z, (size_t)H * nz * sizeof(double));
+    double *d = h->d_scratch;
+    CU(h, cudaMemcpyAsync(d, hb, n_in * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CU(h, launch_simulate(h->cfg.dtype, h->ep, H, h->cfg.bounds_low, h->cfg.bounds_high, 0, d, d + ns, d + ns + H,
+                          d + n_in + 1, d + n_in, h->stream));
+    h->launches++;
+    CU(h, cudaMemcpyAsync(hb + n_in, d + n_in, n_out * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    if (cost_out) *cost_out = hb[n_in];
+    if (xs_out) memcpy(xs_out, hb + n_in + 1, (size_t)(H + 1) * ns * sizeof(double));
+    return MPC_OK;
+}
+
+int mpc_model_step(mpc_handle *h, int32_t n, const double *x, const double *u, const double *g, double *cost_out,
+                   double *xn_out) {
+    if (!h || !x || !u || n < 1) return fail(h, MPC_EINVAL, "bad argument");
+    CU(h, cudaSetDevice(h->cfg.device));
+    const int ns = h->ns, nz = h->nz;
+    const size_t n_in = (size_t)n * (ns + 1 + nz), n_out = (size_t)n * (1 + ns);
+    int rc = ensure_scratch(h, n_in + n_out);
+    if (rc) return rc;
+    double *d = h->d_scratch;
+    double *dx = d, *du = d + (size_t)n * ns, *dg = du + n, *dc = d + n_in, *dxn = dc + n;
+    CU(h, cudaMemcpyAsync(dx, x, (size_t)n * ns * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(du, u, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (g)
+        CU(h, cudaMemcpyAsync(dg, g, (size_t)n * nz * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    else
+        CU(h, cudaMemsetAsync(dg, 0, (size_t)n * nz * sizeof(double), h->stream));
+    CU(h, launch_model_step(h->cfg.dtype, h->ep, n, dx, du, dg, dc, dxn, h->stream));
+    h->launches++;
+    if (cost_out) CU(h, cudaMemcpyAsync(cost_out, dc, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (xn_out) CU(h, cudaMemcpyAsync(xn_out, dxn, (size_t)n * ns * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- multi-GPU
+int mpc_comm_create_id(void *id_out) {
+    if (!id_out) return MPC_EINVAL;
+    std::string err;
+    if (!nccl_load(&err)) return fail(nullptr, MPC_ENCCL, "%s", err.c_str());
+    ncclUniqueId id;
+    ncclResult_t r = g_nccl.GetUniqueId(&id);
+    if (r != 0) return fail(nullptr, MPC_ENCCL, "ncclGetUniqueId: %s", g_nccl.GetErrorString(r));
+    static_assert(sizeof(ncclUniqueId) == MPC_COMM_ID_BYTES, "id size");
+    memcpy(id_out, &id, sizeof id);
+    return MPC_OK;
+}
+
+int mpc_comm_init(mpc_handle *h, const void *id_bytes) {
+    if (!h || !id_bytes) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.world == 1) return MPC_OK;
+    std::string err;
+    if (!nccl_load(&err)) return fail(h, MPC_ENCCL, "%s", err.c_str());
+    CU(h, cudaSetDevice(h->cfg.device));
+    ncclUniqueId id;
+    memcpy(&id, id_bytes, sizeof id);
+    ncclResult_t r = g_nccl.CommInitRank(&h->comm, h->cfg.world, id, h->cfg.rank);
+    if (r != 0) return fail(h, MPC_ENCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString(r));
+    return MPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- measurement
+int mpc_upload_inputs(mpc_handle *h, const double *x, const double *g_z, const double *U_in) {
+    if (!h) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    int rc = stage_inputs(h, x, g_z, U_in);
+    if (rc) return rc;
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+int mpc_solve_enqueue(mpc_handle *h) {
+    if (!h) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    if (h->cfg.agent == MPC_AGENT_MPPI) return mppi_enqueue(h, 1);
+    if (h->cfg.noise != MPC_NOISE_PHILOX) return fail(h, MPC_ESTATE, "device-resident CEM solve needs PHILOX noise");
+    CU(h, launch_cem_reset(cem_args(h, 0, 0), cem_bufs(h), h->stream));
+    h->launches++;
+    for (int it = 0; it < h->cfg.max_iter; ++it) {
+        int rc = cem_enqueue_iter(h, it);
+        if (rc) return rc;
+    }
+    CU(h, launch_cem_finish(h->cfg.dtype, h->ep, cem_args(h, 0, 1), cem_bufs(h), h->stream));
+    h->launches++;
+    h->solves++;
+    return MPC_OK;
+}
+
+int mpc_download_outputs(mpc_handle *h, double *u0, double *U_out, double *xs_out, double *cost_out) {
+    if (!h) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    return fetch_outputs(h, 1, u0, U_out, xs_out, cost_out);
+}
+
+int mpc_timer_start(mpc_handle *h) {
+    if (!h) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    CU(h, cudaEventRecord(h->ev0, h->stream));
+    return MPC_OK;
+}
+
+int mpc_timer_stop(mpc_handle *h, float *ms_out) {
+    if (!h || !ms_out) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    CU(h, cudaEventRecord(h->ev1, h->stream));
+    CU(h, cudaEventSynchronize(h->ev1));
+    CU(h, cudaEventElapsedTime(ms_out, h->ev0, h->ev1));
+    return MPC_OK;
+}
+
+int mpc_set_profiling(mpc_handle *h, int32_t on) {
+    if (!h) return MPC_EINVAL;
+    h->profiling = on != 0;
+    return MPC_OK;
+}
+
+int mpc_get_rollout_ms(mpc_handle *h, float *ms_out) {
+    if (!h || !ms_out) return MPC_EINVAL;
+    if (!h->profiling) return fail(h, MPC_ESTATE, "profiling is off: call mpc_set_profiling(h, 1) before the solve");
+    CU(h, cudaSetDevice(h->cfg.device));
+    CU(h, cudaEventSynchronize(h->evr1));
+    CU(h, cudaEventElapsedTime(ms_out, h->evr0, h->evr1));
+    return MPC_OK;
+}
+
+int mpc_sync(mpc_handle *h) {
+    if (!h) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+int64_t mpc_launch_count(const mpc_handle *h) { return h ? h->launches : 0; }
+
+int mpc_get_geometry(const mpc_handle *h, int32_t out[6]) {
+    if (!h || !out) return MPC_EINVAL;
+    out[0] = h->g.grid;
+    out[1] = TILE;
+    out[2] = (int32_t)h->g.smem_rollout;
+    out[3] = h->g.total_tiles;
+    out[4] = h->g.K_local;
+    out[5] = h->g.k_begin;
+    return MPC_OK;
+}
+
+int mpc_flush_l2(mpc_handle *h) {
+    if (!h) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    if (!h->d_flush) {
+        h->flush_elems = (size_t)256 << 20 >> 2;  // 256 MiB > 126 MB of L2
+        CU(h, cudaMalloc(&h->d_flush, h->flush_elems * sizeof(float)));
+    }
+    CU(h, launch_fill(h->d_flush, h->flush_elems, (float)h->solves, h->stream));
+    h->launches++;
+    return MPC_OK;
+}
+
+int mpc_measure_fma_peak(int32_t device, int32_t dtype, double *tflops_out) {
+    if (!tflops_out) return MPC_EINVAL;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+        return fail(nullptr, MPC_ECUDA, "no such CUDA device %d", device);
+    CU(nullptr, cudaSetDevice(device));
+    int sms = 0;
+    CU(nullptr, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    float *sink = nullptr;
+    CU(nullptr, cudaMalloc(&sink, 4));
+    cudaEvent_t e0, e1;
+    CU(nullptr, cudaEventCreate(&e0));
+    CU(nullptr, cudaEventCreate(&e1));
+    const int blocks = sms * 8, iters = dtype == MPC_F32 ? 8192 : 4096;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        CU(nullptr, cudaEventRecord(e0, 0));
+        CU(nullptr, launch_fma_peak(dtype == MPC_F32 ? DT_F32 : DT_F64, sink, blocks, iters, 0));
+        CU(nullptr, cudaEventRecord(e1, 0));
+        CU(nullptr, cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CU(nullptr, cudaEventElapsedTime(&ms, e0, e1));
+        const double flops = (double)blocks * 256.0 * 16.0 * (double)iters * 2.0;
+        const double tf = flops / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(sink);
+    *tflops_out = best;
+    return MPC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,865 @@
+// kernels.cu — sm_100a device code of the sampling-MPC inner loop.
+//
+//   mppi_rollout_kernel   MPPI.f for every sample (mppi.py:35-48) fused with the softmin-weighted noise sum of
+//                         MPPI._calc_action (mppi.py:59-67): the noise tile is staged ONCE in shared memory by
+//                         bulk async copies (cp.async.bulk + mbarrier), rolled out with the state in registers,
+//                         then reused for sum_k w_k eps[k][t] with an online (running-min) rescaling, so the noise
+//                         tensor is read from HBM once per solve.
+//   mppi_finalize_kernel  merges the per-block partials (log-sum-exp style), planned_us += erg (mppi.py:69), and the
+//                         clipped plan's nominal rollout (agent.py:64-69,97-108).
+//   cem_*                 CEM._calc_action (cem.py:54-78): rollout of clip(mu + sd*z), radix top-n_elite select,
+//                         elite mean / std refit with alpha smoothing and the epsilon test.
+#include "kernels.cuh"
+#include "envs.cuh"
+#include "philox.cuh"
+
+#include <float.h>
+
+namespace mpc {
+
+// ------------------------------------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+// orders generic-proxy shared-memory accesses before later async-proxy (bulk copy) writes to the same buffer
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(__cvta_generic_to_global(src_gmem)), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+
+// ------------------------------------------------------------------------------------------------ reductions
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// all threads get the result; red must hold >= blockDim/32 doubles; contains two barriers
+template <bool IS_MIN>
+__device__ __forceinline__ double block_reduce(double v, double *red) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = IS_MIN ? warp_min(v) : warp_sum(v);
+    __syncthreads();  // protect red from the previous use
+    if (lane == 0) red[w] = v;
+    __syncthreads();
+    double r = red[0];
+    for (int i = 1; i < nw; ++i) r = IS_MIN ? fmin(r, red[i]) : r + red[i];
+    return r;
+}
+
+// Folded constants narrowed once on the host and passed by value: they live in the kernel-parameter constant bank,
+// so FFMA/DFMA read them as c[bank][offset] operands instead of holding registers.
+template <typename R>
+static EnvConst<R> make_env(const EnvParamsHost &ep) {
+    EnvConst<R> ec;
+    for (int i = 0; i < 24; ++i) ec.c[i] = (R)ep.c[i];
+    return ec;
+}
+
+// Nominal rollout of one plan by a single thread: Agent.simulate_trajectory (agent.py:97-108).
+// us: plan (already clipped by the caller if required), g_z rows per step, xs [H+1][ns] (nullable), returns cost.
+template <class Env, typename R>
+__device__ double nominal_rollout(const EnvConst<R> &ec, int H, const double *x0, const double *us, const double *g_z,
+                                  double *xs) {
+    constexpr int NS = Env::NS, NZ = Env::NS + 1;
+    R x[NS];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+        x[i] = (R)x0[i];
+        if (xs) xs[i] = x0[i];
+    }
+    double reward = 0.0;
+    for (int t = 0; t < H; ++t) {
+        R g[NZ];
+#pragma unroll
+        for (int i = 0; i < NZ; ++i) g[i] = (R)g_z[t * NZ + i];
+        const R c = Env::step(ec, x, (R)us[t], g);
+        reward += -(double)c;
+        if (xs) {
+#pragma unroll
+            for (int i = 0; i < NS; ++i) xs[(t + 1) * NS + i] = (double)x[i];
+        }
+    }
+    return -reward;
+}
+
+// ================================================================================================ MPPI rollout
+// Shared memory: [H][TILE] noise tile (R) | sU[H] (R) | sw[TILE] (R) | red[8] (double) | mbarrier
+template <typename R>
+struct RolloutSmem {
+    static __host__ __device__ size_t tile_bytes(int H) { return (size_t)H * TILE * sizeof(R); }
+    static __host__ __device__ size_t total(int H) {
+        size_t b = tile_bytes(H);
+        b += ((size_t)H * sizeof(R) + 15) / 16 * 16;
+        b += TILE * sizeof(R);
+        b += 8 * sizeof(double);
+        b += 16;
+        return b;
+    }
+};
+
+template <class Env, typename R, int NOISE>
+__global__ void __launch_bounds__(TILE) mppi_rollout_kernel(const MppiArgs a, const EnvConst<R> ec,
+                                                           const R *__restrict__ noise,
+                                                           const double *__restrict__ x0g,
+                                                           const double *__restrict__ g_z,
+                                                           const double *__restrict__ Ug, double *__restrict__ S_out,
+                                                           double *__restrict__ part) {
+    constexpr int NS = Env::NS, NZ = Env::NS + 1;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int H = a.g.H;
+    R *tile = reinterpret_cast<R *>(smem_raw);
+    unsigned char *p = smem_raw + RolloutSmem<R>::tile_bytes(H);
+    R *sU = reinterpret_cast<R *>(p);
+    p += ((size_t)H * sizeof(R) + 15) / 16 * 16;
+    R *sw = reinterpret_cast<R *>(p);
+    p += TILE * sizeof(R);
+    double *red = reinterpret_cast<double *>(p);
+    p += 8 * sizeof(double);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(p);
+
+    const int tid = threadIdx.x;
+
+    const int tile0 = blockIdx.x * a.g.chunk;
+    const int tile1 = min(tile0 + a.g.chunk, a.g.total_tiles);
+    if (tile0 >= tile1) return;
+
+    if (NOISE == NOISE_TENSOR) {
+        if (tid == 0) {
+            mbar_init(bar, 1);
+            fence_mbar_init();
+        }
+        __syncthreads();
+    }
+
+    // running softmin state of the current solve (identical in every thread) and this thread's E slots
+    int cur = -1;
+    double beta_run = INFINITY, eta_run = 0.0;
+    double E_run[MAX_EH];
+    R g[NZ];
+    R xinit[NS];
+    uint32_t phase = 0;
+    const R pert = (R)a.pert;
+
+    auto flush = [&]() {
+        const int first_block = (int)(((long long)cur * a.g.tiles_per_solve) / a.g.chunk);
+        const int slot = blockIdx.x - first_block;
+        double *rec = part + ((size_t)cur * a.g.max_parts + slot) * (PART_HDR + H);
+        if (tid == 0) {
+            rec[0] = beta_run;
+            rec[1] = eta_run;
+        }
+#pragma unroll
+        for (int j = 0; j < MAX_EH; ++j) {
+            const int t = tid + j * TILE;
+            if (t < H) rec[PART_HDR + t] = E_run[j];
+        }
+    };
+
+    for (int tg = tile0; tg < tile1; ++tg) {
+        const int b = tg / a.g.tiles_per_solve;
+        const int kt = tg - b * a.g.tiles_per_solve;
+        if (b != cur) {
+            if (cur >= 0) flush();
+            cur = b;
+            beta_run = INFINITY;
+            eta_run = 0.0;
+#pragma unroll
+            for (int j = 0; j < MAX_EH; ++j) E_run[j] = 0.0;
+            __syncthreads();  // nobody still reads sU of the previous solve
+            for (int t = tid; t < H; t += TILE) sU[t] = (R)Ug[(size_t)b * H + t];
+#pragma unroll
+            for (int i = 0; i < NZ; ++i) g[i] = (R)g_z[(size_t)b * H * NZ + i];  // goal row 0 (model.py:34,38)
+#pragma unroll
+            for (int i = 0; i < NS; ++i) xinit[i] = (R)x0g[(size_t)b * NS + i];
+        }
+        // ---- stage the [H][TILE] noise tile ------------------------------------------------------------
+        if (NOISE == NOISE_TENSOR) {
+            __syncthreads();  // the previous tile's readers are done (generic proxy) ...
+            if (tid == 0) {
+                fence_proxy_async();  // ... before the async proxy overwrites it
+                const R *src = noise + (a.noise_batched ? (size_t)b * H * a.g.Kpad : 0) + (size_t)kt * TILE;
+                mbar_expect_tx(bar, (uint32_t)(H * TILE * sizeof(R)));
+                for (int t = 0; t < H; ++t)
+                    bulk_g2s(tile + (size_t)t * TILE, src + (size_t)t * a.g.Kpad, TILE * sizeof(R), bar);
+            }
+        }
+        __syncthreads();  // sU visible
+        const int kl = kt * TILE + tid;  // local sample index
+        const bool valid = kl < a.g.K_local;
+        R x[NS];
+#pragma unroll
+        for (int i = 0; i < NS; ++i) x[i] = xinit[i];
+        double S = 0.0;
+        if (NOISE == NOISE_TENSOR) {
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+            for (int t = 0; t < H; ++t) {
+                const R e = tile[t * TILE + tid];
+                const R u = sU[t] + e;                       // mppi.py:39
+                const R c = Env::step(ec, x, u, g);          // mppi.py:43-44
+                S += (double)(c + pert * u * e);             // mppi.py:45-46
+            }
+        } else {
+            const uint32_t kglob = (uint32_t)(a.g.k_begin + kl);
+            const R sig = (R)a.sigma;
+            for (int t4 = 0; t4 < H; t4 += 4) {
+                float z[4];
+                philox_normal4(a.seed, 0u, a.draw, kglob, (uint32_t)(t4 >> 2), z);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int t = t4 + i;
+                    if (t < H) {
+                        const R e = sig * (R)z[i];
+                        tile[t * TILE + tid] = e;
+                        const R u = sU[t] + e;
+                        const R c = Env::step(ec, x, u, g);
+                        S += (double)(c + pert * u * e);
+                    }
+                }
+            }
+        }
+        if (!valid) S = INFINITY;
+        if (valid) S_out[(size_t)b * a.g.Kpad + kl] = S;
+        // ---- online softmin: rescale the running sums to the new minimum (mppi.py:59-62) ------------------
+        const double beta_tile = block_reduce<true>(S, red);
+        const double beta_new = fmin(beta_run, beta_tile);
+        const double scale_old = (eta_run == 0.0) ? 0.0 : exp(a.neg_inv_lam * (beta_run - beta_new));
+        const double w = valid ? exp(a.neg_inv_lam * (S - beta_new)) : 0.0;
+        sw[tid] = (R)w;
+        const double eta_tile = block_reduce<false>(w, red);  // its barriers also publish sw and the Philox tile
+        eta_run = eta_run * scale_old + eta_tile;
+        beta_run = beta_new;
+        // ---- E[t] += sum_k w_k eps[k][t]   (thread t owns E[t]; rotated start => no bank conflicts) --------
+#pragma unroll
+        for (int j = 0; j < MAX_EH; ++j) {
+            const int t = tid + j * TILE;
+            if (t < H) {
+                const R *row = tile + (size_t)t * TILE;
+                R acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
+#pragma unroll 4
+                for (int i = 0; i < TILE; i += 4) {
+                    const int k0 = (i + tid) & (TILE - 1), k1 = (i + 1 + tid) & (TILE - 1),
+                              k2 = (i + 2 + tid) & (TILE - 1), k3 = (i + 3 + tid) & (TILE - 1);
+                    acc0 = M<R>::fma(sw[k0], row[k0], acc0);
+                    acc1 = M<R>::fma(sw[k1], row[k1], acc1);
+                    acc2 = M<R>::fma(sw[k2], row[k2], acc2);
+                    acc3 = M<R>::fma(sw[k3], row[k3], acc3);
+                }
+                E_run[j] = E_run[j] * scale_old + (double)((acc0 + acc1) + (acc2 + acc3));
+            }
+        }
+    }
+    flush();
+}
+
+// ================================================================================================ MPPI finalize
+// One block per solve.  src records [count][2+H] -> (beta, eta, E).  STAGE 0/2 apply, STAGE 1 writes a rank record.
+template <class Env, typename R>
+__global__ void __launch_bounds__(256) mppi_finalize_kernel(const MppiArgs a, const EnvConst<R> ec, const int stage,
+                                                            const double *__restrict__ part,
+                                                            double *__restrict__ rank_part,
+                                                            const double *__restrict__ x0g,
+                                                            const double *__restrict__ g_z, double *__restrict__ Ug,
+                                                            double *__restrict__ out) {
+    constexpr int NS = Env::NS, NZ = Env::NS + 1;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int H = a.g.H, b = blockIdx.x, tid = threadIdx.x;
+    const int rec_len = PART_HDR + H;
+    __shared__ double red[8];
+    double *sscale = reinterpret_cast<double *>(smem_raw);  // [count]
+    double *sUc = sscale + ((stage == 2) ? a.world : a.g.max_parts);  // [H] clipped plan
+
+    const double *src;
+    int count;
+    size_t stride;  // between records of the same solve
+    if (stage == 2) {
+        src = rank_part + (size_t)b * rec_len;
+        count = a.world;
+        stride = (size_t)a.g.B * rec_len;
+    } else {
+        const int first = (int)(((long long)b * a.g.tiles_per_solve) / a.g.chunk);
+        const int last = (int)((((long long)(b + 1)) * a.g.tiles_per_solve - 1) / a.g.chunk);
+        count = last - first + 1;
+        src = part + (size_t)b * a.g.max_parts * rec_len;
+        stride = rec_len;
+    }
+    double m = INFINITY;
+    for (int j = tid; j < count; j += blockDim.x) m = fmin(m, src[j * stride]);
+    const double beta = block_reduce<true>(m, red);
+    double es = 0.0;
+    for (int j = tid; j < count; j += blockDim.x) {
+        const double bj = src[j * stride];
+        const double sc = (bj == INFINITY) ? 0.0 : exp(a.neg_inv_lam * (bj - beta));
+        sscale[j] = sc;
+        es += sc * src[j * stride + 1];
+    }
+    const double eta = block_reduce<false>(es, red);  // barriers publish sscale
+    double *U = Ug + (size_t)b * H;
+    double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
+    for (int t = tid; t < H; t += blockDim.x) {
+        double e0 = 0.0, e1 = 0.0, e2 = 0.0, e3 = 0.0;
+        int j = 0;
+        for (; j + 3 < count; j += 4) {
+            e0 += sscale[j] * src[(size_t)j * stride + PART_HDR + t];
+            e1 += sscale[j + 1] * src[(size_t)(j + 1) * stride + PART_HDR + t];
+            e2 += sscale[j + 2] * src[(size_t)(j + 2) * stride + PART_HDR + t];
+            e3 += sscale[j + 3] * src[(size_t)(j + 3) * stride + PART_HDR + t];
+        }
+        for (; j < count; ++j) e0 += sscale[j] * src[(size_t)j * stride + PART_HDR + t];
+        const double E = (e0 + e1) + (e2 + e3);
+        if (stage == 1) {
+            rank_part[((size_t)a.rank * a.g.B + b) * rec_len + PART_HDR + t] = E;
+        } else {
+            const double un = U[t] + (1.0 / eta) * E;  // w = (1/eta)*tmp ; planned_us += erg   mppi.py:62,69
+            U[t] = un;
+            o[1 + t] = un;
+            sUc[t] = fmin(fmax(un, a.lo), a.hi);  // agent.py:64-65
+        }
+    }
+    if (stage == 1) {
+        if (tid == 0) {
+            double *rec = rank_part + ((size_t)a.rank * a.g.B + b) * rec_len;
+            rec[0] = beta;
+            rec[1] = eta;
+        }
+        return;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        o[0] = U[0];  // u0 = planned_us[0]  (mppi.py:71)
+        if (a.want_traj) {
+            o[1 + H] = nominal_rollout<Env, R>(ec, H, x0g + (size_t)b * NS, sUc, g_z + (size_t)b * H * NZ, o + 2 + H);
+        }
+    }
+}
+
+// ================================================================================================ noise utilities
+// [K_local][H] float64 (reference layout, du = 1) -> [H][Kpad] in the rollout dtype, padding zero-filled.
+template <typename R>
+__global__ void transpose_noise_kernel(const double *__restrict__ src, R *__restrict__ dst, int K_local, int Kpad,
+                                       int H) {
+    __shared__ double t[32][33];
+    const int k0 = blockIdx.x * 32, h0 = blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int k = k0 + r, h = h0 + threadIdx.x;
+        t[r][threadIdx.x] = (k < K_local && h < H) ? src[(size_t)k * H + h] : 0.0;
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int h = h0 + r, k = k0 + threadIdx.x;
+        if (h < H && k < Kpad) dst[(size_t)h * Kpad + k] = (R)t[threadIdx.x][r];
+    }
+}
+
+template <typename R>
+__global__ void philox_fill_kernel(R *__restrict__ dst, int K_local, int k_begin, int Kpad, int H, double scale,
+                                   uint64_t seed, uint32_t draw, uint32_t stream) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= Kpad) return;
+    const bool valid = k < K_local;
+    for (int t4 = 0; t4 < H; t4 += 4) {
+        float z[4] = {0.f, 0.f, 0.f, 0.f};
+        if (valid) philox_normal4(seed, stream, draw, (uint32_t)(k_begin + k), (uint32_t)(t4 >> 2), z);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (t4 + i < H) dst[(size_t)(t4 + i) * Kpad + k] = (R)scale * (R)z[i];
+    }
+}
+
+__global__ void philox_materialize_kernel(double *__restrict__ dst, int K_local, int k_begin, int H, uint64_t seed,
+                                          uint32_t draw, uint32_t stream) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K_local) return;
+    for (int t4 = 0; t4 < H; t4 += 4) {
+        float z[4];
+        philox_normal4(seed, stream, draw, (uint32_t)(k_begin + k), (uint32_t)(t4 >> 2), z);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (t4 + i < H) dst[(size_t)k * H + t4 + i] = (double)z[i];
+    }
+}
+
+// ================================================================================================ CEM
+// sel[] layout
+enum { SEL_DONE = 0, SEL_ITERS = 1, SEL_NOTSMALL = 2, SEL_BLOCKS = 3, SEL_WORDS = 8 };
+
+__device__ __forceinline__ unsigned long long reward_key(double r) {
+    // order-preserving map double -> u64 (larger reward => larger key); NaN sorts below everything
+    if (r != r) return 0ull;
+    unsigned long long u = (unsigned long long)__double_as_longlong(r);
+    return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
+}
+
+// CEM.f (cem.py:42-48) for samples clip(mu + sd*z) (cem.py:58-60), one thread per sample.
+template <class Env, typename R, int NOISE>
+__global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, const EnvConst<R> ec,
+                                                          const R *__restrict__ zt, const double *__restrict__ x0g,
+                                                          const double *__restrict__ g_z,
+                                                          const double *__restrict__ mu,
+                                                          const double *__restrict__ sd, double *__restrict__ Rhist,
+                                                          unsigned long long *__restrict__ keys,
+                                                          const int *__restrict__ sel) {
+    constexpr int NS = Env::NS, NZ = Env::NS + 1;
+    if (sel[SEL_DONE]) return;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int H = a.g.H, tid = threadIdx.x;
+    R *smu = reinterpret_cast<R *>(smem_raw);
+    R *ssd = smu + H;
+    for (int t = tid; t < H; t += TILE) {
+        smu[t] = (R)mu[t];
+        ssd[t] = (R)sd[t];
+    }
+    R g[NZ], x[NS];
+#pragma unroll
+    for (int i = 0; i < NZ; ++i) g[i] = (R)g_z[i];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) x[i] = (R)x0g[i];
+    __syncthreads();
+    const int k = blockIdx.x * TILE + tid;
+    if (k >= a.g.K_local) return;
+    const R lo = (R)a.lo, hi = (R)a.hi;
+    double reward = 0.0;
+    if (NOISE == NOISE_TENSOR) {
+        for (int t = 0; t < H; ++t) {
+            const R z = zt[(size_t)t * a.g.Kpad + k];
+            const R u = clip(M<R>::fma(ssd[t], z, smu[t]), lo, hi);
+            reward += -(double)Env::step(ec, x, u, g);
+        }
+    } else {
+        const uint32_t kglob = (uint32_t)(a.g.k_begin + k);
+        for (int t4 = 0; t4 < H; t4 += 4) {
+            float z[4];
+            philox_normal4(a.seed, 1u, (uint32_t)a.iter, kglob, (uint32_t)(t4 >> 2), z);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int t = t4 + i;
+                if (t < H) {
+                    const R u = clip(M<R>::fma(ssd[t], (R)z[i], smu[t]), lo, hi);
+                    reward += -(double)Env::step(ec, x, u, g);
+                }
+            }
+        }
+    }
+    Rhist[(size_t)a.iter * a.g.Kpad + k] = reward;
+    keys[k] = reward_key(reward);
+}
+
+// exclusive block scan of one int per thread (blockDim = 1024); returns exclusive prefix, *total = block total
+__device__ __forceinline__ int block_scan_excl(int v, int *swarp, int *total) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    __syncthreads();
+    if (lane == 31) swarp[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        int s = (lane < nw) ? swarp[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, s, o);
+            if (lane >= o) s += n;
+        }
+        swarp[32 + lane] = s;  // inclusive warp totals
+    }
+    __syncthreads();
+    const int base = (w == 0) ? 0 : swarp[32 + w - 1];
+    *total = swarp[32 + nw - 1];
+    return base + inc - v;
+}
+
+// Radix select of the n_elite largest keys (np.argsort(-rewards)[:n_elite], cem.py:67) by one block:
+// 8 passes of 8 bits from the top find the n_elite-th largest key T; then an ordered compaction emits, ascending by
+// index, every k with key > T plus the lowest-index keys equal to T needed to reach n_elite.
+__global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const unsigned long long *__restrict__ keys,
+                                                         int *__restrict__ elite_hist, int *__restrict__ sel) {
+    if (sel[SEL_DONE]) return;
+    __shared__ int hist[256];
+    __shared__ int swarp[64];
+    __shared__ unsigned long long s_prefix;
+    __shared__ int s_want;
+    const int K = a.g.K_local, tid = threadIdx.x;
+    if (tid == 0) {
+        s_prefix = 0ull;
+        s_want = a.n_elite;
+    }
+    unsigned long long mask = 0ull;
+    for (int shift = 56; shift >= 0; shift -= 8) {
+        if (tid < 256) hist[tid] = 0;
+        __syncthreads();
+        const unsigned long long prefix = s_prefix;
+        const int want = s_want;
+        for (int k = tid; k < K; k += blockDim.x) {
+            const unsigned long long key = keys[k];
+            if ((key & mask) == prefix) atomicAdd(&hist[(int)((key >> shift) & 0xffull)], 1);
+        }
+        __syncthreads();
+        // descending inclusive scan over the 256 bins: thread i looks at bin 255 - i
+        const int v = (tid < 256) ? hist[255 - tid] : 0;
+        int total;
+        const int excl = block_scan_excl(v, swarp, &total);
+        if (tid < 256 && excl < want && excl + v >= want) {
+            s_prefix = prefix | ((unsigned long long)(255 - tid) << shift);
+            s_want = want - excl;
+        }
+        mask |= 0xffull << shift;
+        __syncthreads();
+    }
+    const unsigned long long T = s_prefix;
+    const int want_ties = s_want;  // how many keys == T belong to the elite set
+    int *elite = elite_hist + (size_t)a.iter * a.n_elite;
+    int tie_base = 0, sel_base = 0;
+    for (int k0 = 0; k0 < K; k0 += blockDim.x) {
+        const int k = k0 + tid;
+        const unsigned long long key = (k < K) ? keys[k] : 0ull;
+        const int is_tie = (k < K && key == T) ? 1 : 0;
+        const int is_gt = (k < K && key > T) ? 1 : 0;
+        int tot_tie, tot_sel;
+        const int tie_rank = tie_base + block_scan_excl(is_tie, swarp, &tot_tie);
+        const int chosen = is_gt | (is_tie && tie_rank < want_ties);
+        const int pos = sel_base + block_scan_excl(chosen, swarp, &tot_sel);
+        if (chosen && pos < a.n_elite) elite[pos] = k;
+        tie_base += tot_tie;
+        sel_base += tot_sel;
+    }
+}
+
+// Elite refit (cem.py:69-76): one block per time step t.
+template <typename R, int NOISE>
+__global__ void __launch_bounds__(128) cem_refit_kernel(const CemArgs a, const R *__restrict__ zt,
+                                                       const int *__restrict__ elite_hist, double *__restrict__ mu,
+                                                       double *__restrict__ sd, int *__restrict__ sel) {
+    if (sel[SEL_DONE]) return;
+    __shared__ double red[8];
+    const int t = blockIdx.x, tid = threadIdx.x, n = a.n_elite;
+    const int *elite = elite_hist + (size_t)a.iter * n;
+    const R m0 = (R)mu[t], s0 = (R)sd[t], lo = (R)a.lo, hi = (R)a.hi;
+    auto sample = [&](int e) -> double {
+        const int k = elite[e];
+        R z;
+        if (NOISE == NOISE_TENSOR) {
+            z = zt[(size_t)t * a.g.Kpad + k];
+        } else {
+            float z4[4];
+            philox_normal4(a.seed, 1u, (uint32_t)a.iter, (uint32_t)(a.g.k_begin + k), (uint32_t)(t >> 2), z4);
+            z = (R)z4[t & 3];
+        }
+        return (double)clip(M<R>::fma(s0, z, m0), lo, hi);  // identical expression to the rollout's
+    };
+    double s = 0.0;
+    for (int e = tid; e < n; e += blockDim.x) s += sample(e);
+    const double mean = block_reduce<false>(s, red) / n;       // np.mean(elites, axis=0)
+    double v = 0.0;
+    for (int e = tid; e < n; e += blockDim.x) {
+        const double d = sample(e) - mean;
+        v += d * d;
+    }
+    const double var = block_reduce<false>(v, red) / n;        // np.std: ddof = 0, two-pass
+    if (tid == 0) {
+        const double new_mu = a.alpha * mu[t] + (1 - a.alpha) * mean;     // cem.py:71-72
+        const double new_sd = a.alpha * sd[t] + (1 - a.alpha) * sqrt(var);  // cem.py:73
+        mu[t] = new_mu;
+        sd[t] = new_sd;
+        if (!(new_sd < a.epsilon)) atomicAdd(&sel[SEL_NOTSMALL], 1);
+        __threadfence();
+        const int arrived = atomicAdd(&sel[SEL_BLOCKS], 1);
+        if (arrived == (int)gridDim.x - 1) {  // last block: evaluate (std < epsilon).all()   cem.py:75-76
+            __threadfence();
+            const int notsmall = atomicAdd(&sel[SEL_NOTSMALL], 0);
+            sel[SEL_ITERS] = a.iter + 1;
+            sel[SEL_NOTSMALL] = 0;
+            sel[SEL_BLOCKS] = 0;
+            if (notsmall == 0) sel[SEL_DONE] = 1;
+        }
+    }
+}
+
+__global__ void cem_reset_kernel(const CemArgs a, double *__restrict__ sd, int *__restrict__ sel) {
+    for (int t = threadIdx.x; t < a.g.H; t += blockDim.x) sd[t] = a.sigma;  // std = self.std.copy()  cem.py:56
+    if (threadIdx.x < SEL_WORDS) sel[threadIdx.x] = 0;
+}
+
+// u0 = planned_us[0] (cem.py:77), plus the clipped plan's nominal rollout (agent.py:64-69).
+template <class Env, typename R>
+__global__ void cem_finish_kernel(const CemArgs a, const EnvConst<R> ec, const double *__restrict__ x0g,
+                                  const double *__restrict__ g_z, const double *__restrict__ mu,
+                                  const int *__restrict__ sel, double *__restrict__ out) {
+    constexpr int NS = Env::NS;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *sUc = reinterpret_cast<double *>(smem_raw);
+    const int H = a.g.H;
+    for (int t = threadIdx.x; t < H; t += blockDim.x) {
+        out[1 + t] = mu[t];
+        sUc[t] = fmin(fmax(mu[t], a.lo), a.hi);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        out[0] = mu[0];
+        out[2 + H + (H + 1) * NS] = (double)sel[SEL_ITERS];
+        if (a.want_traj) {
+            out[1 + H] = nominal_rollout<Env, R>(ec, H, x0g, sUc, g_z, out + 2 + H);
+        }
+    }
+}
+
+// ================================================================================================ small kernels
+template <class Env, typename R>
+__global__ void simulate_kernel(const EnvConst<R> ec, int H, double lo, double hi, int do_clip,
+                                const double *__restrict__ x0, const double *__restrict__ us,
+                                const double *__restrict__ g_z, double *__restrict__ xs, double *__restrict__ cost) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *sU = reinterpret_cast<double *>(smem_raw);
+    for (int t = threadIdx.x; t < H; t += blockDim.x) sU[t] = do_clip ? fmin(fmax(us[t], lo), hi) : us[t];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        *cost = nominal_rollout<Env, R>(ec, H, x0, sU, g_z, xs);
+    }
+}
+
+template <class Env, typename R>
+__global__ void model_step_kernel(const EnvConst<R> ec, int n, const double *__restrict__ xg,
+                                  const double *__restrict__ ug, const double *__restrict__ gg,
+                                  double *__restrict__ cost, double *__restrict__ xn) {
+    constexpr int NS = Env::NS, NZ = Env::NS + 1;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    R x[NS], g[NZ];
+#pragma unroll
+    for (int j = 0; j < NS; ++j) x[j] = (R)xg[(size_t)i * NS + j];
+#pragma unroll
+    for (int j = 0; j < NZ; ++j) g[j] = (R)gg[(size_t)i * NZ + j];
+    cost[i] = (double)Env::step(ec, x, (R)ug[i], g);
+#pragma unroll
+    for (int j = 0; j < NS; ++j) xn[(size_t)i * NS + j] = (double)x[j];
+}
+
+// FMA-pipe peak: 16 independent chains per thread, no memory traffic.
+template <typename R>
+__global__ void __launch_bounds__(256) fma_peak_kernel(float *sink, int iters) {
+    R a[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = (R)(threadIdx.x + i) * (R)1e-3;
+    const R m = (R)0.999, c = (R)1e-4;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) a[i] = M<R>::fma(a[i], m, c);
+    }
+    R s = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += a[i];
+    if (s == (R)123456789) sink[0] = (float)s;
+}
+
+__global__ void fill_kernel(float *p, size_t n, float v) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) p[i] = v;
+}
+
+// ================================================================================================ dispatch
+size_t mppi_rollout_smem(int dtype, int H) {
+    return dtype == DT_F32 ? RolloutSmem<float>::total(H) : RolloutSmem<double>::total(H);
+}
+
+template <class Env, typename R, int NOISE>
+static cudaError_t mppi_rollout_go(const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b, cudaStream_t s) {
+    auto kern = mppi_rollout_kernel<Env, R, NOISE>;
+    const size_t smem = RolloutSmem<R>::total(a.g.H);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kern<<<a.g.grid, TILE, smem, s>>>(a, make_env<R>(ep), (const R *)b.noise, b.x0, b.g_z, b.U, b.S, b.part);
+    return cudaGetLastError();
+}
+
+template <class Env, typename R, int NOISE>
+static int mppi_rollout_occ(int H) {
+    auto kern = mppi_rollout_kernel<Env, R, NOISE>;
+    const size_t smem = RolloutSmem<R>::total(H);
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, TILE, smem) != cudaSuccess) return 0;
+    return occ;
+}
+
+#define MPC_DISPATCH_ENV_DTYPE(ENVID, DTYPE, CALL)                                   \
+    do {                                                                             \
+        if ((DTYPE) == DT_F32) {                                                     \
+            typedef float R_;                                                        \
+            switch (ENVID) {                                                         \
+            case ENV_PENDULUM: { typedef Pendulum<R_> E_; CALL; } break;             \
+            case ENV_CARTPOLE: { typedef CartPole<R_> E_; CALL; } break;             \
+            default: { typedef Acrobot<R_> E_; CALL; } break;                        \
+            }                                                                        \
+        } else {                                                                     \
+            typedef double R_;                                                       \
+            switch (ENVID) {                                                         \
+            case ENV_PENDULUM: { typedef Pendulum<R_> E_; CALL; } break;             \
+            case ENV_CARTPOLE: { typedef CartPole<R_> E_; CALL; } break;             \
+            default: { typedef Acrobot<R_> E_; CALL; } break;                        \
+            }                                                                        \
+        }                                                                            \
+    } while (0)
+
+cudaError_t launch_mppi_rollout(int dtype, int noise, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                cudaStream_t s) {
+    cudaError_t e = cudaSuccess;
+    if (noise == NOISE_TENSOR)
+        MPC_DISPATCH_ENV_DTYPE(ep.env, dtype, (e = mppi_rollout_go<E_, R_, NOISE_TENSOR>(a, ep, b, s)));
+    else
+        MPC_DISPATCH_ENV_DTYPE(ep.env, dtype, (e = mppi_rollout_go<E_, R_, NOISE_PHILOX>(a, ep, b, s)));
+    return e;
+}
+
+int mppi_rollout_occupancy(int dtype, int noise, int env, int H) {
+    int occ = 0;
+    if (noise == NOISE_TENSOR)
+        MPC_DISPATCH_ENV_DTYPE(env, dtype, (occ = mppi_rollout_occ<E_, R_, NOISE_TENSOR>(H)));
+    else
+        MPC_DISPATCH_ENV_DTYPE(env, dtype, (occ = mppi_rollout_occ<E_, R_, NOISE_PHILOX>(H)));
+    return occ;
+}
+
+cudaError_t launch_mppi_finalize(int dtype, int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                 cudaStream_t s) {
+    const int count = (stage == 2) ? a.world : a.g.max_parts;
+    const size_t smem = ((size_t)count + a.g.H) * sizeof(double);
+    MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
+                           (mppi_finalize_kernel<E_, R_><<<a.g.B, 256, smem, s>>>(a, make_env<R_>(ep), stage, b.part, b.rank_part,
+                                                                                   b.x0, b.g_z, b.U, b.out)));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_transpose_noise(int dtype, const double *src, void *dst, int K_local, int Kpad, int H,
+                                   cudaStream_t s) {
+    dim3 grid((Kpad + 31) / 32, (H + 31) / 32), block(32, 8);
+    if (dtype == DT_F32)
+        transpose_noise_kernel<float><<<grid, block, 0, s>>>(src, (float *)dst, K_local, Kpad, H);
+    else
+        transpose_noise_kernel<double><<<grid, block, 0, s>>>(src, (double *)dst, K_local, Kpad, H);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_philox_fill(int dtype, void *dst, int K_local, int k_begin, int Kpad, int H, double scale,
+                               uint64_t seed, uint32_t draw, cudaStream_t s) {
+    const int grid = (Kpad + 127) / 128;
+    if (dtype == DT_F32)
+        philox_fill_kernel<float><<<grid, 128, 0, s>>>((float *)dst, K_local, k_begin, Kpad, H, scale, seed, draw, 0u);
+    else
+        philox_fill_kernel<double><<<grid, 128, 0, s>>>((double *)dst, K_local, k_begin, Kpad, H, scale, seed, draw, 0u);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_philox_materialize(double *dst, int K_local, int k_begin, int H, uint64_t seed, uint32_t draw,
+                                      cudaStream_t s) {
+    // stream id is folded into bit 31 of draw by the caller-facing API: MPPI uses stream 0, CEM stream 1
+    const uint32_t stream = draw >> 31, d = draw & 0x7fffffffu;
+    philox_materialize_kernel<<<(K_local + 127) / 128, 128, 0, s>>>(dst, K_local, k_begin, H, seed, d, stream);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cem_rollout(int dtype, int noise, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
+                               cudaStream_t s) {
+    const size_t smem = 2 * (size_t)a.g.H * sizeof(double);
+    const int grid = a.g.tiles_per_solve;
+    if (noise == NOISE_TENSOR)
+        MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
+                               (cem_rollout_kernel<E_, R_, NOISE_TENSOR><<<grid, TILE, smem, s>>>(
+                                   a, make_env<R_>(ep), (const R_ *)b.z, b.x0, b.g_z, b.mu, b.sd, b.R, b.keys, b.sel)));
+    else
+        MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
+                               (cem_rollout_kernel<E_, R_, NOISE_PHILOX><<<grid, TILE, smem, s>>>(
+                                   a, make_env<R_>(ep), (const R_ *)b.z, b.x0, b.g_z, b.mu, b.sd, b.R, b.keys, b.sel)));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    cem_select_kernel<<<1, 1024, 0, s>>>(a, b.keys, b.elite_idx, b.sel);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cem_refit(int dtype, int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    if (dtype == DT_F32) {
+        if (noise == NOISE_TENSOR)
+            cem_refit_kernel<float, NOISE_TENSOR><<<a.g.H, 128, 0, s>>>(a, (const float *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
+        else
+            cem_refit_kernel<float, NOISE_PHILOX><<<a.g.H, 128, 0, s>>>(a, (const float *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
+    } else {
+        if (noise == NOISE_TENSOR)
+            cem_refit_kernel<double, NOISE_TENSOR><<<a.g.H, 128, 0, s>>>(a, (const double *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
+        else
+            cem_refit_kernel<double, NOISE_PHILOX><<<a.g.H, 128, 0, s>>>(a, (const double *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cem_finish(int dtype, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    const size_t smem = (size_t)a.g.H * sizeof(double);
+    MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
+                           (cem_finish_kernel<E_, R_><<<1, 128, smem, s>>>(a, make_env<R_>(ep), b.x0, b.g_z, b.mu, b.sel, b.out)));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cem_reset(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    cem_reset_kernel<<<1, 128, 0, s>>>(a, b.sd, b.sel);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_simulate(int dtype, const EnvParamsHost &ep, int H, double lo, double hi, int do_clip,
+                            const double *x0, const double *us, const double *g_z, double *xs, double *cost,
+                            cudaStream_t s) {
+    const size_t smem = (size_t)H * sizeof(double);
+    MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
+                           (simulate_kernel<E_, R_><<<1, 64, smem, s>>>(make_env<R_>(ep), H, lo, hi, do_clip, x0, us, g_z, xs, cost)));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_model_step(int dtype, const EnvParamsHost &ep, int n, const double *x, const double *u,
+                              const double *g, double *cost, double *xn, cudaStream_t s) {
+    MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
+                           (model_step_kernel<E_, R_><<<(n + 127) / 128, 128, 0, s>>>(make_env<R_>(ep), n, x, u, g, cost, xn)));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaStream_t s) {
+    if (dtype == DT_F32)
+        fma_peak_kernel<float><<<blocks, 256, 0, s>>>(sink, iters);
+    else
+        fma_peak_kernel<double><<<blocks, 256, 0, s>>>(sink, iters);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s) {
+    fill_kernel<<<148 * 8, 256, 0, s>>>(p, n, v);
+    return cudaGetLastError();
+}
+
+}  // namespace mpc

@@ -1,0 +1,114 @@
+// kernels.cuh — launch-side declarations shared by kernels.cu (device code) and capi.cu (the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mpc {
+
+constexpr int TILE = 128;       // samples per noise tile == threads per rollout block
+constexpr int MAX_EH = 4;       // horizon slots per thread in the weighted-sum pass: H <= TILE * MAX_EH
+constexpr int PART_HDR = 2;     // partial record = [beta, eta, E[0..H-1]]
+
+enum { NOISE_TENSOR = 0, NOISE_PHILOX = 1 };
+enum { DT_F64 = 0, DT_F32 = 1 };
+
+struct EnvParamsHost {
+    int env;
+    double c[24];  // folded constants in float64 (see fold_env_params)
+};
+
+// Geometry of one handle's shard; identical for every solve.
+struct Geometry {
+    int K_local;          // samples of each solve owned by this handle
+    int k_begin;          // global index of the first one
+    int Kpad;             // K_local rounded up to a multiple of TILE (row stride of the noise tensor)
+    int H;
+    int B;                // batch of independent solves
+    int tiles_per_solve;  // Kpad / TILE
+    int total_tiles;      // B * tiles_per_solve
+    int chunk;            // consecutive tiles per rollout block
+    int grid;             // rollout blocks = ceil(total_tiles / chunk)
+    int max_parts;        // partial records per solve (blocks that can overlap one solve)
+    int ns;
+    size_t smem_rollout;  // dynamic shared memory of the rollout kernel
+};
+
+struct MppiArgs {
+    Geometry g;
+    double neg_inv_lam;   // -(1/lam)                       mppi.py:60
+    double pert;          // lam * pinv(std^2)              mppi.py:45-46
+    double sigma;
+    double lo, hi;        // action bounds (agent.py:64-65)
+    uint64_t seed;
+    uint32_t draw;        // Philox draw index
+    int noise_batched;    // TENSOR: 1 = one tensor per solve of the batch, 0 = shared
+    int want_traj;        // compute the clipped nominal rollout in the finalize kernel
+    int world;            // >1: finalize writes a rank partial instead of applying
+    int rank;
+};
+
+struct CemArgs {
+    Geometry g;
+    double sigma, lo, hi, alpha, epsilon;
+    int n_elite;
+    int iter;             // iteration index (Philox draw, history slot)
+    uint64_t seed;
+    int want_traj;
+};
+
+struct MppiBuffers {
+    const void *noise;     // R [Bn][H][Kpad]
+    const double *x0;      // [B][ns]
+    const double *g_z;     // [B][H][nz]
+    double *U;             // [B][H]   device-resident plan (in: before, out: after)
+    double *S;             // [B][Kpad]
+    double *part;          // [B][max_parts][2+H]
+    double *rank_part;     // [world][B][2+H]  (all-gather buffer; this rank writes slot `rank`)
+    double *out;           // [B][out_stride]: u0, U[H], cost, xs[(H+1)*ns]
+};
+
+struct CemBuffers {
+    const void *z;         // R [H][Kpad] standard normals of this iteration (TENSOR)
+    const double *x0;      // [ns]
+    const double *g_z;     // [H][nz]
+    double *mu;            // [H]
+    double *sd;            // [H]
+    double *R;             // [max_iter][Kpad] rewards history
+    unsigned long long *keys;  // [Kpad] order-preserving keys of this iteration
+    int *elite_idx;        // [max_iter][n_elite]
+    int *sel;              // scratch: [0]=done flag, [1]=iters executed, [2]=elite counter, ...
+    double *out;           // u0, U[H], cost, xs
+};
+
+// launches (kernels.cu); all return cudaGetLastError()
+cudaError_t launch_mppi_rollout(int dtype, int noise, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                cudaStream_t s);
+// stage: 0 = single GPU (merge block partials, apply, nominal rollout)
+//        1 = multi GPU first half  (merge block partials -> rank_part[rank])
+//        2 = multi GPU second half (merge rank partials, apply, nominal rollout)
+cudaError_t launch_mppi_finalize(int dtype, int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                 cudaStream_t s);
+cudaError_t launch_transpose_noise(int dtype, const double *src_KH, void *dst_HK, int K_local, int Kpad, int H,
+                                   cudaStream_t s);
+cudaError_t launch_philox_fill(int dtype, void *dst_HK, int K_local, int k_begin, int Kpad, int H, double scale,
+                               uint64_t seed, uint32_t draw, cudaStream_t s);
+cudaError_t launch_philox_materialize(double *dst_KH, int K_local, int k_begin, int H, uint64_t seed, uint32_t draw,
+                                      cudaStream_t s);
+cudaError_t launch_cem_rollout(int dtype, int noise, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
+                               cudaStream_t s);
+cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s);
+cudaError_t launch_cem_refit(int dtype, int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s);
+cudaError_t launch_cem_finish(int dtype, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s);
+cudaError_t launch_cem_reset(const CemArgs &a, const CemBuffers &b, cudaStream_t s);
+cudaError_t launch_simulate(int dtype, const EnvParamsHost &ep, int H, double lo, double hi, int do_clip,
+                            const double *x0, const double *us, const double *g_z, double *xs, double *cost,
+                            cudaStream_t s);
+cudaError_t launch_model_step(int dtype, const EnvParamsHost &ep, int n, const double *x, const double *u,
+                              const double *g, double *cost, double *xn, cudaStream_t s);
+cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaStream_t s);
+cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s);
+
+size_t mppi_rollout_smem(int dtype, int H);
+size_t cem_select_smem();
+
+}  // namespace mpc

@@ -1,0 +1,43 @@
+"""K-sharding across GPUs — host side.  One process per GPU; only the sample dimension shards (the reference's
+Pool.map fan-out over samples, mppi.py:55-57, becomes rank-local rollouts plus ONE small exchange per solve).
+
+Exchange record per rank and solve (float64, length 2 + H):
+    rec[0]   beta_r = min_k S_k over the rank's shard
+    rec[1]   eta_r  = sum_k exp(-(S_k - beta_r) / lam)
+    rec[2+t] E_r[t] = sum_k exp(-(S_k - beta_r) / lam) * eps[k][t]
+`merge_partials` is the specification of what the device does with the gathered records (mppi_finalize_kernel,
+stage 2); the transport is NCCL all-gather on the solver's stream (mpc_comm_init) or anything the caller has
+(mpc_mppi_rollout_partial / mpc_mppi_apply_partials).
+"""
+import numpy as np
+
+
+def shard_range(K, rank, world):
+    """Contiguous shard [k_begin, k_end) of rank `rank` — identical to the geometry computed in mpc_create."""
+    return K * rank // world, K * (rank + 1) // world
+
+
+def merge_partials(recs, lam):
+    """recs [world][2+H] -> (beta, eta, erg[H]) with erg = sum_k w_k eps[k] for the normalised weights of mppi.py:59-62."""
+    recs = np.asarray(recs, dtype=np.float64)
+    beta = recs[:, 0].min()
+    scale = np.exp(-(1 / lam) * (recs[:, 0] - beta))
+    eta = float(np.sum(scale * recs[:, 1]))
+    erg = (1 / eta) * (scale[:, None] * recs[:, 2:]).sum(axis=0)
+    return beta, eta, erg
+
+
+def broadcast_comm_id(create_id, group=None, src=0):
+    """Rank `src` creates the communicator id (bytes), everybody receives it through torch.distributed (any backend)."""
+    import torch
+    import torch.distributed as dist
+    if dist.get_rank(group) == src:
+        buf = torch.tensor(list(create_id()), dtype=torch.uint8)
+    else:
+        buf = torch.zeros(128, dtype=torch.uint8)
+    dev = None
+    if dist.get_backend(group) == "nccl":
+        dev = torch.device("cuda", torch.cuda.current_device())
+        buf = buf.to(dev)
+    dist.broadcast(buf, src=src, group=group)
+    return bytes(buf.cpu().tolist())

@@ -1,0 +1,344 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Every check calls the CUDA path through the C ABI
+(libmpcb200.so via ctypes) and compares with
+  * the committed golden fixtures produced by executing the reference (tests/golden, oracle/gen_golden.py), and
+  * the CPU oracle (oracle/mpc_oracle.c) on the same seeded inputs and the IDENTICAL noise tensor.
+
+Tolerances (BASELINE.json north_star): float64 mode rel 1e-12 on costs; float32 mode rel 1e-5 on costs.
+Actions/plans are a softmin of the costs, so their error is the cost error amplified by max|S|/lam;
+the bound used for them is written next to each assertion.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import mpc_b200
+from mpc_b200 import capi
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+ENVS = ["pendulum", "cartpole", "acrobot"]
+ENV_ID = {"pendulum": 0, "cartpole": 1, "acrobot": 2}
+START = {"pendulum": np.array([np.pi, 0.0]), "cartpole": np.array([0.0, 0.0, np.pi, 0.0]),
+         "acrobot": np.array([0.0, 0.0, 0.0, 0.0])}
+F64_COST_RTOL = 1e-12
+F32_COST_RTOL = 1e-5
+
+
+def _load(golden_dir, name):
+    d = np.load(os.path.join(golden_dir, name))
+    meta = json.loads(str(d["meta"])) if "meta" in d.files else None
+    return d, meta
+
+
+def _solver(kind, env, K, H, **kw):
+    return capi.Solver(kind, ENV_ID[env], orc.default_params(env), K=K, H=H, bounds=orc.BOUNDS[env], **kw)
+
+
+def _plan_tol(S, lam, cost_rtol):
+    """Error bound for the softmin-weighted plan: relative weight error ~ cost error / lam."""
+    return max(10 * cost_rtol, 4 * cost_rtol * float(np.max(np.abs(S))) / lam)
+
+
+# ------------------------------------------------------------------------------------------- single steps
+@pytest.mark.parametrize("env", ENVS)
+@pytest.mark.parametrize("dtype", ["f64", "f32"])
+def test_model_step_kat(golden_dir, env, dtype):
+    d, _ = _load(golden_dir, "step_kat.npz")
+    s = _solver("MPPI", env, 1, 1, dtype=dtype, noise="philox")
+    cost, xn = s.model_step(d[env + "_x"], d[env + "_u"][:, 0], d[env + "_g"])
+    if dtype == "f64":
+        np.testing.assert_allclose(cost, d[env + "_cost"], rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(xn, d[env + "_xn"], rtol=1e-12, atol=1e-12)
+    else:
+        # float32 arithmetic on inputs up to |x| ~ 30: one-step error is a few float32 ulps of the largest term
+        np.testing.assert_allclose(cost, d[env + "_cost"], rtol=2e-5, atol=1e-4)
+        np.testing.assert_allclose(xn, d[env + "_xn"], rtol=1e-5, atol=2e-5)
+    s.close()
+
+
+# ------------------------------------------------------------------------------------------- MPPI, golden
+@pytest.mark.parametrize("dtype", ["f64", "f32"])
+def test_mppi_golden_cases(golden_dir, dtype):
+    d, meta = _load(golden_dir, "mppi_cases.npz")
+    rt = F64_COST_RTOL if dtype == "f64" else F32_COST_RTOL
+    for ci, mt in enumerate(meta):
+        p = "c%d_" % ci
+        K, H = mt["K"], mt["H"]
+        s = _solver("MPPI", mt["env"], K, H, dtype=dtype, lam=mt["lam"], sigma=mt["std"])
+        s.set_noise(d[p + "delta_u"].reshape(K, H))
+        nz = s.nz
+        g_z = np.repeat(d[p + "goal"][None, :], H, axis=0)
+        U = d[p + "U_in"].reshape(-1).copy()
+        for sv in range(mt["n_solves"]):
+            u0, Unew, xs, cost = s.mppi_solve(d[p + "x"], g_z, U)
+            S = s.mppi_costs()[0]
+            Sref = d[p + "costs"][sv]
+            if dtype == "f64":
+                np.testing.assert_allclose(S, Sref, rtol=rt, err_msg="case %d solve %d" % (ci, sv))
+            else:
+                # float32: rel 1e-5 for the bulk; chaotic divergence lets a small tail exceed it
+                rel = np.abs(S - Sref) / np.abs(Sref)
+                assert np.quantile(rel, 0.95) <= rt, "case %d: p95 rel err %.2e" % (ci, np.quantile(rel, 0.95))
+                assert rel.max() <= 2e-3, "case %d: max rel err %.2e" % (ci, rel.max())
+            if dtype == "f64":
+                tol = _plan_tol(Sref, mt["lam"], rt)
+                np.testing.assert_allclose(Unew[0], d[p + "U_out"][sv].reshape(-1), rtol=tol, atol=tol,
+                                           err_msg="plan case %d solve %d" % (ci, sv))
+                assert u0[0] == pytest.approx(float(d[p + "u0"][sv][0]), rel=tol, abs=tol)
+            # the reference keeps refining the same plan without clipping in bare _calc_action
+            U = d[p + "U_out"][sv].reshape(-1).copy()
+        s.close()
+
+
+def _rand_case(env, K, H, seed, sigma=1.0):
+    rng = np.random.RandomState(seed)
+    x = START[env] + rng.normal(0, 0.2, orc.STATE_SIZE[env])
+    U = rng.uniform(-0.5, 0.5, H)
+    eps = rng.normal(0, sigma, (K, H))
+    return x, U, eps
+
+
+@pytest.mark.parametrize("env", ENVS)
+@pytest.mark.parametrize("dtype", ["f64", "f32"])
+def test_mppi_vs_oracle_tensor_noise(env, dtype):
+    """K = 4096 (32 tiles + a ragged one at 4100), H = 50, identical noise tensor on both sides."""
+    for K, H, lam in ((4096, 50, 0.5), (4100, 37, 1.0)):
+        x, U, eps = _rand_case(env, K, H, seed=K + H)
+        m = orc.model(env)
+        S_ref, U_ref, u0_ref = orc.mppi_solve(m, x, U, eps, lam, 1.0, nthreads=0)
+        s = _solver("MPPI", env, K, H, dtype=dtype, lam=lam, sigma=1.0)
+        s.set_noise(eps)
+        u0, Unew, xs, cost = s.mppi_solve(x, None, U)
+        S = s.mppi_costs()[0]
+        rel = np.abs(S - S_ref) / np.abs(S_ref)
+        if dtype == "f64":
+            assert rel.max() <= F64_COST_RTOL, rel.max()
+            tol = _plan_tol(S_ref, lam, F64_COST_RTOL)
+            np.testing.assert_allclose(Unew[0], U_ref, rtol=tol, atol=tol)
+        else:
+            assert np.quantile(rel, 0.95) <= F32_COST_RTOL, np.quantile(rel, 0.95)
+            assert rel.max() <= 2e-3, rel.max()
+            # plan: conditioning bound eps32 * max|S| / lam
+            tol = 6e-8 * float(np.max(np.abs(S_ref))) / lam * 4 + 1e-5
+            np.testing.assert_allclose(Unew[0], U_ref, atol=tol, rtol=0)
+        # nominal rollout of the clipped plan == oracle simulate of the same plan
+        lo, hi = orc.BOUNDS[env]
+        xs_ref, c_ref = orc.simulate(m, x, np.clip(Unew[0], lo, hi))
+        rt = 1e-11 if dtype == "f64" else 2e-4
+        np.testing.assert_allclose(xs[0], xs_ref, rtol=rt, atol=rt)
+        assert cost[0] == pytest.approx(c_ref, rel=rt * 10)
+        s.close()
+
+
+@pytest.mark.parametrize("env", ENVS)
+@pytest.mark.parametrize("dtype", ["f64", "f32"])
+def test_mppi_vs_oracle_philox_noise(env, dtype):
+    """In-kernel Philox noise: materialise the same stream and hand it to the oracle."""
+    K, H, lam, sigma = 2048 + 77, 50, 0.5, 0.7
+    x, U, _ = _rand_case(env, K, H, seed=5)
+    s = _solver("MPPI", env, K, H, dtype=dtype, noise="philox", lam=lam, sigma=sigma, seed=1234)
+    z = s.philox_noise(0)
+    assert abs(z.mean()) < 0.02 and abs(z.std() - 1) < 0.02
+    if dtype == "f32":
+        eps = (np.float32(sigma) * z.astype(np.float32)).astype(np.float64)
+    else:
+        eps = sigma * z
+    S_ref, U_ref, _ = orc.mppi_solve(orc.model(env), x, U, eps, lam, sigma, nthreads=0)
+    u0, Unew, xs, cost = s.mppi_solve(x, None, U)
+    S = s.mppi_costs()[0]
+    rel = np.abs(S - S_ref) / np.abs(S_ref)
+    if dtype == "f64":
+        assert rel.max() <= F64_COST_RTOL, rel.max()
+        tol = _plan_tol(S_ref, lam, F64_COST_RTOL)
+        np.testing.assert_allclose(Unew[0], U_ref, rtol=tol, atol=tol)
+    else:
+        assert np.quantile(rel, 0.95) <= F32_COST_RTOL
+    # the tensor path fed the materialised noise gives the same plan as the in-kernel path
+    s2 = _solver("MPPI", env, K, H, dtype=dtype, lam=lam, sigma=sigma)
+    s2.set_noise(eps)
+    _, U2, _, _ = s2.mppi_solve(x, None, U)
+    np.testing.assert_allclose(U2[0], Unew[0], rtol=1e-9, atol=1e-12)
+    s.close()
+    s2.close()
+
+
+def test_mppi_batch_of_independent_solves():
+    """BASELINE config 5 in miniature: B independent CartPole solves in one call == B single solves."""
+    env, B, K, H, lam = "cartpole", 7, 300, 25, 0.5
+    rng = np.random.RandomState(3)
+    eps = rng.normal(0, 1, (K, H))
+    xs0 = START[env] + rng.normal(0, 0.2, (B, 4))
+    Us = rng.uniform(-0.3, 0.3, (B, H))
+    sb = _solver("MPPI", env, K, H, dtype="f64", lam=lam, batch=B)
+    sb.set_noise(eps)
+    u0b, Ub, xsb, cb = sb.mppi_solve(xs0, None, Us)
+    Sb = sb.mppi_costs()
+    m = orc.model(env)
+    for b in range(B):
+        S_ref, U_ref, _ = orc.mppi_solve(m, xs0[b], Us[b], eps, lam, 1.0)
+        np.testing.assert_allclose(Sb[b], S_ref, rtol=F64_COST_RTOL)
+        tol = _plan_tol(S_ref, lam, F64_COST_RTOL)
+        np.testing.assert_allclose(Ub[b], U_ref, rtol=tol, atol=tol)
+    sb.close()
+
+
+def test_mppi_full_size_properties():
+    """BASELINE full size (K = 2^20, H = 50, float32, Philox): size-independent properties.
+       (1) sample k's cost depends only on (seed, k): the first 4096 costs equal a K = 4096 solve's costs bit for bit;
+       (2) the plan equals the oracle's softmin update (float64, CPU) of the GPU's own costs and noise;
+       (3) two consecutive identical solves are bit-identical (no atomics / ordering nondeterminism)."""
+    env, K, H, lam = "pendulum", 1 << 20, 50, 0.5
+    x = START[env] + 0.1
+    U = np.zeros(H)
+    big = _solver("MPPI", env, K, H, dtype="f32", noise="philox", lam=lam, seed=7)
+    small = _solver("MPPI", env, 4096, H, dtype="f32", noise="philox", lam=lam, seed=7)
+    u0, Ub, _, _ = big.mppi_solve(x, None, U)
+    Sb = big.mppi_costs()[0]
+    small.mppi_solve(x, None, U)
+    Ss = small.mppi_costs()[0]
+    assert np.array_equal(Sb[:4096], Ss)
+    z = big.philox_noise(0)
+    eps = z.astype(np.float32).astype(np.float64)
+    U_ref, w = orc.mppi_update(Sb, eps, lam, U)
+    assert abs(w.sum() - 1) < 1e-9
+    np.testing.assert_allclose(Ub[0], U_ref, atol=2e-6, rtol=0)  # float32 weights/products inside a tile
+    u0b, Ub2, _, _ = big.mppi_solve(x, None, U)
+    assert np.array_equal(Ub, Ub2)
+    big.close()
+    small.close()
+
+
+# ------------------------------------------------------------------------------------------- CEM
+@pytest.mark.parametrize("dtype", ["f64", "f32"])
+def test_cem_golden_cases(golden_dir, dtype):
+    d, meta = _load(golden_dir, "cem_cases.npz")
+    for ci, mt in enumerate(meta):
+        p = "c%d_" % ci
+        K, H = mt["K"], mt["H"]
+        s = _solver("CEM", mt["env"], K, H, dtype=dtype, sigma=mt["std"], max_iter=mt["max_iter"],
+                    n_elite=mt["n_elite"], epsilon=mt["epsilon"], alpha=mt["alpha"])
+        s.cem_begin(d[p + "x"], None, d[p + "U_in"].reshape(-1))
+        iters = 0
+        for it in range(mt["max_iter"]):
+            iters += 1
+            if s.cem_iterate(d[p + "z"][it]):
+                break
+            if it + 1 == d[p + "z"].shape[0]:
+                break
+        u0, U, xs, cost = s.cem_end()
+        assert iters == mt["iters"], "case %d: %d iterations, reference %d" % (ci, iters, mt["iters"])
+        if dtype == "f64":
+            for it in range(iters):
+                R = s.cem_rewards(it)
+                np.testing.assert_allclose(R, d[p + "rewards"][it], rtol=F64_COST_RTOL, err_msg="case %d it %d" % (ci, it))
+                el = s.cem_elites(it)
+                assert np.array_equal(np.sort(el), d[p + "elites"][it]), "elite set, case %d it %d" % (ci, it)
+            np.testing.assert_allclose(U, d[p + "mu"][iters - 1][:, 0], rtol=1e-12, atol=1e-13)
+            np.testing.assert_allclose(s.cem_std(), d[p + "sd"][iters - 1][:, 0], rtol=1e-10, atol=1e-13)
+            assert u0[0] == pytest.approx(float(d[p + "u0"][0]), rel=1e-12, abs=1e-13)
+        else:
+            R = s.cem_rewards(0)
+            rel = np.abs(R - d[p + "rewards"][0]) / np.abs(d[p + "rewards"][0])
+            assert np.quantile(rel, 0.95) <= F32_COST_RTOL
+        s.close()
+
+
+@pytest.mark.parametrize("env", ENVS)
+def test_cem_vs_oracle_config2_shape(env):
+    """BASELINE config 2 shape: K = 4096, H = 50, n_elite = 409, 5 iterations, alpha 0.2 (host noise)."""
+    K, H, iters, n_elite = 4096, 50, 5, 409
+    rng = np.random.RandomState(11)
+    x = START[env] + rng.normal(0, 0.2, orc.STATE_SIZE[env])
+    z = rng.standard_normal((iters, K, H))
+    mu0 = np.zeros(H)
+    ref = orc.cem_solve(orc.model(env), x, mu0, z, n_elite, 1e-5, 0.2, 1.0, nthreads=0)
+    s = _solver("CEM", env, K, H, dtype="f64", sigma=1.0, max_iter=iters, n_elite=n_elite, epsilon=1e-5, alpha=0.2)
+    s.cem_begin(x, None, mu0)
+    for it in range(iters):
+        s.cem_iterate(z[it])
+    u0, U, xs, cost = s.cem_end()
+    for it in range(iters):
+        R = s.cem_rewards(it)
+        np.testing.assert_allclose(R, ref["rewards"][it], rtol=F64_COST_RTOL)
+        el = np.sort(s.cem_elites(it))
+        if not np.array_equal(el, ref["elites"][it]):
+            # allowed only where rewards at the elite boundary are tied to within the cost tolerance
+            diff = np.setxor1d(el, ref["elites"][it])
+            thr = np.sort(ref["rewards"][it])[::-1][n_elite - 1]
+            assert np.all(np.abs(ref["rewards"][it][diff] - thr) <= 1e-11 * abs(thr)), "elite sets differ off-tie"
+    np.testing.assert_allclose(U, ref["mu"], rtol=1e-11, atol=1e-13)
+    s.close()
+
+
+def test_cem_philox_on_device_iterations():
+    """All iterations enqueued at once with in-kernel noise and the device-side early break; checked against the
+    oracle fed the materialised normals."""
+    env, K, H, iters, n_elite = "cartpole", 1000, 30, 4, 100
+    x = START[env] + 0.05
+    s = _solver("CEM", env, K, H, dtype="f64", noise="philox", sigma=1.0, max_iter=iters, n_elite=n_elite,
+                epsilon=1e-5, alpha=0.2, seed=99)
+    u0, U, xs, cost, n = s.cem_solve(x, None, np.zeros(H))
+    assert n == iters
+    z = np.stack([s.philox_noise(it) for it in range(iters)])
+    ref = orc.cem_solve(orc.model(env), x, np.zeros(H), z, n_elite, 1e-5, 0.2, 1.0)
+    np.testing.assert_allclose(U, ref["mu"], rtol=1e-10, atol=1e-12)
+    for it in range(iters):
+        assert np.array_equal(np.sort(s.cem_elites(it)), ref["elites"][it])
+    # early break on the device: a huge epsilon stops after the first refit
+    s2 = _solver("CEM", env, K, H, dtype="f64", noise="philox", sigma=1.0, max_iter=iters, n_elite=n_elite,
+                 epsilon=10.0, alpha=0.2, seed=99)
+    *_, n2 = s2.cem_solve(x, None, np.zeros(H))
+    assert n2 == 1
+    s.close()
+    s2.close()
+
+
+# ------------------------------------------------------------------------------------------- agents API (drop-in)
+def test_agents_reproduce_reference_episodes(golden_dir):
+    """Closed loop through the drop-in classes: same np.random.seed => same delta_u / CEM draws => same actions,
+    plans, logged trajectories as the reference agents (fixture = reference run)."""
+    d, meta = _load(golden_dir, "episode_cases.npz")
+    for ci, mt in enumerate(meta):
+        p = "c%d_" % ci
+        np.random.seed(mt["seed"])
+        model = mpc_b200.ENV_NAMES[mt["env"]]()
+        cls = mpc_b200.MPPI if mt["agent"] == "MPPI" else mpc_b200.CEM
+        agent = cls(model, dict(mt["params"]))
+        if mt["agent"] == "MPPI":
+            assert np.array_equal(agent.delta_u, d[p + "delta_u"])
+        ns = model.state_size
+        goal = np.zeros(ns + 1)
+        agent.warm_start(d[p + "states"][0], mt["warm"], goal_state=goal)
+        lam = mt["params"].get("lam", 1.0)
+        tol = 1e-9 if mt["agent"] == "MPPI" and lam < 0.1 else 1e-10
+        np.testing.assert_allclose(agent.planned_us, d[p + "U_after_warm"], rtol=tol, atol=tol)
+        for i in range(mt["steps"]):
+            a = agent.predict_action(d[p + "states"][i], goal_state=goal)
+            np.testing.assert_allclose(a, d[p + "actions"][i], rtol=tol, atol=tol, err_msg="case %d step %d" % (ci, i))
+            np.testing.assert_allclose(agent.planned_us, d[p + "U"][i], rtol=tol, atol=tol)
+            np.testing.assert_allclose(agent.planned_xs, d[p + "planned_xs"][i], rtol=1e-8, atol=1e-8)
+            assert float(agent.planned_costs) == pytest.approx(d[p + "planned_costs"][i], rel=1e-8)
+        assert len(agent.planning_state_history) == mt["steps"]
+        agent.close()
+
+
+def test_simulate_and_model_predict_api():
+    m = mpc_b200.AcrobotModel()
+    x = np.array([0.3, -0.2, 0.5, -1.0])
+    xn = m.predict(x, np.array([0.7]))
+    c_ref, xn_ref = orc.step(orc.model("acrobot"), x, 0.7)
+    np.testing.assert_allclose(xn, xn_ref, rtol=1e-12, atol=1e-13)
+    assert -m.get_reward() == pytest.approx(c_ref, rel=1e-12)
+    m.close()
+
+
+def test_errors_are_loud():
+    with pytest.raises(capi.MpcError):
+        _solver("MPPI", "pendulum", 64, 5000)           # H beyond the supported horizon
+    s = _solver("MPPI", "pendulum", 64, 10, lam=0.5)
+    with pytest.raises(capi.MpcError):
+        s.mppi_solve(np.zeros(2))                        # noise tensor never set
+    s.close()
