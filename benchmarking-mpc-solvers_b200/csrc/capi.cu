@@ -152,6 +152,7 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         c[11] = 4 * l * total_m;
         c[12] = 3 * m_p_l;
         for (int i = 0; i < 5; ++i) c[13 + i] = -p[8 + i];
+        c[18] = p[7];
     } else if (env == MPC_ENV_ACROBOT) {  // acrobot_model.py:100-132
         const double m1 = p[1], m2 = p[2], l1 = p[3], lc1 = p[4], lc2 = p[5], I1 = p[6], I2 = p[7], g = p[8];
         c[0] = p[0];
@@ -164,6 +165,14 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         c[7] = p[9];
         c[8] = p[10];
         for (int i = 0; i < 5; ++i) c[9 + i] = p[11 + i];
+        c[14] = m1 * (lc1 * lc1);
+        c[15] = (l1 * l1) + (lc2 * lc2);
+        c[16] = 2 * l1 * lc2;
+        c[17] = m2;
+        c[18] = I1;
+        c[19] = I2;
+        c[20] = lc2 * lc2;
+        c[21] = l1 * lc2;
     } else {
         return -1;
     }

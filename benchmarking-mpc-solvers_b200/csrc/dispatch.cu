@@ -1,0 +1,196 @@
+// dispatch.cu — dtype-independent kernels (CEM radix select, reset, Philox materialise, L2 flush) and the
+// float32 / float64 switch over the two compilations of kernels.cu.
+#include "kernels.cuh"
+#include "philox.cuh"
+
+namespace mpc {
+
+enum { SEL_DONE = 0, SEL_ITERS = 1, SEL_NOTSMALL = 2, SEL_BLOCKS = 3, SEL_WORDS = 8 };
+
+__global__ void philox_materialize_kernel(double *__restrict__ dst, int K_local, int k_begin, int H, uint64_t seed,
+                                          uint32_t draw, uint32_t stream) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K_local) return;
+    for (int t4 = 0; t4 < H; t4 += 4) {
+        float z[4];
+        philox_normal4(seed, stream, draw, (uint32_t)(k_begin + k), (uint32_t)(t4 >> 2), z);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (t4 + i < H) dst[(size_t)k * H + t4 + i] = (double)z[i];
+    }
+}
+
+// exclusive block scan of one int per thread (blockDim = 1024); returns exclusive prefix, *total = block total
+__device__ __forceinline__ int block_scan_excl(int v, int *swarp, int *total) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    __syncthreads();
+    if (lane == 31) swarp[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        int s = (lane < nw) ? swarp[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, s, o);
+            if (lane >= o) s += n;
+        }
+        swarp[32 + lane] = s;  // inclusive warp totals
+    }
+    __syncthreads();
+    const int base = (w == 0) ? 0 : swarp[32 + w - 1];
+    *total = swarp[32 + nw - 1];
+    return base + inc - v;
+}
+
+// Radix select of the n_elite largest keys (np.argsort(-rewards)[:n_elite], cem.py:67) by one block:
+// 8 passes of 8 bits from the top find the n_elite-th largest key T; then an ordered compaction emits, ascending by
+// index, every k with key > T plus the lowest-index keys equal to T needed to reach n_elite.
+__global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const unsigned long long *__restrict__ keys,
+                                                         int *__restrict__ elite_hist, int *__restrict__ sel) {
+    if (sel[SEL_DONE]) return;
+    __shared__ int hist[256];
+    __shared__ int swarp[64];
+    __shared__ unsigned long long s_prefix;
+    __shared__ int s_want;
+    const int K = a.g.K_local, tid = threadIdx.x;
+    if (tid == 0) {
+        s_prefix = 0ull;
+        s_want = a.n_elite;
+    }
+    unsigned long long mask = 0ull;
+    for (int shift = 56; shift >= 0; shift -= 8) {
+        if (tid < 256) hist[tid] = 0;
+        __syncthreads();
+        const unsigned long long prefix = s_prefix;
+        const int want = s_want;
+        for (int k = tid; k < K; k += blockDim.x) {
+            const unsigned long long key = keys[k];
+            if ((key & mask) == prefix) atomicAdd(&hist[(int)((key >> shift) & 0xffull)], 1);
+        }
+        __syncthreads();
+        // descending inclusive scan over the 256 bins: thread i looks at bin 255 - i
+        const int v = (tid < 256) ? hist[255 - tid] : 0;
+        int total;
+        const int excl = block_scan_excl(v, swarp, &total);
+        if (tid < 256 && excl < want && excl + v >= want) {
+            s_prefix = prefix | ((unsigned long long)(255 - tid) << shift);
+            s_want = want - excl;
+        }
+        mask |= 0xffull << shift;
+        __syncthreads();
+    }
+    const unsigned long long T = s_prefix;
+    const int want_ties = s_want;  // how many keys == T belong to the elite set
+    int *elite = elite_hist + (size_t)a.iter * a.n_elite;
+    int tie_base = 0, sel_base = 0;
+    for (int k0 = 0; k0 < K; k0 += blockDim.x) {
+        const int k = k0 + tid;
+        const unsigned long long key = (k < K) ? keys[k] : 0ull;
+        const int is_tie = (k < K && key == T) ? 1 : 0;
+        const int is_gt = (k < K && key > T) ? 1 : 0;
+        int tot_tie, tot_sel;
+        const int tie_rank = tie_base + block_scan_excl(is_tie, swarp, &tot_tie);
+        const int chosen = is_gt | (is_tie && tie_rank < want_ties);
+        const int pos = sel_base + block_scan_excl(chosen, swarp, &tot_sel);
+        if (chosen && pos < a.n_elite) elite[pos] = k;
+        tie_base += tot_tie;
+        sel_base += tot_sel;
+    }
+}
+
+__global__ void cem_reset_kernel(const CemArgs a, double *__restrict__ sd, int *__restrict__ sel) {
+    for (int t = threadIdx.x; t < a.g.H; t += blockDim.x) sd[t] = a.sigma;  // std = self.std.copy()  cem.py:56
+    if (threadIdx.x < SEL_WORDS) sel[threadIdx.x] = 0;
+}
+
+__global__ void fill_kernel(float *p, size_t n, float v) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) p[i] = v;
+}
+
+
+#define DECL2(ret, name, ...) ret name##_f32(__VA_ARGS__); ret name##_f64(__VA_ARGS__);
+DECL2(size_t, mppi_rollout_smem, int)
+DECL2(cudaError_t, launch_mppi_rollout, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
+DECL2(int, mppi_rollout_occupancy, int, int, int)
+DECL2(cudaError_t, launch_mppi_finalize, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
+DECL2(cudaError_t, launch_transpose_noise, const double *, void *, int, int, int, cudaStream_t)
+DECL2(cudaError_t, launch_philox_fill, void *, int, int, int, int, double, uint64_t, uint32_t, cudaStream_t)
+DECL2(cudaError_t, launch_cem_rollout, int, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
+DECL2(cudaError_t, launch_cem_refit, int, const CemArgs &, const CemBuffers &, cudaStream_t)
+DECL2(cudaError_t, launch_cem_finish, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
+DECL2(cudaError_t, launch_simulate, const EnvParamsHost &, int, double, double, int, const double *, const double *,
+      const double *, double *, double *, cudaStream_t)
+DECL2(cudaError_t, launch_model_step, const EnvParamsHost &, int, const double *, const double *, const double *,
+      double *, double *, cudaStream_t)
+DECL2(cudaError_t, launch_fma_peak, float *, int, int, cudaStream_t)
+#undef DECL2
+#define BY_DTYPE(name, ...) ((dtype) == DT_F32 ? name##_f32(__VA_ARGS__) : name##_f64(__VA_ARGS__))
+
+size_t mppi_rollout_smem(int dtype, int H) { return BY_DTYPE(mppi_rollout_smem, H); }
+int mppi_rollout_occupancy(int dtype, int noise, int env, int H) { return BY_DTYPE(mppi_rollout_occupancy, noise, env, H); }
+cudaError_t launch_mppi_rollout(int dtype, int noise, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                cudaStream_t s) {
+    return BY_DTYPE(launch_mppi_rollout, noise, ep, a, b, s);
+}
+cudaError_t launch_mppi_finalize(int dtype, int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                 cudaStream_t s) {
+    return BY_DTYPE(launch_mppi_finalize, stage, ep, a, b, s);
+}
+cudaError_t launch_transpose_noise(int dtype, const double *src, void *dst, int K_local, int Kpad, int H,
+                                   cudaStream_t s) {
+    return BY_DTYPE(launch_transpose_noise, src, dst, K_local, Kpad, H, s);
+}
+cudaError_t launch_philox_fill(int dtype, void *dst, int K_local, int k_begin, int Kpad, int H, double scale,
+                               uint64_t seed, uint32_t draw, cudaStream_t s) {
+    return BY_DTYPE(launch_philox_fill, dst, K_local, k_begin, Kpad, H, scale, seed, draw, s);
+}
+cudaError_t launch_philox_materialize(double *dst, int K_local, int k_begin, int H, uint64_t seed, uint32_t draw,
+                                      cudaStream_t s) {
+    // the Philox stream id rides in bit 31 of draw: MPPI uses stream 0, CEM stream 1
+    const uint32_t stream = draw >> 31, d = draw & 0x7fffffffu;
+    philox_materialize_kernel<<<(K_local + 127) / 128, 128, 0, s>>>(dst, K_local, k_begin, H, seed, d, stream);
+    return cudaGetLastError();
+}
+cudaError_t launch_cem_rollout(int dtype, int noise, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
+                               cudaStream_t s) {
+    return BY_DTYPE(launch_cem_rollout, noise, ep, a, b, s);
+}
+cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    cem_select_kernel<<<1, 1024, 0, s>>>(a, b.keys, b.elite_idx, b.sel);
+    return cudaGetLastError();
+}
+cudaError_t launch_cem_refit(int dtype, int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    return BY_DTYPE(launch_cem_refit, noise, a, b, s);
+}
+cudaError_t launch_cem_finish(int dtype, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    return BY_DTYPE(launch_cem_finish, ep, a, b, s);
+}
+cudaError_t launch_cem_reset(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    cem_reset_kernel<<<1, 128, 0, s>>>(a, b.sd, b.sel);
+    return cudaGetLastError();
+}
+cudaError_t launch_simulate(int dtype, const EnvParamsHost &ep, int H, double lo, double hi, int do_clip,
+                            const double *x0, const double *us, const double *g_z, double *xs, double *cost,
+                            cudaStream_t s) {
+    return BY_DTYPE(launch_simulate, ep, H, lo, hi, do_clip, x0, us, g_z, xs, cost, s);
+}
+cudaError_t launch_model_step(int dtype, const EnvParamsHost &ep, int n, const double *x, const double *u,
+                              const double *g, double *cost, double *xn, cudaStream_t s) {
+    return BY_DTYPE(launch_model_step, ep, n, x, u, g, cost, xn, s);
+}
+cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaStream_t s) {
+    return BY_DTYPE(launch_fma_peak, sink, blocks, iters, s);
+}
+cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s) {
+    fill_kernel<<<148 * 8, 256, 0, s>>>(p, n, v);
+    return cudaGetLastError();
+}
+
+}  // namespace mpc

@@ -392,19 +392,6 @@ __global__ void philox_fill_kernel(R *__restrict__ dst, int K_local, int k_begin
     }
 }
 
-__global__ void philox_materialize_kernel(double *__restrict__ dst, int K_local, int k_begin, int H, uint64_t seed,
-                                          uint32_t draw, uint32_t stream) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= K_local) return;
-    for (int t4 = 0; t4 < H; t4 += 4) {
-        float z[4];
-        philox_normal4(seed, stream, draw, (uint32_t)(k_begin + k), (uint32_t)(t4 >> 2), z);
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-            if (t4 + i < H) dst[(size_t)k * H + t4 + i] = (double)z[i];
-    }
-}
-
 // ================================================================================================ CEM
 // sel[] layout
 enum { SEL_DONE = 0, SEL_ITERS = 1, SEL_NOTSMALL = 2, SEL_BLOCKS = 3, SEL_WORDS = 8 };
@@ -470,89 +457,6 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
     keys[k] = reward_key(reward);
 }
 
-// exclusive block scan of one int per thread (blockDim = 1024); returns exclusive prefix, *total = block total
-__device__ __forceinline__ int block_scan_excl(int v, int *swarp, int *total) {
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    int inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int n = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += n;
-    }
-    __syncthreads();
-    if (lane == 31) swarp[w] = inc;
-    __syncthreads();
-    if (w == 0) {
-        int s = (lane < nw) ? swarp[lane] : 0;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int n = __shfl_up_sync(0xffffffffu, s, o);
-            if (lane >= o) s += n;
-        }
-        swarp[32 + lane] = s;  // inclusive warp totals
-    }
-    __syncthreads();
-    const int base = (w == 0) ? 0 : swarp[32 + w - 1];
-    *total = swarp[32 + nw - 1];
-    return base + inc - v;
-}
-
-// Radix select of the n_elite largest keys (np.argsort(-rewards)[:n_elite], cem.py:67) by one block:
-// 8 passes of 8 bits from the top find the n_elite-th largest key T; then an ordered compaction emits, ascending by
-// index, every k with key > T plus the lowest-index keys equal to T needed to reach n_elite.
-__global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const unsigned long long *__restrict__ keys,
-                                                         int *__restrict__ elite_hist, int *__restrict__ sel) {
-    if (sel[SEL_DONE]) return;
-    __shared__ int hist[256];
-    __shared__ int swarp[64];
-    __shared__ unsigned long long s_prefix;
-    __shared__ int s_want;
-    const int K = a.g.K_local, tid = threadIdx.x;
-    if (tid == 0) {
-        s_prefix = 0ull;
-        s_want = a.n_elite;
-    }
-    unsigned long long mask = 0ull;
-    for (int shift = 56; shift >= 0; shift -= 8) {
-        if (tid < 256) hist[tid] = 0;
-        __syncthreads();
-        const unsigned long long prefix = s_prefix;
-        const int want = s_want;
-        for (int k = tid; k < K; k += blockDim.x) {
-            const unsigned long long key = keys[k];
-            if ((key & mask) == prefix) atomicAdd(&hist[(int)((key >> shift) & 0xffull)], 1);
-        }
-        __syncthreads();
-        // descending inclusive scan over the 256 bins: thread i looks at bin 255 - i
-        const int v = (tid < 256) ? hist[255 - tid] : 0;
-        int total;
-        const int excl = block_scan_excl(v, swarp, &total);
-        if (tid < 256 && excl < want && excl + v >= want) {
-            s_prefix = prefix | ((unsigned long long)(255 - tid) << shift);
-            s_want = want - excl;
-        }
-        mask |= 0xffull << shift;
-        __syncthreads();
-    }
-    const unsigned long long T = s_prefix;
-    const int want_ties = s_want;  // how many keys == T belong to the elite set
-    int *elite = elite_hist + (size_t)a.iter * a.n_elite;
-    int tie_base = 0, sel_base = 0;
-    for (int k0 = 0; k0 < K; k0 += blockDim.x) {
-        const int k = k0 + tid;
-        const unsigned long long key = (k < K) ? keys[k] : 0ull;
-        const int is_tie = (k < K && key == T) ? 1 : 0;
-        const int is_gt = (k < K && key > T) ? 1 : 0;
-        int tot_tie, tot_sel;
-        const int tie_rank = tie_base + block_scan_excl(is_tie, swarp, &tot_tie);
-        const int chosen = is_gt | (is_tie && tie_rank < want_ties);
-        const int pos = sel_base + block_scan_excl(chosen, swarp, &tot_sel);
-        if (chosen && pos < a.n_elite) elite[pos] = k;
-        tie_base += tot_tie;
-        sel_base += tot_sel;
-    }
-}
-
 // Elite refit (cem.py:69-76): one block per time step t.
 template <typename R, int NOISE>
 __global__ void __launch_bounds__(128) cem_refit_kernel(const CemArgs a, const R *__restrict__ zt,
@@ -601,11 +505,6 @@ __global__ void __launch_bounds__(128) cem_refit_kernel(const CemArgs a, const R
             if (notsmall == 0) sel[SEL_DONE] = 1;
         }
     }
-}
-
-__global__ void cem_reset_kernel(const CemArgs a, double *__restrict__ sd, int *__restrict__ sel) {
-    for (int t = threadIdx.x; t < a.g.H; t += blockDim.x) sd[t] = a.sigma;  // std = self.std.copy()  cem.py:56
-    if (threadIdx.x < SEL_WORDS) sel[threadIdx.x] = 0;
 }
 
 // u0 = planned_us[0] (cem.py:77), plus the clipped plan's nominal rollout (agent.py:64-69).
@@ -679,23 +578,36 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float *sink, int iters) {
     if (s == (R)123456789) sink[0] = (float)s;
 }
 
-__global__ void fill_kernel(float *p, size_t n, float v) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (; i < n; i += stride) p[i] = v;
-}
+// ================================================================================================ per-dtype launchers
+// This file is compiled twice (build.py): -DMPC_REAL=float -DMPC_SUFFIX=_f32 with FMA contraction on, and
+// -DMPC_REAL=double -DMPC_SUFFIX=_f64 with -fmad=false so the float64 path keeps the reference's rounding sequence.
+#ifndef MPC_REAL
+#error "compile with -DMPC_REAL=float|double -DMPC_SUFFIX=_f32|_f64"
+#endif
+#define MPC_CAT_(a, b) a##b
+#define MPC_CAT(a, b) MPC_CAT_(a, b)
+#define FN(name) MPC_CAT(name, MPC_SUFFIX)
+typedef MPC_REAL R_;
 
-// ================================================================================================ dispatch
-size_t mppi_rollout_smem(int dtype, int H) {
-    return dtype == DT_F32 ? RolloutSmem<float>::total(H) : RolloutSmem<double>::total(H);
-}
+#define MPC_DISPATCH_ENV(ENVID, CALL)                                \
+    do {                                                             \
+        switch (ENVID) {                                             \
+        case ENV_PENDULUM: { typedef Pendulum<R_> E_; CALL; } break; \
+        case ENV_CARTPOLE: { typedef CartPole<R_> E_; CALL; } break; \
+        default: { typedef Acrobot<R_> E_; CALL; } break;            \
+        }                                                            \
+    } while (0)
 
 template <class Env, typename R, int NOISE>
 static cudaError_t mppi_rollout_go(const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b, cudaStream_t s) {
     auto kern = mppi_rollout_kernel<Env, R, NOISE>;
     const size_t smem = RolloutSmem<R>::total(a.g.H);
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
+    static size_t smem_set = 0;  // per instantiation: raise the dynamic shared memory limit only when it grows
+    if (smem > smem_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        smem_set = smem;
+    }
     kern<<<a.g.grid, TILE, smem, s>>>(a, make_env<R>(ep), (const R *)b.noise, b.x0, b.g_z, b.U, b.S, b.part);
     return cudaGetLastError();
 }
@@ -710,155 +622,93 @@ static int mppi_rollout_occ(int H) {
     return occ;
 }
 
-#define MPC_DISPATCH_ENV_DTYPE(ENVID, DTYPE, CALL)                                   \
-    do {                                                                             \
-        if ((DTYPE) == DT_F32) {                                                     \
-            typedef float R_;                                                        \
-            switch (ENVID) {                                                         \
-            case ENV_PENDULUM: { typedef Pendulum<R_> E_; CALL; } break;             \
-            case ENV_CARTPOLE: { typedef CartPole<R_> E_; CALL; } break;             \
-            default: { typedef Acrobot<R_> E_; CALL; } break;                        \
-            }                                                                        \
-        } else {                                                                     \
-            typedef double R_;                                                       \
-            switch (ENVID) {                                                         \
-            case ENV_PENDULUM: { typedef Pendulum<R_> E_; CALL; } break;             \
-            case ENV_CARTPOLE: { typedef CartPole<R_> E_; CALL; } break;             \
-            default: { typedef Acrobot<R_> E_; CALL; } break;                        \
-            }                                                                        \
-        }                                                                            \
-    } while (0)
+size_t FN(mppi_rollout_smem)(int H) { return RolloutSmem<R_>::total(H); }
 
-cudaError_t launch_mppi_rollout(int dtype, int noise, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
-                                cudaStream_t s) {
+cudaError_t FN(launch_mppi_rollout)(int noise, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                    cudaStream_t s) {
     cudaError_t e = cudaSuccess;
     if (noise == NOISE_TENSOR)
-        MPC_DISPATCH_ENV_DTYPE(ep.env, dtype, (e = mppi_rollout_go<E_, R_, NOISE_TENSOR>(a, ep, b, s)));
+        MPC_DISPATCH_ENV(ep.env, (e = mppi_rollout_go<E_, R_, NOISE_TENSOR>(a, ep, b, s)));
     else
-        MPC_DISPATCH_ENV_DTYPE(ep.env, dtype, (e = mppi_rollout_go<E_, R_, NOISE_PHILOX>(a, ep, b, s)));
+        MPC_DISPATCH_ENV(ep.env, (e = mppi_rollout_go<E_, R_, NOISE_PHILOX>(a, ep, b, s)));
     return e;
 }
 
-int mppi_rollout_occupancy(int dtype, int noise, int env, int H) {
+int FN(mppi_rollout_occupancy)(int noise, int env, int H) {
     int occ = 0;
     if (noise == NOISE_TENSOR)
-        MPC_DISPATCH_ENV_DTYPE(env, dtype, (occ = mppi_rollout_occ<E_, R_, NOISE_TENSOR>(H)));
+        MPC_DISPATCH_ENV(env, (occ = mppi_rollout_occ<E_, R_, NOISE_TENSOR>(H)));
     else
-        MPC_DISPATCH_ENV_DTYPE(env, dtype, (occ = mppi_rollout_occ<E_, R_, NOISE_PHILOX>(H)));
+        MPC_DISPATCH_ENV(env, (occ = mppi_rollout_occ<E_, R_, NOISE_PHILOX>(H)));
     return occ;
 }
 
-cudaError_t launch_mppi_finalize(int dtype, int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
-                                 cudaStream_t s) {
+cudaError_t FN(launch_mppi_finalize)(int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                     cudaStream_t s) {
     const int count = (stage == 2) ? a.world : a.g.max_parts;
     const size_t smem = ((size_t)count + a.g.H) * sizeof(double);
-    MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
-                           (mppi_finalize_kernel<E_, R_><<<a.g.B, 256, smem, s>>>(a, make_env<R_>(ep), stage, b.part, b.rank_part,
-                                                                                   b.x0, b.g_z, b.U, b.out)));
+    MPC_DISPATCH_ENV(ep.env, (mppi_finalize_kernel<E_, R_><<<a.g.B, 256, smem, s>>>(
+                                 a, make_env<R_>(ep), stage, b.part, b.rank_part, b.x0, b.g_z, b.U, b.out)));
     return cudaGetLastError();
 }
 
-cudaError_t launch_transpose_noise(int dtype, const double *src, void *dst, int K_local, int Kpad, int H,
-                                   cudaStream_t s) {
+cudaError_t FN(launch_transpose_noise)(const double *src, void *dst, int K_local, int Kpad, int H, cudaStream_t s) {
     dim3 grid((Kpad + 31) / 32, (H + 31) / 32), block(32, 8);
-    if (dtype == DT_F32)
-        transpose_noise_kernel<float><<<grid, block, 0, s>>>(src, (float *)dst, K_local, Kpad, H);
-    else
-        transpose_noise_kernel<double><<<grid, block, 0, s>>>(src, (double *)dst, K_local, Kpad, H);
+    transpose_noise_kernel<R_><<<grid, block, 0, s>>>(src, (R_ *)dst, K_local, Kpad, H);
     return cudaGetLastError();
 }
 
-cudaError_t launch_philox_fill(int dtype, void *dst, int K_local, int k_begin, int Kpad, int H, double scale,
-                               uint64_t seed, uint32_t draw, cudaStream_t s) {
-    const int grid = (Kpad + 127) / 128;
-    if (dtype == DT_F32)
-        philox_fill_kernel<float><<<grid, 128, 0, s>>>((float *)dst, K_local, k_begin, Kpad, H, scale, seed, draw, 0u);
-    else
-        philox_fill_kernel<double><<<grid, 128, 0, s>>>((double *)dst, K_local, k_begin, Kpad, H, scale, seed, draw, 0u);
+cudaError_t FN(launch_philox_fill)(void *dst, int K_local, int k_begin, int Kpad, int H, double scale, uint64_t seed,
+                                   uint32_t draw, cudaStream_t s) {
+    philox_fill_kernel<R_><<<(Kpad + 127) / 128, 128, 0, s>>>((R_ *)dst, K_local, k_begin, Kpad, H, scale, seed, draw, 0u);
     return cudaGetLastError();
 }
 
-cudaError_t launch_philox_materialize(double *dst, int K_local, int k_begin, int H, uint64_t seed, uint32_t draw,
-                                      cudaStream_t s) {
-    // stream id is folded into bit 31 of draw by the caller-facing API: MPPI uses stream 0, CEM stream 1
-    const uint32_t stream = draw >> 31, d = draw & 0x7fffffffu;
-    philox_materialize_kernel<<<(K_local + 127) / 128, 128, 0, s>>>(dst, K_local, k_begin, H, seed, d, stream);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_cem_rollout(int dtype, int noise, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
-                               cudaStream_t s) {
+cudaError_t FN(launch_cem_rollout)(int noise, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
+                                   cudaStream_t s) {
     const size_t smem = 2 * (size_t)a.g.H * sizeof(double);
     const int grid = a.g.tiles_per_solve;
     if (noise == NOISE_TENSOR)
-        MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
-                               (cem_rollout_kernel<E_, R_, NOISE_TENSOR><<<grid, TILE, smem, s>>>(
-                                   a, make_env<R_>(ep), (const R_ *)b.z, b.x0, b.g_z, b.mu, b.sd, b.R, b.keys, b.sel)));
+        MPC_DISPATCH_ENV(ep.env, (cem_rollout_kernel<E_, R_, NOISE_TENSOR><<<grid, TILE, smem, s>>>(
+                                     a, make_env<R_>(ep), (const R_ *)b.z, b.x0, b.g_z, b.mu, b.sd, b.R, b.keys, b.sel)));
     else
-        MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
-                               (cem_rollout_kernel<E_, R_, NOISE_PHILOX><<<grid, TILE, smem, s>>>(
-                                   a, make_env<R_>(ep), (const R_ *)b.z, b.x0, b.g_z, b.mu, b.sd, b.R, b.keys, b.sel)));
+        MPC_DISPATCH_ENV(ep.env, (cem_rollout_kernel<E_, R_, NOISE_PHILOX><<<grid, TILE, smem, s>>>(
+                                     a, make_env<R_>(ep), (const R_ *)b.z, b.x0, b.g_z, b.mu, b.sd, b.R, b.keys, b.sel)));
     return cudaGetLastError();
 }
 
-cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
-    cem_select_kernel<<<1, 1024, 0, s>>>(a, b.keys, b.elite_idx, b.sel);
+cudaError_t FN(launch_cem_refit)(int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    if (noise == NOISE_TENSOR)
+        cem_refit_kernel<R_, NOISE_TENSOR><<<a.g.H, 128, 0, s>>>(a, (const R_ *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
+    else
+        cem_refit_kernel<R_, NOISE_PHILOX><<<a.g.H, 128, 0, s>>>(a, (const R_ *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
     return cudaGetLastError();
 }
 
-cudaError_t launch_cem_refit(int dtype, int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
-    if (dtype == DT_F32) {
-        if (noise == NOISE_TENSOR)
-            cem_refit_kernel<float, NOISE_TENSOR><<<a.g.H, 128, 0, s>>>(a, (const float *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
-        else
-            cem_refit_kernel<float, NOISE_PHILOX><<<a.g.H, 128, 0, s>>>(a, (const float *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
-    } else {
-        if (noise == NOISE_TENSOR)
-            cem_refit_kernel<double, NOISE_TENSOR><<<a.g.H, 128, 0, s>>>(a, (const double *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
-        else
-            cem_refit_kernel<double, NOISE_PHILOX><<<a.g.H, 128, 0, s>>>(a, (const double *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
-    }
-    return cudaGetLastError();
-}
-
-cudaError_t launch_cem_finish(int dtype, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+cudaError_t FN(launch_cem_finish)(const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
     const size_t smem = (size_t)a.g.H * sizeof(double);
-    MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
-                           (cem_finish_kernel<E_, R_><<<1, 128, smem, s>>>(a, make_env<R_>(ep), b.x0, b.g_z, b.mu, b.sel, b.out)));
+    MPC_DISPATCH_ENV(ep.env, (cem_finish_kernel<E_, R_><<<1, 128, smem, s>>>(a, make_env<R_>(ep), b.x0, b.g_z, b.mu,
+                                                                             b.sel, b.out)));
     return cudaGetLastError();
 }
 
-cudaError_t launch_cem_reset(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
-    cem_reset_kernel<<<1, 128, 0, s>>>(a, b.sd, b.sel);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_simulate(int dtype, const EnvParamsHost &ep, int H, double lo, double hi, int do_clip,
-                            const double *x0, const double *us, const double *g_z, double *xs, double *cost,
-                            cudaStream_t s) {
+cudaError_t FN(launch_simulate)(const EnvParamsHost &ep, int H, double lo, double hi, int do_clip, const double *x0,
+                                const double *us, const double *g_z, double *xs, double *cost, cudaStream_t s) {
     const size_t smem = (size_t)H * sizeof(double);
-    MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
-                           (simulate_kernel<E_, R_><<<1, 64, smem, s>>>(make_env<R_>(ep), H, lo, hi, do_clip, x0, us, g_z, xs, cost)));
+    MPC_DISPATCH_ENV(ep.env, (simulate_kernel<E_, R_><<<1, 64, smem, s>>>(make_env<R_>(ep), H, lo, hi, do_clip, x0, us,
+                                                                          g_z, xs, cost)));
     return cudaGetLastError();
 }
 
-cudaError_t launch_model_step(int dtype, const EnvParamsHost &ep, int n, const double *x, const double *u,
-                              const double *g, double *cost, double *xn, cudaStream_t s) {
-    MPC_DISPATCH_ENV_DTYPE(ep.env, dtype,
-                           (model_step_kernel<E_, R_><<<(n + 127) / 128, 128, 0, s>>>(make_env<R_>(ep), n, x, u, g, cost, xn)));
+cudaError_t FN(launch_model_step)(const EnvParamsHost &ep, int n, const double *x, const double *u, const double *g,
+                                  double *cost, double *xn, cudaStream_t s) {
+    MPC_DISPATCH_ENV(ep.env, (model_step_kernel<E_, R_><<<(n + 127) / 128, 128, 0, s>>>(make_env<R_>(ep), n, x, u, g,
+                                                                                        cost, xn)));
     return cudaGetLastError();
 }
 
-cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaStream_t s) {
-    if (dtype == DT_F32)
-        fma_peak_kernel<float><<<blocks, 256, 0, s>>>(sink, iters);
-    else
-        fma_peak_kernel<double><<<blocks, 256, 0, s>>>(sink, iters);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s) {
-    fill_kernel<<<148 * 8, 256, 0, s>>>(p, n, v);
+cudaError_t FN(launch_fma_peak)(float *sink, int blocks, int iters, cudaStream_t s) {
+    fma_peak_kernel<R_><<<blocks, 256, 0, s>>>(sink, iters);
     return cudaGetLastError();
 }
 

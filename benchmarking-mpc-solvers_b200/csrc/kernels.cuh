@@ -109,6 +109,5 @@ cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaS
 cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s);
 
 size_t mppi_rollout_smem(int dtype, int H);
-size_t cem_select_smem();
 
 }  // namespace mpc
