@@ -279,21 +279,28 @@ __global__ void __launch_bounds__(TILE) mppi_rollout_kernel(const MppiArgs a, co
 }
 
 // ================================================================================================ MPPI finalize
-// One block per solve.  src records [count][2+H] -> (beta, eta, E).  STAGE 0/2 apply, STAGE 1 writes a rank record.
+// One block of FIN_THREADS per solve.  src records [count][2+H] -> (beta, eta, E).  STAGE 0/2 apply, STAGE 1 writes a
+// rank record.  The merge is latency-bound (count x H doubles scattered over L2), so it is spread over all warps:
+// warp w owns records j = w, w + nw, ... (eight loads in flight per thread), lanes own time steps; the per-warp
+// sums meet in shared memory in a fixed order, so repeated solves are bit-identical.
+constexpr int FIN_THREADS = 1024;
 template <class Env, typename R>
-__global__ void __launch_bounds__(256) mppi_finalize_kernel(const MppiArgs a, const EnvConst<R> ec, const int stage,
-                                                            const double *__restrict__ part,
-                                                            double *__restrict__ rank_part,
-                                                            const double *__restrict__ x0g,
-                                                            const double *__restrict__ g_z, double *__restrict__ Ug,
-                                                            double *__restrict__ out) {
+__global__ void __launch_bounds__(FIN_THREADS) mppi_finalize_kernel(const MppiArgs a, const EnvConst<R> ec,
+                                                                    const int stage, const double *__restrict__ part,
+                                                                    double *__restrict__ rank_part,
+                                                                    const double *__restrict__ x0g,
+                                                                    const double *__restrict__ g_z,
+                                                                    double *__restrict__ Ug, double *__restrict__ out) {
     constexpr int NS = Env::NS, NZ = Env::NS + 1;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int H = a.g.H, b = blockIdx.x, tid = threadIdx.x;
+    const int lane = tid & 31, w = tid >> 5, nw = FIN_THREADS / 32;
     const int rec_len = PART_HDR + H;
-    __shared__ double red[8];
-    double *sscale = reinterpret_cast<double *>(smem_raw);  // [count]
-    double *sUc = sscale + ((stage == 2) ? a.world : a.g.max_parts);  // [H] clipped plan
+    __shared__ double red[FIN_THREADS / 32];
+    const int cap = (stage == 2) ? a.world : a.g.max_parts;
+    double *sscale = reinterpret_cast<double *>(smem_raw);  // [cap]
+    double *sUc = sscale + cap;                             // [H] clipped plan
+    double *sE = sUc + H;                                   // [nw][H] per-warp sums
 
     const double *src;
     int count;
@@ -310,29 +317,41 @@ __global__ void __launch_bounds__(256) mppi_finalize_kernel(const MppiArgs a, co
         stride = rec_len;
     }
     double m = INFINITY;
-    for (int j = tid; j < count; j += blockDim.x) m = fmin(m, src[j * stride]);
+    for (int j = tid; j < count; j += FIN_THREADS) m = fmin(m, src[j * stride]);
     const double beta = block_reduce<true>(m, red);
     double es = 0.0;
-    for (int j = tid; j < count; j += blockDim.x) {
+    for (int j = tid; j < count; j += FIN_THREADS) {
         const double bj = src[j * stride];
         const double sc = (bj == INFINITY) ? 0.0 : exp(a.neg_inv_lam * (bj - beta));
         sscale[j] = sc;
         es += sc * src[j * stride + 1];
     }
     const double eta = block_reduce<false>(es, red);  // barriers publish sscale
+    for (int t0 = 0; t0 < H; t0 += 32) {
+        const int t = t0 + lane;
+        double e[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) e[i] = 0.0;
+        if (t < H) {
+            const double *col = src + PART_HDR + t;
+            int j = w;
+            for (; j + 7 * nw < count; j += 8 * nw) {
+                double v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = col[(size_t)(j + i * nw) * stride];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) e[i] += sscale[j + i * nw] * v[i];
+            }
+            for (; j < count; j += nw) e[0] += sscale[j] * col[(size_t)j * stride];
+            sE[w * H + t] = ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
+        }
+    }
+    __syncthreads();
     double *U = Ug + (size_t)b * H;
     double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
-    for (int t = tid; t < H; t += blockDim.x) {
-        double e0 = 0.0, e1 = 0.0, e2 = 0.0, e3 = 0.0;
-        int j = 0;
-        for (; j + 3 < count; j += 4) {
-            e0 += sscale[j] * src[(size_t)j * stride + PART_HDR + t];
-            e1 += sscale[j + 1] * src[(size_t)(j + 1) * stride + PART_HDR + t];
-            e2 += sscale[j + 2] * src[(size_t)(j + 2) * stride + PART_HDR + t];
-            e3 += sscale[j + 3] * src[(size_t)(j + 3) * stride + PART_HDR + t];
-        }
-        for (; j < count; ++j) e0 += sscale[j] * src[(size_t)j * stride + PART_HDR + t];
-        const double E = (e0 + e1) + (e2 + e3);
+    for (int t = tid; t < H; t += FIN_THREADS) {
+        double E = 0.0;
+        for (int i = 0; i < nw; ++i) E += sE[i * H + t];
         if (stage == 1) {
             rank_part[((size_t)a.rank * a.g.B + b) * rec_len + PART_HDR + t] = E;
         } else {
@@ -643,13 +662,27 @@ int FN(mppi_rollout_occupancy)(int noise, int env, int H) {
     return occ;
 }
 
+template <class Env, typename R>
+static cudaError_t mppi_finalize_go(int stage, const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b,
+                                    cudaStream_t s) {
+    auto kern = mppi_finalize_kernel<Env, R>;
+    const int cap = (stage == 2) ? a.world : a.g.max_parts;
+    const size_t smem = ((size_t)cap + a.g.H + (size_t)(FIN_THREADS / 32) * a.g.H) * sizeof(double);
+    static size_t smem_set = 48 * 1024;
+    if (smem > smem_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        smem_set = smem;
+    }
+    kern<<<a.g.B, FIN_THREADS, smem, s>>>(a, make_env<R>(ep), stage, b.part, b.rank_part, b.x0, b.g_z, b.U, b.out);
+    return cudaGetLastError();
+}
+
 cudaError_t FN(launch_mppi_finalize)(int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
                                      cudaStream_t s) {
-    const int count = (stage == 2) ? a.world : a.g.max_parts;
-    const size_t smem = ((size_t)count + a.g.H) * sizeof(double);
-    MPC_DISPATCH_ENV(ep.env, (mppi_finalize_kernel<E_, R_><<<a.g.B, 256, smem, s>>>(
-                                 a, make_env<R_>(ep), stage, b.part, b.rank_part, b.x0, b.g_z, b.U, b.out)));
-    return cudaGetLastError();
+    cudaError_t e = cudaSuccess;
+    MPC_DISPATCH_ENV(ep.env, (e = mppi_finalize_go<E_, R_>(stage, a, ep, b, s)));
+    return e;
 }
 
 cudaError_t FN(launch_transpose_noise)(const double *src, void *dst, int K_local, int Kpad, int H, cudaStream_t s) {
