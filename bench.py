@@ -334,7 +334,8 @@ def run_ours(args, dist):
     mpc_b200.build_library()
     agent, env, K, H, prm = WORKLOADS[args.workload]
     peaks, peaks_src = measured_peaks()
-    s = make_solver(capi, None, agent, env, K, H, prm, dist, dtype=args.dtype, noise=args.noise)
+    s = make_solver(capi, None, agent, env, K, H, prm, dist, dtype=args.dtype, noise=args.noise, lanes=args.lanes,
+                    fast_math=args.fast_math)
     s.set_profiling(True)
     esz = 4 if args.dtype == "f32" else 8
     shard_bytes = s.K_local * H * esz
@@ -376,7 +377,8 @@ def run_ours(args, dist):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": args.workload, "agent": agent, "env": env, "K": K, "H": H, **prm,
-                   "noise": args.noise, "K_per_gpu": s.K_local,
+                   "noise": args.noise, "lanes_per_thread": args.lanes or (2 if args.dtype == "f32" else 1),
+                   "fast_math": bool(args.fast_math), "K_per_gpu": s.K_local,
                    "cache": ("L2 flushed (256 MiB write) between timed steps" if flush else
                              "noise shard %.0f MB per GPU > L2 (126 MB): no flush" % (shard_bytes / 1e6)),
                    "parallelism": "K-shard x%d, one all-gather of (beta, eta, E[H]) per solve" % dist.world},
@@ -426,6 +428,8 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
     ap.add_argument("--noise", default="tensor", choices=["tensor", "philox"])
+    ap.add_argument("--lanes", type=int, default=0, choices=[0, 1, 2], help="f32 samples per thread (0 = default 2)")
+    ap.add_argument("--fast-math", type=int, default=0, choices=[0, 1], help="f32: MUFU trig instead of polynomial")
     ap.add_argument("--no-extra", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

@@ -6,7 +6,8 @@ sampling inner loop executed by libmpcb200.so on a B200.
 
 `model` may be one of this package's models or an instance of the reference's own model classes.
 Extra, optional params keys (defaults reproduce the reference): "dtype" ("f64" | "f32"), "noise" ("tensor": host
-numpy noise exactly as the reference draws it | "philox": generated in-kernel), "seed", "resample", "device",
+numpy noise exactly as the reference draws it | "philox": generated in-kernel), "fast_math" (f32: MUFU trig),
+"lanes" (f32 MPPI: samples per thread, 1 | 2), "seed", "resample", "device",
 "rank"/"world"/"comm_id" (K-sharding across GPUs, one process per GPU).
 
 What stays on the host is only what the reference's Agent base class does around `_calc_action`
@@ -101,7 +102,8 @@ class _GpuAgent(Agent):
             dtype=params.get("dtype", "f64"), noise=params.get("noise", "tensor"),
             bounds=(float(np.ravel(self.bounds_low)[0]), float(np.ravel(self.bounds_high)[0])),
             device=params.get("device", 0), rank=params.get("rank", 0), world=params.get("world", 1),
-            seed=params.get("seed", 0), resample=params.get("resample", False), **kw)
+            seed=params.get("seed", 0), resample=params.get("resample", False),
+            fast_math=params.get("fast_math", False), lanes=params.get("lanes", 0), **kw)
         if params.get("world", 1) > 1:
             self._solver.comm_init(params["comm_id"])
         self._traj = None  # (x, clipped plan, g_z) -> (xs, cost) produced by the last solve

@@ -37,7 +37,7 @@ class MpcConfig(C.Structure):
         ("struct_size", C.c_uint32), ("agent", C.c_int32), ("env", C.c_int32), ("dtype", C.c_int32),
         ("noise", C.c_int32), ("device", C.c_int32), ("K", C.c_int32), ("H", C.c_int32), ("batch", C.c_int32),
         ("rank", C.c_int32), ("world", C.c_int32), ("max_iter", C.c_int32), ("n_elite", C.c_int32),
-        ("resample", C.c_int32),
+        ("resample", C.c_int32), ("fast_math", C.c_int32), ("lanes", C.c_int32),
         ("lam", C.c_double), ("sigma", C.c_double), ("epsilon", C.c_double), ("alpha", C.c_double),
         ("bounds_low", C.c_double), ("bounds_high", C.c_double), ("seed", C.c_uint64),
         ("env_params", C.c_double * MAX_ENV_PARAMS),
@@ -124,7 +124,7 @@ class Solver:
 
     def __init__(self, agent, env, env_params, K, H, *, dtype="f64", noise="tensor", lam=1.0, sigma=1.0,
                  max_iter=1, n_elite=1, epsilon=0.0, alpha=0.0, bounds=(-1.0, 1.0), batch=1, device=0, rank=0,
-                 world=1, seed=0, resample=False):
+                 world=1, seed=0, resample=False, fast_math=False, lanes=0):
         self._h = None
         L = load()
         cfg = MpcConfig()
@@ -136,6 +136,7 @@ class Solver:
         cfg.device, cfg.K, cfg.H, cfg.batch = int(device), int(K), int(H), int(batch)
         cfg.rank, cfg.world = int(rank), int(world)
         cfg.max_iter, cfg.n_elite, cfg.resample = int(max_iter), int(n_elite), int(bool(resample))
+        cfg.fast_math, cfg.lanes = int(bool(fast_math)), int(lanes)
         cfg.lam, cfg.sigma, cfg.epsilon, cfg.alpha = float(lam), float(sigma), float(epsilon), float(alpha)
         cfg.bounds_low, cfg.bounds_high = float(bounds[0]), float(bounds[1])
         cfg.seed = int(seed) & 0xFFFFFFFFFFFFFFFF

@@ -126,7 +126,7 @@ static int fail(mpc_handle *h, int code, const char *fmt, ...) {
 static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
     memset(out, 0, sizeof *out);
     out->env = env;
-    double *c = out->c;
+    double *c = out->c, *f = out->f;
     if (env == MPC_ENV_PENDULUM) {  // pendulum_model.py:14-21,28-38
         const double g = p[0], m = p[1], l = p[2];
         c[0] = -3 * g / (2 * l);
@@ -135,6 +135,15 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         c[3] = p[4];
         c[4] = p[5];
         c[5] = p[6]; c[6] = p[7]; c[7] = p[8];
+        f[0] = -c[0] * p[3];
+        f[1] = c[1] * p[3];
+        f[2] = p[3];
+        f[3] = p[4];
+        f[4] = p[5];
+        for (int i = 0; i < 3; ++i) {
+            if (p[6 + i] < 0) return -2;
+            f[5 + i] = sqrt(p[6 + i]);
+        }
     } else if (env == MPC_ENV_CARTPOLE) {  // cartpole_swingup_model.py:25-33,63-85
         const double g = p[0], m_c = p[1], m_p = p[2], l = p[3], b = p[6];
         const double total_m = m_p + m_c, m_p_l = m_p * l;
@@ -153,6 +162,19 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         c[12] = 3 * m_p_l;
         for (int i = 0; i < 5; ++i) c[13 + i] = -p[8 + i];
         c[18] = p[7];
+        f[0] = 1.0 / p[7];
+        f[1] = 4 * p[4];
+        f[2] = p[5];
+        f[3] = 6 * p[4] / l;
+        f[4] = c[4]; f[5] = c[5]; f[6] = c[6]; f[7] = c[7]; f[8] = c[8];
+        f[9] = c[9] / l;
+        f[10] = c[10] / l;
+        f[11] = 6 * b / l;
+        f[12] = 1.0;
+        for (int i = 0; i < 5; ++i) {
+            if (-p[8 + i] < 0) return -2;
+            f[13 + i] = sqrt(-p[8 + i]);
+        }
     } else if (env == MPC_ENV_ACROBOT) {  // acrobot_model.py:100-132
         const double m1 = p[1], m2 = p[2], l1 = p[3], lc1 = p[4], lc2 = p[5], I1 = p[6], I2 = p[7], g = p[8];
         c[0] = p[0];
@@ -173,6 +195,13 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         c[19] = I2;
         c[20] = lc2 * lc2;
         c[21] = l1 * lc2;
+        for (int i = 0; i < 9; ++i) f[i] = c[i];
+        f[9] = p[0] / 2;
+        f[10] = p[0] / 6;
+        if (p[11] < 0 || p[15] < 0) return -2;
+        f[11] = sqrt(p[11]);
+        f[12] = sqrt(p[15]);
+        f[13] = p[12]; f[14] = p[13]; f[15] = p[14];
     } else {
         return -1;
     }
@@ -180,7 +209,6 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
 }
 
 namespace mpc {
-int mppi_rollout_occupancy(int dtype, int noise, int env, int H);  // kernels.cu
 }
 
 static size_t off_x(const mpc_handle *) { return 0; }
@@ -297,7 +325,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     if (cfg->noise != MPC_NOISE_TENSOR && cfg->noise != MPC_NOISE_PHILOX)
         return fail(nullptr, MPC_EINVAL, "unknown noise mode %d", cfg->noise);
     if (cfg->K < 1 || cfg->H < 1 || cfg->batch < 1) return fail(nullptr, MPC_EINVAL, "K, H, batch must be >= 1");
-    if (cfg->H > TILE * MAX_EH) return fail(nullptr, MPC_EINVAL, "H = %d exceeds the supported %d", cfg->H, TILE * MAX_EH);
+    if (cfg->lanes < 0 || cfg->lanes > 2) return fail(nullptr, MPC_EINVAL, "lanes must be 0 (default), 1 or 2");
     if (cfg->world < 1 || cfg->rank < 0 || cfg->rank >= cfg->world)
         return fail(nullptr, MPC_EINVAL, "bad rank/world %d/%d", cfg->rank, cfg->world);
     if (cfg->K < cfg->world) return fail(nullptr, MPC_EINVAL, "K = %d smaller than world = %d", cfg->K, cfg->world);
@@ -320,9 +348,11 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     mpc_handle *h = new (std::nothrow) mpc_handle();
     if (!h) return fail(nullptr, MPC_ENOMEM, "out of host memory");
     h->cfg = *cfg;
-    if (fold_env_params(cfg->env, cfg->env_params, &h->ep)) {
+    const int fold_rc = fold_env_params(cfg->env, cfg->env_params, &h->ep);
+    if (fold_rc == -1 || (fold_rc == -2 && cfg->dtype == MPC_F32)) {
         delete h;
-        return fail(nullptr, MPC_EINVAL, "bad env");
+        return fail(nullptr, MPC_EINVAL, fold_rc == -1 ? "bad env" : "the float32 flavour folds sqrt(W_i) into the cost "
+                    "residuals and needs non-negative cost weights; use MPC_F64");
     }
     h->ns = (cfg->env == MPC_ENV_PENDULUM) ? 2 : 4;
     h->nz = h->ns + 1;
@@ -357,7 +387,14 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     g.ns = h->ns;
     g.tiles_per_solve = g.Kpad / TILE;
     g.total_tiles = g.B * g.tiles_per_solve;
-    g.smem_rollout = mppi_rollout_smem(cfg->dtype, cfg->H);
+    // rollout flavour: float32 rolls out two samples per thread (packed f32x2) unless asked otherwise
+    const int lanes = (cfg->dtype == MPC_F32 && cfg->agent == MPC_AGENT_MPPI) ? (cfg->lanes ? cfg->lanes : 2) : 1;
+    g.variant = (cfg->dtype == MPC_F32 && cfg->fast_math ? 1 : 0) | (lanes == 2 ? 2 : 0);
+    // weighted-sum pass: H x parts work items over the block's threads, about two rounds
+    const int nt = TILE / lanes;
+    g.parts = 1;
+    while (g.parts < 8 && g.H * g.parts < 2 * nt) g.parts *= 2;
+    g.smem_rollout = mppi_rollout_smem(cfg->dtype, cfg->H, g.parts);
     int max_smem = 0;
     CUC(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
     if (cfg->agent == MPC_AGENT_MPPI && g.smem_rollout > (size_t)max_smem) {
@@ -368,7 +405,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     }
     int occ = 1;
     if (cfg->agent == MPC_AGENT_MPPI) {
-        occ = mppi_rollout_occupancy(cfg->dtype, cfg->noise, cfg->env, cfg->H);
+        occ = mppi_rollout_occupancy(cfg->dtype, cfg->noise, g.variant, cfg->env, cfg->H, g.parts);
         if (occ < 1) occ = 1;
     }
     const int slots = h->num_sms * occ;
@@ -540,7 +577,7 @@ static int mppi_enqueue(mpc_handle *h, int want_traj) {
     const MppiArgs a = mppi_args(h, want_traj);
     const MppiBuffers b = mppi_bufs(h);
     if (h->profiling) CU(h, cudaEventRecord(h->evr0, h->stream));
-    CU(h, launch_mppi_rollout(h->cfg.dtype, h->cfg.noise, h->ep, a, b, h->stream));
+    CU(h, launch_mppi_rollout(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
     if (h->profiling) CU(h, cudaEventRecord(h->evr1, h->stream));
     h->launches++;
     if (h->cfg.world == 1) {
@@ -580,7 +617,7 @@ int mpc_mppi_rollout_partial(mpc_handle *h, const double *x, const double *g_z, 
     if (rc) return rc;
     const MppiArgs a = mppi_args(h, 0);
     const MppiBuffers b = mppi_bufs(h);
-    CU(h, launch_mppi_rollout(h->cfg.dtype, h->cfg.noise, h->ep, a, b, h->stream));
+    CU(h, launch_mppi_rollout(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
     CU(h, launch_mppi_finalize(h->cfg.dtype, 1, h->ep, a, b, h->stream));
     h->launches += 2;
     const size_t cnt = (size_t)h->g.B * (PART_HDR + h->g.H);
@@ -619,7 +656,7 @@ int mpc_mppi_get_costs(mpc_handle *h, double *S_out) {
 static int cem_enqueue_iter(mpc_handle *h, int iter) {
     const CemArgs a = cem_args(h, iter, 0);
     const CemBuffers b = cem_bufs(h);
-    CU(h, launch_cem_rollout(h->cfg.dtype, h->cfg.noise, h->ep, a, b, h->stream));
+    CU(h, launch_cem_rollout(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
     CU(h, launch_cem_select(a, b, h->stream));
     CU(h, launch_cem_refit(h->cfg.dtype, h->cfg.noise, a, b, h->stream));
     h->launches += 3;
@@ -891,7 +928,7 @@ int64_t mpc_launch_count(const mpc_handle *h) { return h ? h->launches : 0; }
 int mpc_get_geometry(const mpc_handle *h, int32_t out[6]) {
     if (!h || !out) return MPC_EINVAL;
     out[0] = h->g.grid;
-    out[1] = TILE;
+    out[1] = TILE / ((h->g.variant & 2) ? 2 : 1);
     out[2] = (int32_t)h->g.smem_rollout;
     out[3] = h->g.total_tiles;
     out[4] = h->g.K_local;

@@ -116,13 +116,13 @@ __global__ void fill_kernel(float *p, size_t n, float v) {
 
 
 #define DECL2(ret, name, ...) ret name##_f32(__VA_ARGS__); ret name##_f64(__VA_ARGS__);
-DECL2(size_t, mppi_rollout_smem, int)
-DECL2(cudaError_t, launch_mppi_rollout, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
-DECL2(int, mppi_rollout_occupancy, int, int, int)
+DECL2(size_t, mppi_rollout_smem, int, int)
+DECL2(cudaError_t, launch_mppi_rollout, int, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
+DECL2(int, mppi_rollout_occupancy, int, int, int, int, int)
 DECL2(cudaError_t, launch_mppi_finalize, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
 DECL2(cudaError_t, launch_transpose_noise, const double *, void *, int, int, int, cudaStream_t)
 DECL2(cudaError_t, launch_philox_fill, void *, int, int, int, int, double, uint64_t, uint32_t, cudaStream_t)
-DECL2(cudaError_t, launch_cem_rollout, int, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
+DECL2(cudaError_t, launch_cem_rollout, int, int, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
 DECL2(cudaError_t, launch_cem_refit, int, const CemArgs &, const CemBuffers &, cudaStream_t)
 DECL2(cudaError_t, launch_cem_finish, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
 DECL2(cudaError_t, launch_simulate, const EnvParamsHost &, int, double, double, int, const double *, const double *,
@@ -133,11 +133,13 @@ DECL2(cudaError_t, launch_fma_peak, float *, int, int, cudaStream_t)
 #undef DECL2
 #define BY_DTYPE(name, ...) ((dtype) == DT_F32 ? name##_f32(__VA_ARGS__) : name##_f64(__VA_ARGS__))
 
-size_t mppi_rollout_smem(int dtype, int H) { return BY_DTYPE(mppi_rollout_smem, H); }
-int mppi_rollout_occupancy(int dtype, int noise, int env, int H) { return BY_DTYPE(mppi_rollout_occupancy, noise, env, H); }
-cudaError_t launch_mppi_rollout(int dtype, int noise, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
-                                cudaStream_t s) {
-    return BY_DTYPE(launch_mppi_rollout, noise, ep, a, b, s);
+size_t mppi_rollout_smem(int dtype, int H, int parts) { return BY_DTYPE(mppi_rollout_smem, H, parts); }
+int mppi_rollout_occupancy(int dtype, int noise, int variant, int env, int H, int parts) {
+    return BY_DTYPE(mppi_rollout_occupancy, noise, variant, env, H, parts);
+}
+cudaError_t launch_mppi_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
+                                const MppiBuffers &b, cudaStream_t s) {
+    return BY_DTYPE(launch_mppi_rollout, noise, variant, ep, a, b, s);
 }
 cudaError_t launch_mppi_finalize(int dtype, int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
                                  cudaStream_t s) {
@@ -158,9 +160,9 @@ cudaError_t launch_philox_materialize(double *dst, int K_local, int k_begin, int
     philox_materialize_kernel<<<(K_local + 127) / 128, 128, 0, s>>>(dst, K_local, k_begin, H, seed, d, stream);
     return cudaGetLastError();
 }
-cudaError_t launch_cem_rollout(int dtype, int noise, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
-                               cudaStream_t s) {
-    return BY_DTYPE(launch_cem_rollout, noise, ep, a, b, s);
+cudaError_t launch_cem_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const CemArgs &a,
+                               const CemBuffers &b, cudaStream_t s) {
+    return BY_DTYPE(launch_cem_rollout, noise, variant, ep, a, b, s);
 }
 cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
     cem_select_kernel<<<1, 1024, 0, s>>>(a, b.keys, b.elite_idx, b.sel);

@@ -73,20 +73,27 @@ __device__ __forceinline__ double block_reduce(double v, double *red) {
 }
 
 // Folded constants narrowed once on the host and passed by value: they live in the kernel-parameter constant bank,
-// so FFMA/DFMA read them as c[bank][offset] operands instead of holding registers.
-template <typename R>
-static EnvConst<R> make_env(const EnvParamsHost &ep) {
-    EnvConst<R> ec;
-    for (int i = 0; i < 24; ++i) ec.c[i] = (R)ep.c[i];
+// so FFMA/FFMA2/DFMA read them as constant (uniform-register) operands instead of holding registers.
+// double <- parity layout c, float / f2 <- throughput layout f (fold_env_params, capi.cu).
+template <typename V>
+static EnvConst<V> make_env(const EnvParamsHost &ep) {
+    EnvConst<V> ec;
+    for (int i = 0; i < 24; ++i) {
+        if constexpr (std::is_same<V, double>::value)
+            ec.c[i] = ep.c[i];
+        else
+            ec.c[i] = V((float)ep.f[i]);
+    }
     return ec;
 }
 
 // Nominal rollout of one plan by a single thread: Agent.simulate_trajectory (agent.py:97-108).
 // us: plan (already clipped by the caller if required), g_z rows per step, xs [H+1][ns] (nullable), returns cost.
-template <class Env, typename R>
-__device__ double nominal_rollout(const EnvConst<R> &ec, int H, const double *x0, const double *us, const double *g_z,
-                                  double *xs) {
+template <class Env>
+__device__ double nominal_rollout(const EnvConst<typename Env::Vec> &ec, int H, const double *x0, const double *us,
+                                  const double *g_z, double *xs) {
     constexpr int NS = Env::NS, NZ = Env::NS + 1;
+    typedef typename Env::S R;
     R x[NS];
 #pragma unroll
     for (int i = 0; i < NS; ++i) {
@@ -95,10 +102,9 @@ __device__ double nominal_rollout(const EnvConst<R> &ec, int H, const double *x0
     }
     double reward = 0.0;
     for (int t = 0; t < H; ++t) {
-        R g[NZ];
-#pragma unroll
-        for (int i = 0; i < NZ; ++i) g[i] = (R)g_z[t * NZ + i];
-        const R c = Env::step(ec, x, (R)us[t], g);
+        R gs[Env::NG];
+        Env::prep_goal(ec, g_z + t * NZ, gs);
+        const R c = Env::step(ec, x, (R)us[t], gs);
         reward += -(double)c;
         if (xs) {
 #pragma unroll
@@ -109,42 +115,72 @@ __device__ double nominal_rollout(const EnvConst<R> &ec, int H, const double *x0
 }
 
 // ================================================================================================ MPPI rollout
-// Shared memory: [H][TILE] noise tile (R) | sU[H] (R) | sw[TILE] (R) | red[8] (double) | mbarrier
+// One block = NT = TILE / PACK threads, each rolling out PACK samples of a 128-sample tile (PACK = 2: the two samples
+// travel in one f2 and every FMA-pipe instruction is an FFMA2/FADD2/FMUL2).
+// Shared memory: noise tile [H][TS] (row stride TS = TILE + pad keeps rows 16-byte aligned for the bulk copies and
+// makes the LDS.128 row reads of the weighted-sum pass conflict-free) | sU[H] | sw[TILE] | sE[H*parts] (float64
+// running sums) | red[8] | mbarrier
 template <typename R>
 struct RolloutSmem {
-    static __host__ __device__ size_t tile_bytes(int H) { return (size_t)H * TILE * sizeof(R); }
-    static __host__ __device__ size_t total(int H) {
-        size_t b = tile_bytes(H);
-        b += ((size_t)H * sizeof(R) + 15) / 16 * 16;
-        b += TILE * sizeof(R);
-        b += 8 * sizeof(double);
-        b += 16;
-        return b;
-    }
+    static constexpr int PAD = 16 / sizeof(R);
+    static constexpr int TS = TILE + PAD;
+    static __host__ __device__ size_t align16(size_t b) { return (b + 15) / 16 * 16; }
+    static __host__ __device__ size_t off_sU(int H) { return (size_t)H * TS * sizeof(R); }
+    static __host__ __device__ size_t off_sw(int H) { return off_sU(H) + align16((size_t)H * sizeof(R)); }
+    static __host__ __device__ size_t off_sE(int H) { return off_sw(H) + TILE * sizeof(R); }
+    static __host__ __device__ size_t off_red(int H, int parts) { return off_sE(H) + (size_t)H * parts * sizeof(double); }
+    static __host__ __device__ size_t off_bar(int H, int parts) { return off_red(H, parts) + 8 * sizeof(double); }
+    static __host__ __device__ size_t total(int H, int parts) { return off_bar(H, parts) + 16; }
 };
 
-template <class Env, typename R, int NOISE>
-__global__ void __launch_bounds__(TILE) mppi_rollout_kernel(const MppiArgs a, const EnvConst<R> ec,
-                                                           const R *__restrict__ noise,
-                                                           const double *__restrict__ x0g,
-                                                           const double *__restrict__ g_z,
-                                                           const double *__restrict__ Ug, double *__restrict__ S_out,
-                                                           double *__restrict__ part) {
-    constexpr int NS = Env::NS, NZ = Env::NS + 1;
+// sum_k w[k] * row[k] over n (multiple of 4) consecutive k: 128-bit shared loads, packed FMAs in float32
+__device__ __forceinline__ double dot_row(const float *row, const float *w, int n) {
+    f2 a0(0.f), a1(0.f);
+#pragma unroll 4
+    for (int i = 0; i < n; i += 4) {
+        const float4 e = *reinterpret_cast<const float4 *>(row + i);
+        const float4 q = *reinterpret_cast<const float4 *>(w + i);
+        a0 = vfma(f2(q.x, q.y), f2(e.x, e.y), a0);
+        a1 = vfma(f2(q.z, q.w), f2(e.z, e.w), a1);
+    }
+    const f2 a = a0 + a1;
+    return (double)(a.v.x + a.v.y);
+}
+__device__ __forceinline__ double dot_row(const double *row, const double *w, int n) {
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll 4
+    for (int i = 0; i < n; i += 2) {
+        const double2 e = *reinterpret_cast<const double2 *>(row + i);
+        const double2 q = *reinterpret_cast<const double2 *>(w + i);
+        a0 = fma(q.x, e.x, a0);
+        a1 = fma(q.y, e.y, a1);
+    }
+    return a0 + a1;
+}
+
+__device__ __forceinline__ float load_lanes(const float *p, float *) { return *p; }
+__device__ __forceinline__ double load_lanes(const double *p, double *) { return *p; }
+__device__ __forceinline__ f2 load_lanes(const float *p, f2 *) { return f2(*reinterpret_cast<const float2 *>(p)); }
+
+template <class Env, int NOISE>
+__global__ void __launch_bounds__(TILE / VT<typename Env::Vec>::N)
+    mppi_rollout_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec, const typename Env::S *__restrict__ noise,
+                        const double *__restrict__ x0g, const double *__restrict__ g_z,
+                        const double *__restrict__ Ug, double *__restrict__ S_out, double *__restrict__ part) {
+    typedef typename Env::Vec V;
+    typedef typename Env::S R;
+    constexpr int NS = Env::NS, NZ = Env::NS + 1, NG = Env::NG, PACK = VT<V>::N, NT = TILE / PACK, CH = Env::CHUNK;
+    constexpr int TS = RolloutSmem<R>::TS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int H = a.g.H;
+    const int H = a.g.H, parts = a.g.parts;
     R *tile = reinterpret_cast<R *>(smem_raw);
-    unsigned char *p = smem_raw + RolloutSmem<R>::tile_bytes(H);
-    R *sU = reinterpret_cast<R *>(p);
-    p += ((size_t)H * sizeof(R) + 15) / 16 * 16;
-    R *sw = reinterpret_cast<R *>(p);
-    p += TILE * sizeof(R);
-    double *red = reinterpret_cast<double *>(p);
-    p += 8 * sizeof(double);
-    uint64_t *bar = reinterpret_cast<uint64_t *>(p);
+    R *sU = reinterpret_cast<R *>(smem_raw + RolloutSmem<R>::off_sU(H));
+    R *sw = reinterpret_cast<R *>(smem_raw + RolloutSmem<R>::off_sw(H));
+    double *sE = reinterpret_cast<double *>(smem_raw + RolloutSmem<R>::off_sE(H));
+    double *red = reinterpret_cast<double *>(smem_raw + RolloutSmem<R>::off_red(H, parts));
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + RolloutSmem<R>::off_bar(H, parts));
 
     const int tid = threadIdx.x;
-
     const int tile0 = blockIdx.x * a.g.chunk;
     const int tile1 = min(tile0 + a.g.chunk, a.g.total_tiles);
     if (tile0 >= tile1) return;
@@ -157,16 +193,17 @@ __global__ void __launch_bounds__(TILE) mppi_rollout_kernel(const MppiArgs a, co
         __syncthreads();
     }
 
-    // running softmin state of the current solve (identical in every thread) and this thread's E slots
+    // running softmin state of the current solve (identical in every thread); E lives in shared memory
     int cur = -1;
     double beta_run = INFINITY, eta_run = 0.0;
-    double E_run[MAX_EH];
-    R g[NZ];
+    R gs[NG];
     R xinit[NS];
     uint32_t phase = 0;
-    const R pert = (R)a.pert;
+    const V pert = V((R)a.pert);
+    const int items = H * parts, KP = TILE / parts;
 
     auto flush = [&]() {
+        __syncthreads();  // every sE item of the last tile is written
         const int first_block = (int)(((long long)cur * a.g.tiles_per_solve) / a.g.chunk);
         const int slot = blockIdx.x - first_block;
         double *rec = part + ((size_t)cur * a.g.max_parts + slot) * (PART_HDR + H);
@@ -174,10 +211,10 @@ __global__ void __launch_bounds__(TILE) mppi_rollout_kernel(const MppiArgs a, co
             rec[0] = beta_run;
             rec[1] = eta_run;
         }
-#pragma unroll
-        for (int j = 0; j < MAX_EH; ++j) {
-            const int t = tid + j * TILE;
-            if (t < H) rec[PART_HDR + t] = E_run[j];
+        for (int t = tid; t < H; t += NT) {
+            double e = 0.0;
+            for (int p = 0; p < parts; ++p) e += sE[p * H + t];
+            rec[PART_HDR + t] = e;
         }
     };
 
@@ -189,12 +226,10 @@ __global__ void __launch_bounds__(TILE) mppi_rollout_kernel(const MppiArgs a, co
             cur = b;
             beta_run = INFINITY;
             eta_run = 0.0;
-#pragma unroll
-            for (int j = 0; j < MAX_EH; ++j) E_run[j] = 0.0;
-            __syncthreads();  // nobody still reads sU of the previous solve
-            for (int t = tid; t < H; t += TILE) sU[t] = (R)Ug[(size_t)b * H + t];
-#pragma unroll
-            for (int i = 0; i < NZ; ++i) g[i] = (R)g_z[(size_t)b * H * NZ + i];  // goal row 0 (model.py:34,38)
+            __syncthreads();  // nobody still reads sU / sE of the previous solve
+            for (int t = tid; t < H; t += NT) sU[t] = (R)Ug[(size_t)b * H + t];
+            for (int w = tid; w < items; w += NT) sE[w] = 0.0;
+            Env::prep_goal(ec, g_z + (size_t)b * H * NZ, gs);  // goal row 0 (model.py:34,38)
 #pragma unroll
             for (int i = 0; i < NS; ++i) xinit[i] = (R)x0g[(size_t)b * NS + i];
         }
@@ -206,73 +241,114 @@ __global__ void __launch_bounds__(TILE) mppi_rollout_kernel(const MppiArgs a, co
                 const R *src = noise + (a.noise_batched ? (size_t)b * H * a.g.Kpad : 0) + (size_t)kt * TILE;
                 mbar_expect_tx(bar, (uint32_t)(H * TILE * sizeof(R)));
                 for (int t = 0; t < H; ++t)
-                    bulk_g2s(tile + (size_t)t * TILE, src + (size_t)t * a.g.Kpad, TILE * sizeof(R), bar);
+                    bulk_g2s(tile + (size_t)t * TS, src + (size_t)t * a.g.Kpad, TILE * sizeof(R), bar);
             }
         }
-        __syncthreads();  // sU visible
-        const int kl = kt * TILE + tid;  // local sample index
-        const bool valid = kl < a.g.K_local;
-        R x[NS];
+        __syncthreads();  // sU visible; (PHILOX) the previous weighted-sum pass has finished reading the tile
+        const int kl = kt * TILE + tid * PACK;  // first local sample index of this thread
+        V x[NS];
 #pragma unroll
-        for (int i = 0; i < NS; ++i) x[i] = xinit[i];
-        double S = 0.0;
+        for (int i = 0; i < NS; ++i) x[i] = V(xinit[i]);
+        double S[PACK];
+#pragma unroll
+        for (int l = 0; l < PACK; ++l) S[l] = 0.0;
+        const R *col = tile + tid * PACK;
+        // one rollout step: noise lanes e -> u = U_t + e (mppi.py:39), cost + step (mppi.py:43-44), perturbation
+        // term lam * u * eps / sigma^2 (mppi.py:45-46)
+        auto one = [&](int t, const V &e, V &acc) {
+            const V u = V(sU[t]) + e;
+            const V c = Env::step(ec, x, u, gs);
+            acc = acc + vfma(u * e, pert, c);
+        };
+        auto fold = [&](const V &acc) {
+#pragma unroll
+            for (int l = 0; l < PACK; ++l) S[l] += (double)lane(acc, l);
+        };
         if (NOISE == NOISE_TENSOR) {
             mbar_wait(bar, phase);
             phase ^= 1u;
-            for (int t = 0; t < H; ++t) {
-                const R e = tile[t * TILE + tid];
-                const R u = sU[t] + e;                       // mppi.py:39
-                const R c = Env::step(ec, x, u, g);          // mppi.py:43-44
-                S += (double)(c + pert * u * e);             // mppi.py:45-46
+            int t = 0;
+            for (; t + CH <= H; t += CH) {
+                V acc = V((R)0);
+#pragma unroll
+                for (int i = 0; i < CH; ++i) one(t + i, load_lanes(col + (size_t)(t + i) * TS, (V *)nullptr), acc);
+                fold(acc);
+            }
+            for (; t < H; ++t) {
+                V acc = V((R)0);
+                one(t, load_lanes(col + (size_t)t * TS, (V *)nullptr), acc);
+                fold(acc);
             }
         } else {
-            const uint32_t kglob = (uint32_t)(a.g.k_begin + kl);
+            // same chunking of the float32 cost sums as the tensor path (CH divides 4), so both noise modes give
+            // bit-identical costs for identical noise values
+            static_assert(4 % CH == 0, "CHUNK must divide the Philox group of 4 steps");
             const R sig = (R)a.sigma;
             for (int t4 = 0; t4 < H; t4 += 4) {
-                float z[4];
-                philox_normal4(a.seed, 0u, a.draw, kglob, (uint32_t)(t4 >> 2), z);
+                float z[PACK][4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int t = t4 + i;
-                    if (t < H) {
-                        const R e = sig * (R)z[i];
-                        tile[t * TILE + tid] = e;
-                        const R u = sU[t] + e;
-                        const R c = Env::step(ec, x, u, g);
-                        S += (double)(c + pert * u * e);
+                for (int l = 0; l < PACK; ++l)
+                    philox_normal4(a.seed, 0u, a.draw, (uint32_t)(a.g.k_begin + kl + l), (uint32_t)(t4 >> 2), z[l]);
+                auto noise_at = [&](int i, int t) {
+                    R el[PACK];
+#pragma unroll
+                    for (int l = 0; l < PACK; ++l) {
+                        el[l] = sig * (R)z[l][i];
+                        tile[(size_t)t * TS + tid * PACK + l] = el[l];
+                    }
+                    if constexpr (PACK == 2)
+                        return V(el[0], el[PACK - 1]);
+                    else
+                        return V(el[0]);
+                };
+#pragma unroll
+                for (int c0 = 0; c0 < 4; c0 += CH) {
+                    const int t = t4 + c0;
+                    if (t + CH <= H) {
+                        V acc = V((R)0);
+#pragma unroll
+                        for (int i = 0; i < CH; ++i) one(t + i, noise_at(c0 + i, t + i), acc);
+                        fold(acc);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < CH; ++i) {
+                            if (t + i < H) {
+                                V acc = V((R)0);
+                                one(t + i, noise_at(c0 + i, t + i), acc);
+                                fold(acc);
+                            }
+                        }
                     }
                 }
             }
         }
-        if (!valid) S = INFINITY;
-        if (valid) S_out[(size_t)b * a.g.Kpad + kl] = S;
+        double Smin = INFINITY;
+#pragma unroll
+        for (int l = 0; l < PACK; ++l) {
+            const bool valid = kl + l < a.g.K_local;
+            if (!valid) S[l] = INFINITY;
+            if (valid) S_out[(size_t)b * a.g.Kpad + kl + l] = S[l];
+            Smin = fmin(Smin, S[l]);
+        }
         // ---- online softmin: rescale the running sums to the new minimum (mppi.py:59-62) ------------------
-        const double beta_tile = block_reduce<true>(S, red);
+        const double beta_tile = block_reduce<true>(Smin, red);
         const double beta_new = fmin(beta_run, beta_tile);
         const double scale_old = (eta_run == 0.0) ? 0.0 : exp(a.neg_inv_lam * (beta_run - beta_new));
-        const double w = valid ? exp(a.neg_inv_lam * (S - beta_new)) : 0.0;
-        sw[tid] = (R)w;
-        const double eta_tile = block_reduce<false>(w, red);  // its barriers also publish sw and the Philox tile
+        double wsum = 0.0;
+#pragma unroll
+        for (int l = 0; l < PACK; ++l) {
+            const double w = (S[l] == INFINITY) ? 0.0 : exp(a.neg_inv_lam * (S[l] - beta_new));
+            sw[tid * PACK + l] = (R)w;
+            wsum += w;
+        }
+        const double eta_tile = block_reduce<false>(wsum, red);  // its barriers also publish sw and the Philox tile
         eta_run = eta_run * scale_old + eta_tile;
         beta_run = beta_new;
-        // ---- E[t] += sum_k w_k eps[k][t]   (thread t owns E[t]; rotated start => no bank conflicts) --------
-#pragma unroll
-        for (int j = 0; j < MAX_EH; ++j) {
-            const int t = tid + j * TILE;
-            if (t < H) {
-                const R *row = tile + (size_t)t * TILE;
-                R acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
-#pragma unroll 4
-                for (int i = 0; i < TILE; i += 4) {
-                    const int k0 = (i + tid) & (TILE - 1), k1 = (i + 1 + tid) & (TILE - 1),
-                              k2 = (i + 2 + tid) & (TILE - 1), k3 = (i + 3 + tid) & (TILE - 1);
-                    acc0 = M<R>::fma(sw[k0], row[k0], acc0);
-                    acc1 = M<R>::fma(sw[k1], row[k1], acc1);
-                    acc2 = M<R>::fma(sw[k2], row[k2], acc2);
-                    acc3 = M<R>::fma(sw[k3], row[k3], acc3);
-                }
-                E_run[j] = E_run[j] * scale_old + (double)((acc0 + acc1) + (acc2 + acc3));
-            }
+        // ---- E[t] += sum_k w_k eps[k][t]: item (part, t) = row t, k in [part*KP, (part+1)*KP) ------------------
+        for (int w = tid; w < items; w += NT) {
+            const int p = w / H, t = w - p * H;
+            const double acc = dot_row(tile + (size_t)t * TS + p * KP, sw + p * KP, KP);
+            sE[w] = sE[w] * scale_old + acc;
         }
     }
     flush();
@@ -284,8 +360,8 @@ __global__ void __launch_bounds__(TILE) mppi_rollout_kernel(const MppiArgs a, co
 // warp w owns records j = w, w + nw, ... (eight loads in flight per thread), lanes own time steps; the per-warp
 // sums meet in shared memory in a fixed order, so repeated solves are bit-identical.
 constexpr int FIN_THREADS = 1024;
-template <class Env, typename R>
-__global__ void __launch_bounds__(FIN_THREADS) mppi_finalize_kernel(const MppiArgs a, const EnvConst<R> ec,
+template <class Env>
+__global__ void __launch_bounds__(FIN_THREADS) mppi_finalize_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec,
                                                                     const int stage, const double *__restrict__ part,
                                                                     double *__restrict__ rank_part,
                                                                     const double *__restrict__ x0g,
@@ -373,7 +449,7 @@ __global__ void __launch_bounds__(FIN_THREADS) mppi_finalize_kernel(const MppiAr
     if (tid == 0) {
         o[0] = U[0];  // u0 = planned_us[0]  (mppi.py:71)
         if (a.want_traj) {
-            o[1 + H] = nominal_rollout<Env, R>(ec, H, x0g + (size_t)b * NS, sUc, g_z + (size_t)b * H * NZ, o + 2 + H);
+            o[1 + H] = nominal_rollout<Env>(ec, H, x0g + (size_t)b * NS, sUc, g_z + (size_t)b * H * NZ, o + 2 + H);
         }
     }
 }
@@ -423,15 +499,17 @@ __device__ __forceinline__ unsigned long long reward_key(double r) {
 }
 
 // CEM.f (cem.py:42-48) for samples clip(mu + sd*z) (cem.py:58-60), one thread per sample.
-template <class Env, typename R, int NOISE>
-__global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, const EnvConst<R> ec,
-                                                          const R *__restrict__ zt, const double *__restrict__ x0g,
+template <class Env, int NOISE>
+__global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, const EnvConst<typename Env::Vec> ec,
+                                                          const typename Env::S *__restrict__ zt,
+                                                          const double *__restrict__ x0g,
                                                           const double *__restrict__ g_z,
                                                           const double *__restrict__ mu,
                                                           const double *__restrict__ sd, double *__restrict__ Rhist,
                                                           unsigned long long *__restrict__ keys,
                                                           const int *__restrict__ sel) {
-    constexpr int NS = Env::NS, NZ = Env::NS + 1;
+    typedef typename Env::S R;
+    constexpr int NS = Env::NS, NG = Env::NG;
     if (sel[SEL_DONE]) return;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int H = a.g.H, tid = threadIdx.x;
@@ -441,9 +519,8 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
         smu[t] = (R)mu[t];
         ssd[t] = (R)sd[t];
     }
-    R g[NZ], x[NS];
-#pragma unroll
-    for (int i = 0; i < NZ; ++i) g[i] = (R)g_z[i];
+    R gs[NG], x[NS];
+    Env::prep_goal(ec, g_z, gs);
 #pragma unroll
     for (int i = 0; i < NS; ++i) x[i] = (R)x0g[i];
     __syncthreads();
@@ -454,8 +531,8 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
     if (NOISE == NOISE_TENSOR) {
         for (int t = 0; t < H; ++t) {
             const R z = zt[(size_t)t * a.g.Kpad + k];
-            const R u = clip(M<R>::fma(ssd[t], z, smu[t]), lo, hi);
-            reward += -(double)Env::step(ec, x, u, g);
+            const R u = vclip(vfma(ssd[t], z, smu[t]), lo, hi);
+            reward += -(double)Env::step(ec, x, u, gs);
         }
     } else {
         const uint32_t kglob = (uint32_t)(a.g.k_begin + k);
@@ -466,8 +543,8 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
             for (int i = 0; i < 4; ++i) {
                 const int t = t4 + i;
                 if (t < H) {
-                    const R u = clip(M<R>::fma(ssd[t], (R)z[i], smu[t]), lo, hi);
-                    reward += -(double)Env::step(ec, x, u, g);
+                    const R u = vclip(vfma(ssd[t], (R)z[i], smu[t]), lo, hi);
+                    reward += -(double)Env::step(ec, x, u, gs);
                 }
             }
         }
@@ -496,7 +573,7 @@ __global__ void __launch_bounds__(128) cem_refit_kernel(const CemArgs a, const R
             philox_normal4(a.seed, 1u, (uint32_t)a.iter, (uint32_t)(a.g.k_begin + k), (uint32_t)(t >> 2), z4);
             z = (R)z4[t & 3];
         }
-        return (double)clip(M<R>::fma(s0, z, m0), lo, hi);  // identical expression to the rollout's
+        return (double)vclip(vfma(s0, z, m0), lo, hi);  // identical expression to the rollout's
     };
     double s = 0.0;
     for (int e = tid; e < n; e += blockDim.x) s += sample(e);
@@ -527,8 +604,8 @@ __global__ void __launch_bounds__(128) cem_refit_kernel(const CemArgs a, const R
 }
 
 // u0 = planned_us[0] (cem.py:77), plus the clipped plan's nominal rollout (agent.py:64-69).
-template <class Env, typename R>
-__global__ void cem_finish_kernel(const CemArgs a, const EnvConst<R> ec, const double *__restrict__ x0g,
+template <class Env>
+__global__ void cem_finish_kernel(const CemArgs a, const EnvConst<typename Env::Vec> ec, const double *__restrict__ x0g,
                                   const double *__restrict__ g_z, const double *__restrict__ mu,
                                   const int *__restrict__ sel, double *__restrict__ out) {
     constexpr int NS = Env::NS;
@@ -544,14 +621,14 @@ __global__ void cem_finish_kernel(const CemArgs a, const EnvConst<R> ec, const d
         out[0] = mu[0];
         out[2 + H + (H + 1) * NS] = (double)sel[SEL_ITERS];
         if (a.want_traj) {
-            out[1 + H] = nominal_rollout<Env, R>(ec, H, x0g, sUc, g_z, out + 2 + H);
+            out[1 + H] = nominal_rollout<Env>(ec, H, x0g, sUc, g_z, out + 2 + H);
         }
     }
 }
 
 // ================================================================================================ small kernels
-template <class Env, typename R>
-__global__ void simulate_kernel(const EnvConst<R> ec, int H, double lo, double hi, int do_clip,
+template <class Env>
+__global__ void simulate_kernel(const EnvConst<typename Env::Vec> ec, int H, double lo, double hi, int do_clip,
                                 const double *__restrict__ x0, const double *__restrict__ us,
                                 const double *__restrict__ g_z, double *__restrict__ xs, double *__restrict__ cost) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -559,23 +636,23 @@ __global__ void simulate_kernel(const EnvConst<R> ec, int H, double lo, double h
     for (int t = threadIdx.x; t < H; t += blockDim.x) sU[t] = do_clip ? fmin(fmax(us[t], lo), hi) : us[t];
     __syncthreads();
     if (threadIdx.x == 0) {
-        *cost = nominal_rollout<Env, R>(ec, H, x0, sU, g_z, xs);
+        *cost = nominal_rollout<Env>(ec, H, x0, sU, g_z, xs);
     }
 }
 
-template <class Env, typename R>
-__global__ void model_step_kernel(const EnvConst<R> ec, int n, const double *__restrict__ xg,
+template <class Env>
+__global__ void model_step_kernel(const EnvConst<typename Env::Vec> ec, int n, const double *__restrict__ xg,
                                   const double *__restrict__ ug, const double *__restrict__ gg,
                                   double *__restrict__ cost, double *__restrict__ xn) {
+    typedef typename Env::S R;
     constexpr int NS = Env::NS, NZ = Env::NS + 1;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    R x[NS], g[NZ];
+    R x[NS], gs[Env::NG];
 #pragma unroll
     for (int j = 0; j < NS; ++j) x[j] = (R)xg[(size_t)i * NS + j];
-#pragma unroll
-    for (int j = 0; j < NZ; ++j) g[j] = (R)gg[(size_t)i * NZ + j];
-    cost[i] = (double)Env::step(ec, x, (R)ug[i], g);
+    Env::prep_goal(ec, gg + (size_t)i * NZ, gs);
+    cost[i] = (double)Env::step(ec, x, (R)ug[i], gs);
 #pragma unroll
     for (int j = 0; j < NS; ++j) xn[(size_t)i * NS + j] = (double)x[j];
 }
@@ -589,7 +666,7 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float *sink, int iters) {
     const R m = (R)0.999, c = (R)1e-4;
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) a[i] = M<R>::fma(a[i], m, c);
+        for (int i = 0; i < 16; ++i) a[i] = vfma(a[i], m, c);
     }
     R s = 0;
 #pragma unroll
@@ -608,64 +685,112 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float *sink, int iters) {
 #define FN(name) MPC_CAT(name, MPC_SUFFIX)
 typedef MPC_REAL R_;
 
-#define MPC_DISPATCH_ENV(ENVID, CALL)                                \
-    do {                                                             \
-        switch (ENVID) {                                             \
-        case ENV_PENDULUM: { typedef Pendulum<R_> E_; CALL; } break; \
-        case ENV_CARTPOLE: { typedef CartPole<R_> E_; CALL; } break; \
-        default: { typedef Acrobot<R_> E_; CALL; } break;            \
-        }                                                            \
-    } while (0)
+// variant: bit 0 = fast_math (MUFU trig), bit 1 = two samples per thread (packed f32x2).  float64 has one flavour.
+enum { VAR_FAST = 1, VAR_PACK2 = 2 };
 
-template <class Env, typename R, int NOISE>
+// Calls f(Env{}) with the rollout flavour selected by (env, variant): V = float / f2 x accurate / fast, or double.
+template <class F>
+static void with_rollout_env(int env, int variant, F &&f) {
+    if constexpr (std::is_same<R_, double>::value) {
+        switch (env) {
+        case ENV_PENDULUM: f(Pendulum<double, false>{}); break;
+        case ENV_CARTPOLE: f(CartPole<double, false>{}); break;
+        default: f(Acrobot<double, false>{}); break;
+        }
+    } else {
+#define MPC_ENV_CASES(E)                                      \
+    switch (variant & 3) {                                    \
+    case 0: f(E<float, false>{}); break;                      \
+    case VAR_FAST: f(E<float, true>{}); break;                \
+    case VAR_PACK2: f(E<f2, false>{}); break;                 \
+    default: f(E<f2, true>{}); break;                         \
+    }
+        switch (env) {
+        case ENV_PENDULUM: MPC_ENV_CASES(Pendulum) break;
+        case ENV_CARTPOLE: MPC_ENV_CASES(CartPole) break;
+        default: MPC_ENV_CASES(Acrobot) break;
+        }
+#undef MPC_ENV_CASES
+    }
+}
+
+// One sample per thread: CEM rollouts (accurate or fast trig), nominal rollouts and single steps (always accurate).
+template <class F>
+static void with_scalar_env(int env, bool fast, F &&f) {
+    if constexpr (std::is_same<R_, double>::value) {
+        switch (env) {
+        case ENV_PENDULUM: f(Pendulum<double, false>{}); break;
+        case ENV_CARTPOLE: f(CartPole<double, false>{}); break;
+        default: f(Acrobot<double, false>{}); break;
+        }
+    } else {
+#define MPC_ENV_CASES(E)            \
+    if (fast)                       \
+        f(E<float, true>{});        \
+    else                            \
+        f(E<float, false>{});
+        switch (env) {
+        case ENV_PENDULUM: MPC_ENV_CASES(Pendulum) break;
+        case ENV_CARTPOLE: MPC_ENV_CASES(CartPole) break;
+        default: MPC_ENV_CASES(Acrobot) break;
+        }
+#undef MPC_ENV_CASES
+    }
+}
+
+template <class Env, int NOISE>
 static cudaError_t mppi_rollout_go(const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b, cudaStream_t s) {
-    auto kern = mppi_rollout_kernel<Env, R, NOISE>;
-    const size_t smem = RolloutSmem<R>::total(a.g.H);
+    typedef typename Env::Vec V;
+    auto kern = mppi_rollout_kernel<Env, NOISE>;
+    const size_t smem = RolloutSmem<R_>::total(a.g.H, a.g.parts);
     static size_t smem_set = 0;  // per instantiation: raise the dynamic shared memory limit only when it grows
     if (smem > smem_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         smem_set = smem;
     }
-    kern<<<a.g.grid, TILE, smem, s>>>(a, make_env<R>(ep), (const R *)b.noise, b.x0, b.g_z, b.U, b.S, b.part);
+    kern<<<a.g.grid, TILE / VT<V>::N, smem, s>>>(a, make_env<V>(ep), (const R_ *)b.noise, b.x0, b.g_z, b.U, b.S, b.part);
     return cudaGetLastError();
 }
 
-template <class Env, typename R, int NOISE>
-static int mppi_rollout_occ(int H) {
-    auto kern = mppi_rollout_kernel<Env, R, NOISE>;
-    const size_t smem = RolloutSmem<R>::total(H);
+template <class Env, int NOISE>
+static int mppi_rollout_occ(int H, int parts) {
+    auto kern = mppi_rollout_kernel<Env, NOISE>;
+    const size_t smem = RolloutSmem<R_>::total(H, parts);
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
     int occ = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, TILE, smem) != cudaSuccess) return 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, TILE / VT<typename Env::Vec>::N, smem) != cudaSuccess)
+        return 0;
     return occ;
 }
 
-size_t FN(mppi_rollout_smem)(int H) { return RolloutSmem<R_>::total(H); }
+size_t FN(mppi_rollout_smem)(int H, int parts) { return RolloutSmem<R_>::total(H, parts); }
 
-cudaError_t FN(launch_mppi_rollout)(int noise, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
-                                    cudaStream_t s) {
+cudaError_t FN(launch_mppi_rollout)(int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
+                                    const MppiBuffers &b, cudaStream_t s) {
     cudaError_t e = cudaSuccess;
-    if (noise == NOISE_TENSOR)
-        MPC_DISPATCH_ENV(ep.env, (e = mppi_rollout_go<E_, R_, NOISE_TENSOR>(a, ep, b, s)));
-    else
-        MPC_DISPATCH_ENV(ep.env, (e = mppi_rollout_go<E_, R_, NOISE_PHILOX>(a, ep, b, s)));
+    with_rollout_env(ep.env, variant, [&](auto env) {
+        typedef decltype(env) E;
+        e = (noise == NOISE_TENSOR) ? mppi_rollout_go<E, NOISE_TENSOR>(a, ep, b, s)
+                                    : mppi_rollout_go<E, NOISE_PHILOX>(a, ep, b, s);
+    });
     return e;
 }
 
-int FN(mppi_rollout_occupancy)(int noise, int env, int H) {
+int FN(mppi_rollout_occupancy)(int noise, int variant, int env, int H, int parts) {
     int occ = 0;
-    if (noise == NOISE_TENSOR)
-        MPC_DISPATCH_ENV(env, (occ = mppi_rollout_occ<E_, R_, NOISE_TENSOR>(H)));
-    else
-        MPC_DISPATCH_ENV(env, (occ = mppi_rollout_occ<E_, R_, NOISE_PHILOX>(H)));
+    with_rollout_env(env, variant, [&](auto e) {
+        typedef decltype(e) E;
+        occ = (noise == NOISE_TENSOR) ? mppi_rollout_occ<E, NOISE_TENSOR>(H, parts)
+                                      : mppi_rollout_occ<E, NOISE_PHILOX>(H, parts);
+    });
     return occ;
 }
 
-template <class Env, typename R>
+template <class Env>
 static cudaError_t mppi_finalize_go(int stage, const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b,
                                     cudaStream_t s) {
-    auto kern = mppi_finalize_kernel<Env, R>;
+    auto kern = mppi_finalize_kernel<Env>;
     const int cap = (stage == 2) ? a.world : a.g.max_parts;
     const size_t smem = ((size_t)cap + a.g.H + (size_t)(FIN_THREADS / 32) * a.g.H) * sizeof(double);
     static size_t smem_set = 48 * 1024;
@@ -674,14 +799,15 @@ static cudaError_t mppi_finalize_go(int stage, const MppiArgs &a, const EnvParam
         if (e != cudaSuccess) return e;
         smem_set = smem;
     }
-    kern<<<a.g.B, FIN_THREADS, smem, s>>>(a, make_env<R>(ep), stage, b.part, b.rank_part, b.x0, b.g_z, b.U, b.out);
+    kern<<<a.g.B, FIN_THREADS, smem, s>>>(a, make_env<typename Env::Vec>(ep), stage, b.part, b.rank_part, b.x0, b.g_z,
+                                          b.U, b.out);
     return cudaGetLastError();
 }
 
 cudaError_t FN(launch_mppi_finalize)(int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
                                      cudaStream_t s) {
     cudaError_t e = cudaSuccess;
-    MPC_DISPATCH_ENV(ep.env, (e = mppi_finalize_go<E_, R_>(stage, a, ep, b, s)));
+    with_scalar_env(ep.env, false, [&](auto env) { e = mppi_finalize_go<decltype(env)>(stage, a, ep, b, s); });
     return e;
 }
 
@@ -697,16 +823,20 @@ cudaError_t FN(launch_philox_fill)(void *dst, int K_local, int k_begin, int Kpad
     return cudaGetLastError();
 }
 
-cudaError_t FN(launch_cem_rollout)(int noise, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
-                                   cudaStream_t s) {
+cudaError_t FN(launch_cem_rollout)(int noise, int variant, const EnvParamsHost &ep, const CemArgs &a,
+                                   const CemBuffers &b, cudaStream_t s) {
     const size_t smem = 2 * (size_t)a.g.H * sizeof(double);
     const int grid = a.g.tiles_per_solve;
-    if (noise == NOISE_TENSOR)
-        MPC_DISPATCH_ENV(ep.env, (cem_rollout_kernel<E_, R_, NOISE_TENSOR><<<grid, TILE, smem, s>>>(
-                                     a, make_env<R_>(ep), (const R_ *)b.z, b.x0, b.g_z, b.mu, b.sd, b.R, b.keys, b.sel)));
-    else
-        MPC_DISPATCH_ENV(ep.env, (cem_rollout_kernel<E_, R_, NOISE_PHILOX><<<grid, TILE, smem, s>>>(
-                                     a, make_env<R_>(ep), (const R_ *)b.z, b.x0, b.g_z, b.mu, b.sd, b.R, b.keys, b.sel)));
+    with_scalar_env(ep.env, (variant & VAR_FAST) != 0, [&](auto env) {
+        typedef decltype(env) E;
+        typedef typename E::Vec V;
+        if (noise == NOISE_TENSOR)
+            cem_rollout_kernel<E, NOISE_TENSOR><<<grid, TILE, smem, s>>>(a, make_env<V>(ep), (const R_ *)b.z, b.x0, b.g_z,
+                                                                         b.mu, b.sd, b.R, b.keys, b.sel);
+        else
+            cem_rollout_kernel<E, NOISE_PHILOX><<<grid, TILE, smem, s>>>(a, make_env<V>(ep), (const R_ *)b.z, b.x0, b.g_z,
+                                                                         b.mu, b.sd, b.R, b.keys, b.sel);
+    });
     return cudaGetLastError();
 }
 
@@ -720,23 +850,29 @@ cudaError_t FN(launch_cem_refit)(int noise, const CemArgs &a, const CemBuffers &
 
 cudaError_t FN(launch_cem_finish)(const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
     const size_t smem = (size_t)a.g.H * sizeof(double);
-    MPC_DISPATCH_ENV(ep.env, (cem_finish_kernel<E_, R_><<<1, 128, smem, s>>>(a, make_env<R_>(ep), b.x0, b.g_z, b.mu,
-                                                                             b.sel, b.out)));
+    with_scalar_env(ep.env, false, [&](auto env) {
+        typedef decltype(env) E;
+        cem_finish_kernel<E><<<1, 128, smem, s>>>(a, make_env<typename E::Vec>(ep), b.x0, b.g_z, b.mu, b.sel, b.out);
+    });
     return cudaGetLastError();
 }
 
 cudaError_t FN(launch_simulate)(const EnvParamsHost &ep, int H, double lo, double hi, int do_clip, const double *x0,
                                 const double *us, const double *g_z, double *xs, double *cost, cudaStream_t s) {
     const size_t smem = (size_t)H * sizeof(double);
-    MPC_DISPATCH_ENV(ep.env, (simulate_kernel<E_, R_><<<1, 64, smem, s>>>(make_env<R_>(ep), H, lo, hi, do_clip, x0, us,
-                                                                          g_z, xs, cost)));
+    with_scalar_env(ep.env, false, [&](auto env) {
+        typedef decltype(env) E;
+        simulate_kernel<E><<<1, 64, smem, s>>>(make_env<typename E::Vec>(ep), H, lo, hi, do_clip, x0, us, g_z, xs, cost);
+    });
     return cudaGetLastError();
 }
 
 cudaError_t FN(launch_model_step)(const EnvParamsHost &ep, int n, const double *x, const double *u, const double *g,
                                   double *cost, double *xn, cudaStream_t s) {
-    MPC_DISPATCH_ENV(ep.env, (model_step_kernel<E_, R_><<<(n + 127) / 128, 128, 0, s>>>(make_env<R_>(ep), n, x, u, g,
-                                                                                        cost, xn)));
+    with_scalar_env(ep.env, false, [&](auto env) {
+        typedef decltype(env) E;
+        model_step_kernel<E><<<(n + 127) / 128, 128, 0, s>>>(make_env<typename E::Vec>(ep), n, x, u, g, cost, xn);
+    });
     return cudaGetLastError();
 }
 

@@ -5,8 +5,7 @@
 
 namespace mpc {
 
-constexpr int TILE = 128;       // samples per noise tile == threads per rollout block
-constexpr int MAX_EH = 4;       // horizon slots per thread in the weighted-sum pass: H <= TILE * MAX_EH
+constexpr int TILE = 128;       // samples per noise tile; rollout block = TILE / (samples per thread) threads
 constexpr int PART_HDR = 2;     // partial record = [beta, eta, E[0..H-1]]
 
 enum { NOISE_TENSOR = 0, NOISE_PHILOX = 1 };
@@ -14,7 +13,8 @@ enum { DT_F64 = 0, DT_F32 = 1 };
 
 struct EnvParamsHost {
     int env;
-    double c[24];  // folded constants in float64 (see fold_env_params)
+    double c[24];  // folded constants, float64 parity layout (see fold_env_params)
+    double f[24];  // folded constants, float32 throughput layout (narrowed when the kernel is launched)
 };
 
 // Geometry of one handle's shard; identical for every solve.
@@ -29,6 +29,8 @@ struct Geometry {
     int chunk;            // consecutive tiles per rollout block
     int grid;             // rollout blocks = ceil(total_tiles / chunk)
     int max_parts;        // partial records per solve (blocks that can overlap one solve)
+    int parts;            // k-range splits of the weighted-sum pass (power of two <= 8)
+    int variant;          // rollout flavour: bit 0 fast_math (MUFU trig), bit 1 two samples per thread (f32x2)
     int ns;
     size_t smem_rollout;  // dynamic shared memory of the rollout kernel
 };
@@ -81,7 +83,7 @@ struct CemBuffers {
 };
 
 // launches (kernels.cu); all return cudaGetLastError()
-cudaError_t launch_mppi_rollout(int dtype, int noise, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+cudaError_t launch_mppi_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
                                 cudaStream_t s);
 // stage: 0 = single GPU (merge block partials, apply, nominal rollout)
 //        1 = multi GPU first half  (merge block partials -> rank_part[rank])
@@ -94,7 +96,7 @@ cudaError_t launch_philox_fill(int dtype, void *dst_HK, int K_local, int k_begin
                                uint64_t seed, uint32_t draw, cudaStream_t s);
 cudaError_t launch_philox_materialize(double *dst_KH, int K_local, int k_begin, int H, uint64_t seed, uint32_t draw,
                                       cudaStream_t s);
-cudaError_t launch_cem_rollout(int dtype, int noise, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
+cudaError_t launch_cem_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
                                cudaStream_t s);
 cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s);
 cudaError_t launch_cem_refit(int dtype, int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s);
@@ -108,6 +110,7 @@ cudaError_t launch_model_step(int dtype, const EnvParamsHost &ep, int n, const d
 cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaStream_t s);
 cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s);
 
-size_t mppi_rollout_smem(int dtype, int H);
+size_t mppi_rollout_smem(int dtype, int H, int parts);
+int mppi_rollout_occupancy(int dtype, int noise, int variant, int env, int H, int parts);
 
 }  // namespace mpc

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define MPC_B200_ABI_VERSION 1
+#define MPC_B200_ABI_VERSION 2
 
 typedef struct mpc_handle mpc_handle;
 
@@ -74,6 +74,10 @@ typedef struct {
     int32_t n_elite;      /* CEM (cem.py:24) */
     int32_t resample;     /* PHILOX only: 0 = one fixed noise draw reused by every solve (the reference's MPPI
                              semantics, mppi.py:20-21), 1 = fresh draw per solve */
+    int32_t fast_math;    /* MPC_F32 only: 1 = MUFU.SIN/COS in the dynamics (abs err ~4e-7 per call) instead of the
+                             1-ulp polynomial sincos; 0 = accurate (default) */
+    int32_t lanes;        /* MPC_F32 MPPI only: samples rolled out per thread, 1 or 2 (2 = packed f32x2 arithmetic,
+                             FFMA2); 0 = library default.  Results do not depend on it. */
     double lam;           /* MPPI temperature (mppi.py:17) */
     double sigma;         /* params["std"] (mppi.py:16 / cem.py:28) */
     double epsilon;       /* CEM (cem.py:25) */
