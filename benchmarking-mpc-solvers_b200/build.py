@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmpcb200.so")
-HEADERS = ["kernels.cuh", "envs.cuh", "philox.cuh", os.path.join("..", "..", "include", "mpc_b200.h")]
+HEADERS = ["kernels.cuh", "envs.cuh", "philox.cuh", "vec.cuh", "mppi.cuh", os.path.join("..", "..", "include", "mpc_b200.h")]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
 # (object name, source, extra flags)

@@ -3,6 +3,7 @@
 #include "../../include/mpc_b200.h"
 #include "kernels.cuh"
 
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <math.h>
@@ -73,10 +74,13 @@ struct mpc_handle {
     bool profiling = false;
     // device
     void *d_noise = nullptr;      // R [Bn][H][Kpad]          (MPPI tensor / CEM z of the current iteration)
+    CUtensorMap noise_map;        // TMA descriptor over d_noise: box [H][wt] per warp tile (MPPI, TENSOR mode)
+    bool has_noise_map = false;
     double *d_in = nullptr;       // x0 [B][ns] | g_z [B][H][nz] | U [B][H]
     double *d_S = nullptr;        // [B][Kpad]
     double *d_part = nullptr;     // [B][max_parts][2+H]
     double *d_rank_part = nullptr;  // [world][B][2+H]
+    int *d_done = nullptr;        // [B] block arrival tickets of the solve kernel
     double *d_out = nullptr;      // [B][out_stride] (+1)
     double *d_scratch = nullptr;  // staging for uploads: max(K_local*H, misc)
     size_t scratch_elems = 0;
@@ -228,6 +232,8 @@ static MppiArgs mppi_args(const mpc_handle *h, int want_traj) {
     a.draw = h->cfg.resample ? (uint32_t)(h->solves & 0x7fffffffu) : 0u;
     a.noise_batched = 0;
     a.want_traj = want_traj;
+    a.goal_zero = h->g_zero_on_device ? 1 : 0;
+    a.record_only = h->cfg.world > 1 ? 1 : 0;
     a.world = h->cfg.world;
     a.rank = h->cfg.rank;
     return a;
@@ -236,6 +242,7 @@ static MppiArgs mppi_args(const mpc_handle *h, int want_traj) {
 static MppiBuffers mppi_bufs(const mpc_handle *h) {
     MppiBuffers b;
     b.noise = h->d_noise;
+    b.noise_map = h->has_noise_map ? &h->noise_map : nullptr;
     b.x0 = h->d_in + off_x(h);
     b.g_z = h->d_in + off_gz(h);
     b.U = h->d_in + off_U(h);
@@ -243,6 +250,7 @@ static MppiBuffers mppi_bufs(const mpc_handle *h) {
     b.part = h->d_part;
     b.rank_part = h->d_rank_part;
     b.out = h->d_out;
+    b.done_count = h->d_done;
     return b;
 }
 
@@ -277,6 +285,36 @@ static CemBuffers cem_bufs(const mpc_handle *h) {
     return b;
 }
 
+// TMA descriptor of the resident noise tensor.  cuTensorMapEncodeTiled lives in the driver library; it is resolved
+// through the runtime (no link against libcuda).
+static int encode_noise_map(mpc_handle *h) {
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+            return fail(nullptr, MPC_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+        encode = (encode_fn)fn;
+    }
+    const Geometry &g = h->g;
+    const bool f32 = h->cfg.dtype == MPC_F32;
+    const cuuint64_t esz = f32 ? 4 : 8;
+    const cuuint64_t gdim[3] = {(cuuint64_t)g.Kpad, (cuuint64_t)g.H, 1};
+    const cuuint64_t gstride[2] = {(cuuint64_t)g.Kpad * esz, (cuuint64_t)g.Kpad * esz * g.H};
+    const cuuint32_t box[3] = {(cuuint32_t)g.wt, (cuuint32_t)g.H, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = encode(&h->noise_map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3,
+                        h->d_noise, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(nullptr, MPC_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    h->has_noise_map = true;
+    return MPC_OK;
+}
+
 extern "C" {
 
 int mpc_abi_version(void) { return MPC_B200_ABI_VERSION; }
@@ -293,6 +331,7 @@ int mpc_destroy(mpc_handle *h) {
     cudaFree(h->d_S);
     cudaFree(h->d_part);
     cudaFree(h->d_rank_part);
+    cudaFree(h->d_done);
     cudaFree(h->d_out);
     cudaFree(h->d_scratch);
     cudaFree(h->d_sd);
@@ -384,35 +423,85 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     g.Kpad = (g.K_local + TILE - 1) / TILE * TILE;
     g.H = cfg->H;
     g.B = cfg->batch;
-    g.ns = h->ns;
-    g.tiles_per_solve = g.Kpad / TILE;
-    g.total_tiles = g.B * g.tiles_per_solve;
     // rollout flavour: float32 rolls out two samples per thread (packed f32x2) unless asked otherwise
     const int lanes = (cfg->dtype == MPC_F32 && cfg->agent == MPC_AGENT_MPPI) ? (cfg->lanes ? cfg->lanes : 2) : 1;
     g.variant = (cfg->dtype == MPC_F32 && cfg->fast_math ? 1 : 0) | (lanes == 2 ? 2 : 0);
-    // weighted-sum pass: H x parts work items over the block's threads, about two rounds
-    const int nt = TILE / lanes;
-    g.parts = 1;
-    while (g.parts < 8 && g.H * g.parts < 2 * nt) g.parts *= 2;
-    g.smem_rollout = mppi_rollout_smem(cfg->dtype, cfg->H, g.parts);
-    int max_smem = 0;
-    CUC(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
-    if (cfg->agent == MPC_AGENT_MPPI && g.smem_rollout > (size_t)max_smem) {
-        int rc = fail(nullptr, MPC_EINVAL, "H = %d needs %zu B of shared memory per block (limit %d)", cfg->H,
-                      g.smem_rollout, max_smem);
-        mpc_destroy(h);
-        return rc;
-    }
-    int occ = 1;
+    g.wt = 32 * lanes;
+    g.tiles_per_solve = g.Kpad / g.wt;
+    g.total_tiles = g.B * g.tiles_per_solve;
+    g.ns = h->ns;
     if (cfg->agent == MPC_AGENT_MPPI) {
-        occ = mppi_rollout_occupancy(cfg->dtype, cfg->noise, g.variant, cfg->env, cfg->H, g.parts);
-        if (occ < 1) occ = 1;
+        // ---- solve-kernel shape (mppi.cuh): W warps, ring of S stages, one block per SM -------------------------
+        if (cfg->H > MPPI_MAX_H) {
+            int rc = fail(nullptr, MPC_EINVAL, "H = %d exceeds the %d steps the weighted-sum registers hold", cfg->H,
+                          MPPI_MAX_H);
+            mpc_destroy(h);
+            return rc;
+        }
+        int max_smem = 0;
+        CUC(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
+        const size_t esz_r = cfg->dtype == MPC_F32 ? 4 : 8;
+        const size_t stage = mppi_stage_bytes(cfg->dtype, g.variant, cfg->H);
+        const long long fixed = 1024 + (long long)MPPI_MAX_WARPS * (cfg->H + g.wt) * esz_r + MPPI_MAX_WARPS * 8 * 2;
+        int s_cap = (int)(((long long)max_smem - fixed) / (long long)stage);
+        if (s_cap > 32) s_cap = 32;
+        if (s_cap < 1) {
+            int rc = fail(nullptr, MPC_EINVAL, "H = %d needs %zu B of shared memory per warp tile (limit %d)", cfg->H, stage,
+                          max_smem);
+            mpc_destroy(h);
+            return rc;
+        }
+        int W, S;
+        if (cfg->noise == MPC_NOISE_PHILOX) {
+            W = S = s_cap < MPPI_MAX_WARPS ? s_cap : MPPI_MAX_WARPS;  // one private buffer per warp, nothing to prefetch
+        } else {
+            // measured (tools/tune_probe.py, profiles/): more resident warps beat deeper prefetch, and warp counts that
+            // fill the four SM sub-partitions evenly (multiples of 4) beat the ones in between
+            S = s_cap;
+            W = S < MPPI_MAX_WARPS ? S : MPPI_MAX_WARPS;
+            if (W >= 8) W -= W % 4;
+        }
+        // tuning knobs (profiling only): MPC_B200_WARPS, MPC_B200_STAGES
+        if (const char *e = getenv("MPC_B200_WARPS")) { int v = atoi(e); if (v >= 1 && v <= MPPI_MAX_WARPS && v <= s_cap) W = v; }
+        if (const char *e = getenv("MPC_B200_STAGES")) { int v = atoi(e); if (v >= W && v <= s_cap) S = v; }
+        if (cfg->noise == MPC_NOISE_PHILOX || S < W) S = W;
+        const int tps = g.tiles_per_solve;
+        if (g.B >= h->num_sms && tps <= 4 * W) {  // mode B: many small solves, a block owns whole solves
+            g.solves_per_block = (g.B + h->num_sms - 1) / h->num_sms;
+            g.grid = (g.B + g.solves_per_block - 1) / g.solves_per_block;
+            g.blocks_per_solve = 1;
+            g.chunk = tps;
+            g.max_parts = W;
+            const long long per = (long long)cfg->H * (1 + h->nz) * 8;
+            long long G = (96 * 1024) / per;
+            if (G > g.solves_per_block) G = g.solves_per_block;
+            if (G > W * 32) G = W * 32;
+            g.fin_group = G < 1 ? 1 : (int)G;
+        } else {  // mode A: blocks_per_solve blocks share a solve
+            int nb = g.B >= h->num_sms ? 1 : h->num_sms / g.B;
+            const int want = (tps + W - 1) / W;
+            if (nb > want) nb = want;
+            if (nb < 1) nb = 1;
+            g.chunk = (tps + nb - 1) / nb;
+            nb = (tps + g.chunk - 1) / g.chunk;
+            if (g.chunk < W) { W = g.chunk; if (cfg->noise == MPC_NOISE_PHILOX) S = W; }
+            g.solves_per_block = 0;
+            g.blocks_per_solve = nb;
+            g.grid = g.B * nb;
+            g.max_parts = nb;
+            g.fin_group = 1;
+        }
+        g.warps = W;
+        g.stages = S;
+        const int cap = g.max_parts > W ? g.max_parts : W;
+        g.smem_rollout = mppi_solve_smem(cfg->dtype, g.variant, cfg->H, S, W, cap, g.fin_group, h->nz);
+        if (g.smem_rollout > (size_t)max_smem) {
+            int rc = fail(nullptr, MPC_EINVAL, "solve kernel needs %zu B of shared memory (limit %d)", g.smem_rollout,
+                          max_smem);
+            mpc_destroy(h);
+            return rc;
+        }
     }
-    const int slots = h->num_sms * occ;
-    g.chunk = (g.total_tiles + slots - 1) / slots;
-    g.grid = (g.total_tiles + g.chunk - 1) / g.chunk;
-    g.max_parts = (g.tiles_per_solve + g.chunk - 1) / g.chunk + 1;
-    if (g.max_parts > g.grid) g.max_parts = g.grid;
 
     // ---- buffers ------------------------------------------------------------------------------------------
     const size_t esz = cfg->dtype == MPC_F32 ? 4 : 8;
@@ -431,11 +520,20 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     if (cfg->noise == MPC_NOISE_TENSOR) {
         CUC(cudaMalloc(&h->d_noise, (size_t)g.H * g.Kpad * esz));
         CUC(cudaMemsetAsync(h->d_noise, 0, (size_t)g.H * g.Kpad * esz, h->stream));
+        if (cfg->agent == MPC_AGENT_MPPI) {
+            const int rc = encode_noise_map(h);
+            if (rc) {
+                mpc_destroy(h);
+                return rc;
+            }
+        }
     }
     if (cfg->agent == MPC_AGENT_MPPI) {
         CUC(cudaMalloc(&h->d_S, (size_t)g.B * g.Kpad * sizeof(double)));
         CUC(cudaMalloc(&h->d_part, (size_t)g.B * g.max_parts * rec * sizeof(double)));
         CUC(cudaMalloc(&h->d_rank_part, (size_t)cfg->world * g.B * rec * sizeof(double)));
+        CUC(cudaMalloc(&h->d_done, (size_t)g.B * sizeof(int)));
+        CUC(cudaMemsetAsync(h->d_done, 0, (size_t)g.B * sizeof(int), h->stream));
     } else {
         CUC(cudaMalloc(&h->d_sd, (size_t)g.H * sizeof(double)));
         CUC(cudaMalloc(&h->d_R, (size_t)cfg->max_iter * g.Kpad * sizeof(double)));
@@ -577,20 +675,16 @@ static int mppi_enqueue(mpc_handle *h, int want_traj) {
     const MppiArgs a = mppi_args(h, want_traj);
     const MppiBuffers b = mppi_bufs(h);
     if (h->profiling) CU(h, cudaEventRecord(h->evr0, h->stream));
-    CU(h, launch_mppi_rollout(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
+    CU(h, launch_mppi_solve(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
     if (h->profiling) CU(h, cudaEventRecord(h->evr1, h->stream));
     h->launches++;
-    if (h->cfg.world == 1) {
-        CU(h, launch_mppi_finalize(h->cfg.dtype, 0, h->ep, a, b, h->stream));
-        h->launches++;
-    } else {
-        CU(h, launch_mppi_finalize(h->cfg.dtype, 1, h->ep, a, b, h->stream));
+    if (h->cfg.world > 1) {
         const size_t cnt = (size_t)h->g.B * (PART_HDR + h->g.H);
         ncclResult_t r = g_nccl.AllGather(h->d_rank_part + (size_t)h->cfg.rank * cnt, h->d_rank_part, cnt, ncclFloat64,
                                           h->comm, h->stream);
         if (r != 0) return fail(h, MPC_ENCCL, "ncclAllGather: %s", g_nccl.GetErrorString(r));
-        CU(h, launch_mppi_finalize(h->cfg.dtype, 2, h->ep, a, b, h->stream));
-        h->launches += 3;
+        CU(h, launch_mppi_rank_merge(h->cfg.dtype, h->ep, a, b, h->stream));
+        h->launches += 2;
     }
     h->solves++;
     return MPC_OK;
@@ -615,11 +709,11 @@ int mpc_mppi_rollout_partial(mpc_handle *h, const double *x, const double *g_z, 
     CU(h, cudaSetDevice(h->cfg.device));
     int rc = stage_inputs(h, x, g_z, U_in);
     if (rc) return rc;
-    const MppiArgs a = mppi_args(h, 0);
+    MppiArgs a = mppi_args(h, 0);
+    a.record_only = 1;
     const MppiBuffers b = mppi_bufs(h);
-    CU(h, launch_mppi_rollout(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
-    CU(h, launch_mppi_finalize(h->cfg.dtype, 1, h->ep, a, b, h->stream));
-    h->launches += 2;
+    CU(h, launch_mppi_solve(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
+    h->launches++;
     const size_t cnt = (size_t)h->g.B * (PART_HDR + h->g.H);
     CU(h, cudaMemcpyAsync(rec_out, h->d_rank_part + (size_t)h->cfg.rank * cnt, cnt * sizeof(double),
                           cudaMemcpyDeviceToHost, h->stream));
@@ -635,7 +729,7 @@ int mpc_mppi_apply_partials(mpc_handle *h, const double *recs, double *u0, doubl
     const int want_traj = (xs_out || cost_out) ? 1 : 0;
     const size_t cnt = (size_t)h->cfg.world * h->g.B * (PART_HDR + h->g.H);
     CU(h, cudaMemcpyAsync(h->d_rank_part, recs, cnt * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-    CU(h, launch_mppi_finalize(h->cfg.dtype, 2, h->ep, mppi_args(h, want_traj), mppi_bufs(h), h->stream));
+    CU(h, launch_mppi_rank_merge(h->cfg.dtype, h->ep, mppi_args(h, want_traj), mppi_bufs(h), h->stream));
     h->launches++;
     h->solves++;
     return fetch_outputs(h, want_traj, u0, U_out, xs_out, cost_out);
@@ -928,7 +1022,7 @@ int64_t mpc_launch_count(const mpc_handle *h) { return h ? h->launches : 0; }
 int mpc_get_geometry(const mpc_handle *h, int32_t out[6]) {
     if (!h || !out) return MPC_EINVAL;
     out[0] = h->g.grid;
-    out[1] = TILE / ((h->g.variant & 2) ? 2 : 1);
+    out[1] = h->g.warps * 32;
     out[2] = (int32_t)h->g.smem_rollout;
     out[3] = h->g.total_tiles;
     out[4] = h->g.K_local;

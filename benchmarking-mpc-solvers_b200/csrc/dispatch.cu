@@ -116,10 +116,10 @@ __global__ void fill_kernel(float *p, size_t n, float v) {
 
 
 #define DECL2(ret, name, ...) ret name##_f32(__VA_ARGS__); ret name##_f64(__VA_ARGS__);
-DECL2(size_t, mppi_rollout_smem, int, int)
-DECL2(cudaError_t, launch_mppi_rollout, int, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
-DECL2(int, mppi_rollout_occupancy, int, int, int, int, int)
-DECL2(cudaError_t, launch_mppi_finalize, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
+DECL2(size_t, mppi_solve_smem, int, int, int, int, int, int, int)
+DECL2(size_t, mppi_stage_bytes, int, int)
+DECL2(cudaError_t, launch_mppi_solve, int, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
+DECL2(cudaError_t, launch_mppi_rank_merge, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
 DECL2(cudaError_t, launch_transpose_noise, const double *, void *, int, int, int, cudaStream_t)
 DECL2(cudaError_t, launch_philox_fill, void *, int, int, int, int, double, uint64_t, uint32_t, cudaStream_t)
 DECL2(cudaError_t, launch_cem_rollout, int, int, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
@@ -133,17 +133,17 @@ DECL2(cudaError_t, launch_fma_peak, float *, int, int, cudaStream_t)
 #undef DECL2
 #define BY_DTYPE(name, ...) ((dtype) == DT_F32 ? name##_f32(__VA_ARGS__) : name##_f64(__VA_ARGS__))
 
-size_t mppi_rollout_smem(int dtype, int H, int parts) { return BY_DTYPE(mppi_rollout_smem, H, parts); }
-int mppi_rollout_occupancy(int dtype, int noise, int variant, int env, int H, int parts) {
-    return BY_DTYPE(mppi_rollout_occupancy, noise, variant, env, H, parts);
+size_t mppi_solve_smem(int dtype, int variant, int H, int S, int W, int cap, int G, int nz) {
+    return BY_DTYPE(mppi_solve_smem, variant, H, S, W, cap, G, nz);
 }
-cudaError_t launch_mppi_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
-                                const MppiBuffers &b, cudaStream_t s) {
-    return BY_DTYPE(launch_mppi_rollout, noise, variant, ep, a, b, s);
+size_t mppi_stage_bytes(int dtype, int variant, int H) { return BY_DTYPE(mppi_stage_bytes, variant, H); }
+cudaError_t launch_mppi_solve(int dtype, int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
+                              const MppiBuffers &b, cudaStream_t s) {
+    return BY_DTYPE(launch_mppi_solve, noise, variant, ep, a, b, s);
 }
-cudaError_t launch_mppi_finalize(int dtype, int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
-                                 cudaStream_t s) {
-    return BY_DTYPE(launch_mppi_finalize, stage, ep, a, b, s);
+cudaError_t launch_mppi_rank_merge(int dtype, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                   cudaStream_t s) {
+    return BY_DTYPE(launch_mppi_rank_merge, ep, a, b, s);
 }
 cudaError_t launch_transpose_noise(int dtype, const double *src, void *dst, int K_local, int Kpad, int H,
                                    cudaStream_t s) {

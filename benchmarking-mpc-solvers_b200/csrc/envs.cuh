@@ -39,6 +39,15 @@ struct EnvConst {
     V c[24];
 };
 
+// the one-sample view of the constants (lane 0 of every packed pair)
+template <typename V>
+__device__ __forceinline__ EnvConst<typename VT<V>::S> scalar_consts(const EnvConst<V> &k) {
+    EnvConst<typename VT<V>::S> o;
+#pragma unroll
+    for (int i = 0; i < 24; ++i) o.c[i] = lane(k.c[i], 0);
+    return o;
+}
+
 template <typename V>
 __device__ __forceinline__ typename VT<V>::S k0(const EnvConst<V> &k, int i) {
     return lane(k.c[i], 0);
@@ -56,6 +65,7 @@ struct Pendulum {
     static constexpr int ENV = ENV_PENDULUM;
     typedef typename VT<V>::S S;
     typedef V Vec;
+    typedef Pendulum<S, false> Scalar;  // one sample per thread, accurate trig: nominal rollouts
     // cost = sum W_i (z_i - g_i)^2 with z = -[thn, om, u]  ==  sum (sW_i*[thn, om, u]_i + sW_i*g_i)^2
     static __device__ __forceinline__ void prep_goal(const EnvConst<V> &k, const double *g, S *gs) {
 #pragma unroll
@@ -63,10 +73,10 @@ struct Pendulum {
     }
     static __device__ __forceinline__ V step(const EnvConst<V> &k, V (&x)[NS], const V &u, const S *gs) {
         const V th = x[0], om = x[1];
-        // angle_normalize: ((th + pi) mod 2pi) - pi with numpy's floored remainder == th - 2pi*floor((th + pi)/2pi)
-        const V n = vfloor(vfma(th, V(F_INV_2PI), V(0.5f)));
-        V thn = vfma(n, V(-F_2PI_HI), th);
-        thn = vfma(n, V(-F_2PI_LO), thn);
+        // angle_normalize: ((th + pi) mod 2pi) - pi == th - 2pi*floor((th + pi)/2pi).  Round-to-nearest instead of
+        // floor differs only when th is an odd multiple of pi exactly (+pi instead of -pi): same cost (thn^2) and
+        // |sin| < 1e-7 either way, and it needs no compare/select on the ALU pipe.
+        const V thn = vwrap_pi(th);
         const V d0 = vfma(k.c[5], thn, V(gs[0])), d1 = vfma(k.c[6], om, V(gs[1])), d2 = vfma(k.c[7], u, V(gs[2]));
         const V cost = vfma(d0, d0, vfma(d1, d1, d2 * d2));   // u NOT clipped in the cost   pendulum_model.py:40-50
         // dynamics: sin(th + pi) = -sin(th) = -sin(thn)                                      pendulum_model.py:28-38
@@ -86,6 +96,7 @@ struct Pendulum<double, FAST> {
     static constexpr int ENV = ENV_PENDULUM;
     typedef double S;
     typedef double Vec;
+    typedef Pendulum<double, FAST> Scalar;
     static __device__ __forceinline__ void prep_goal(const EnvConst<double> &, const double *g, double *gs) {
 #pragma unroll
         for (int i = 0; i < 3; ++i) gs[i] = g[i];
@@ -122,6 +133,7 @@ struct CartPole {
     static constexpr int ENV = ENV_CARTPOLE;
     typedef typename VT<V>::S S;
     typedef V Vec;
+    typedef CartPole<S, false> Scalar;  // one sample per thread, accurate trig: nominal rollouts
     // z = [xc, pd, 1 - cos th, thd, u]; residual_i = sW_i (z_i - g_i)
     static __device__ __forceinline__ void prep_goal(const EnvConst<V> &k, const double *g, S *gs) {
         gs[0] = -k0(k, 13) * (S)g[0];
@@ -169,6 +181,7 @@ struct CartPole<double, FAST> {
     static constexpr int ENV = ENV_CARTPOLE;
     typedef double S;
     typedef double Vec;
+    typedef CartPole<double, FAST> Scalar;
     static __device__ __forceinline__ void prep_goal(const EnvConst<double> &, const double *g, double *gs) {
 #pragma unroll
         for (int i = 0; i < 5; ++i) gs[i] = g[i];
@@ -210,6 +223,7 @@ struct Acrobot {
     static constexpr int ENV = ENV_ACROBOT;
     typedef typename VT<V>::S S;
     typedef V Vec;
+    typedef Acrobot<S, false> Scalar;  // one sample per thread, accurate trig: nominal rollouts
     // z = [-cos th1 - cos(th1+th2) - 2, 0, 0, 0, u]                                   acrobot_model.py:162-176
     static __device__ __forceinline__ void prep_goal(const EnvConst<V> &k, const double *g, S *gs) {
         gs[0] = k0(k, 11) * (S)(2.0 + g[0]);  // residual_0 = -(sW0 (c1 + c12) + gs0)
@@ -282,6 +296,7 @@ struct Acrobot<double, FAST> {
     static constexpr int ENV = ENV_ACROBOT;
     typedef double S;
     typedef double Vec;
+    typedef Acrobot<double, FAST> Scalar;
     static __device__ __forceinline__ void prep_goal(const EnvConst<double> &, const double *g, double *gs) {
 #pragma unroll
         for (int i = 0; i < 5; ++i) gs[i] = g[i];

@@ -1,19 +1,18 @@
 // kernels.cu — sm_100a device code of the sampling-MPC inner loop.
 //
-//   mppi_rollout_kernel   MPPI.f for every sample (mppi.py:35-48) fused with the softmin-weighted noise sum of
-//                         MPPI._calc_action (mppi.py:59-67): the noise tile is staged ONCE in shared memory by
-//                         bulk async copies (cp.async.bulk + mbarrier), rolled out with the state in registers,
-//                         then reused for sum_k w_k eps[k][t] with an online (running-min) rescaling, so the noise
-//                         tensor is read from HBM once per solve.
-//   mppi_finalize_kernel  merges the per-block partials (log-sum-exp style), planned_us += erg (mppi.py:69), and the
-//                         clipped plan's nominal rollout (agent.py:64-69,97-108).
+//   mppi_solve_kernel     (mppi.cuh) the whole MPPI solve in one persistent launch: MPPI.f for every sample
+//                         (mppi.py:35-48), softmin-weighted noise sum (mppi.py:59-67), planned_us += erg (mppi.py:69)
+//                         and the clipped plan's nominal rollout (agent.py:64-69,97-108)
+//   mppi_rank_merge_kernel  multi-GPU: merges the gathered rank records and applies them
 //   cem_*                 CEM._calc_action (cem.py:54-78): rollout of clip(mu + sd*z), radix top-n_elite select,
 //                         elite mean / std refit with alpha smoothing and the epsilon test.
 #include "kernels.cuh"
 #include "envs.cuh"
 #include "philox.cuh"
 
+#include <cuda.h>  // CUtensorMap (type only; the encoder is resolved at run time in capi.cu)
 #include <float.h>
+#include <string.h>
 
 namespace mpc {
 
@@ -34,6 +33,14 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                      smem_u32(dst_smem)),
                  "l"(__cvta_generic_to_global(src_gmem)), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
+}
+// TMA: box of a rank-3 tensor map -> shared memory, completing on an mbarrier (SASS: UTMALDG)
+__device__ __forceinline__ void tma_load_3d(void *dst_smem, const CUtensorMap *map, int c0, int c1, int c2, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+        : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     uint32_t ok;
@@ -88,11 +95,13 @@ static EnvConst<V> make_env(const EnvParamsHost &ep) {
 }
 
 // Nominal rollout of one plan by a single thread: Agent.simulate_trajectory (agent.py:97-108).
-// us: plan (already clipped by the caller if required), g_z rows per step, xs [H+1][ns] (nullable), returns cost.
+// us: plan (already clipped by the caller if required); goal row of step t at g_z + t * g_stride (g_stride = 0: one
+// row for every step); xs [H+1][ns] (nullable); returns the cost.  Callers keep us / g_z in shared memory: the loop is
+// a serial dependency chain and must not wait on global loads.
 template <class Env>
 __device__ double nominal_rollout(const EnvConst<typename Env::Vec> &ec, int H, const double *x0, const double *us,
-                                  const double *g_z, double *xs) {
-    constexpr int NS = Env::NS, NZ = Env::NS + 1;
+                                  const double *g_z, int g_stride, double *xs) {
+    constexpr int NS = Env::NS;
     typedef typename Env::S R;
     R x[NS];
 #pragma unroll
@@ -101,9 +110,10 @@ __device__ double nominal_rollout(const EnvConst<typename Env::Vec> &ec, int H, 
         if (xs) xs[i] = x0[i];
     }
     double reward = 0.0;
+    R gs[Env::NG];
+    if (g_stride == 0) Env::prep_goal(ec, g_z, gs);
     for (int t = 0; t < H; ++t) {
-        R gs[Env::NG];
-        Env::prep_goal(ec, g_z + t * NZ, gs);
+        if (g_stride != 0) Env::prep_goal(ec, g_z + t * g_stride, gs);
         const R c = Env::step(ec, x, (R)us[t], gs);
         reward += -(double)c;
         if (xs) {
@@ -114,345 +124,13 @@ __device__ double nominal_rollout(const EnvConst<typename Env::Vec> &ec, int H, 
     return -reward;
 }
 
-// ================================================================================================ MPPI rollout
-// One block = NT = TILE / PACK threads, each rolling out PACK samples of a 128-sample tile (PACK = 2: the two samples
-// travel in one f2 and every FMA-pipe instruction is an FFMA2/FADD2/FMUL2).
-// Shared memory: noise tile [H][TS] (row stride TS = TILE + pad keeps rows 16-byte aligned for the bulk copies and
-// makes the LDS.128 row reads of the weighted-sum pass conflict-free) | sU[H] | sw[TILE] | sE[H*parts] (float64
-// running sums) | red[8] | mbarrier
-template <typename R>
-struct RolloutSmem {
-    static constexpr int PAD = 16 / sizeof(R);
-    static constexpr int TS = TILE + PAD;
-    static __host__ __device__ size_t align16(size_t b) { return (b + 15) / 16 * 16; }
-    static __host__ __device__ size_t off_sU(int H) { return (size_t)H * TS * sizeof(R); }
-    static __host__ __device__ size_t off_sw(int H) { return off_sU(H) + align16((size_t)H * sizeof(R)); }
-    static __host__ __device__ size_t off_sE(int H) { return off_sw(H) + TILE * sizeof(R); }
-    static __host__ __device__ size_t off_red(int H, int parts) { return off_sE(H) + (size_t)H * parts * sizeof(double); }
-    static __host__ __device__ size_t off_bar(int H, int parts) { return off_red(H, parts) + 8 * sizeof(double); }
-    static __host__ __device__ size_t total(int H, int parts) { return off_bar(H, parts) + 16; }
-};
-
-// sum_k w[k] * row[k] over n (multiple of 4) consecutive k: 128-bit shared loads, packed FMAs in float32
-__device__ __forceinline__ double dot_row(const float *row, const float *w, int n) {
-    f2 a0(0.f), a1(0.f);
-#pragma unroll 4
-    for (int i = 0; i < n; i += 4) {
-        const float4 e = *reinterpret_cast<const float4 *>(row + i);
-        const float4 q = *reinterpret_cast<const float4 *>(w + i);
-        a0 = vfma(f2(q.x, q.y), f2(e.x, e.y), a0);
-        a1 = vfma(f2(q.z, q.w), f2(e.z, e.w), a1);
-    }
-    const f2 a = a0 + a1;
-    return (double)(a.v.x + a.v.y);
-}
-__device__ __forceinline__ double dot_row(const double *row, const double *w, int n) {
-    double a0 = 0.0, a1 = 0.0;
-#pragma unroll 4
-    for (int i = 0; i < n; i += 2) {
-        const double2 e = *reinterpret_cast<const double2 *>(row + i);
-        const double2 q = *reinterpret_cast<const double2 *>(w + i);
-        a0 = fma(q.x, e.x, a0);
-        a1 = fma(q.y, e.y, a1);
-    }
-    return a0 + a1;
-}
-
 __device__ __forceinline__ float load_lanes(const float *p, float *) { return *p; }
 __device__ __forceinline__ double load_lanes(const double *p, double *) { return *p; }
 __device__ __forceinline__ f2 load_lanes(const float *p, f2 *) { return f2(*reinterpret_cast<const float2 *>(p)); }
 
-template <class Env, int NOISE>
-__global__ void __launch_bounds__(TILE / VT<typename Env::Vec>::N)
-    mppi_rollout_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec, const typename Env::S *__restrict__ noise,
-                        const double *__restrict__ x0g, const double *__restrict__ g_z,
-                        const double *__restrict__ Ug, double *__restrict__ S_out, double *__restrict__ part) {
-    typedef typename Env::Vec V;
-    typedef typename Env::S R;
-    constexpr int NS = Env::NS, NZ = Env::NS + 1, NG = Env::NG, PACK = VT<V>::N, NT = TILE / PACK, CH = Env::CHUNK;
-    constexpr int TS = RolloutSmem<R>::TS;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int H = a.g.H, parts = a.g.parts;
-    R *tile = reinterpret_cast<R *>(smem_raw);
-    R *sU = reinterpret_cast<R *>(smem_raw + RolloutSmem<R>::off_sU(H));
-    R *sw = reinterpret_cast<R *>(smem_raw + RolloutSmem<R>::off_sw(H));
-    double *sE = reinterpret_cast<double *>(smem_raw + RolloutSmem<R>::off_sE(H));
-    double *red = reinterpret_cast<double *>(smem_raw + RolloutSmem<R>::off_red(H, parts));
-    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + RolloutSmem<R>::off_bar(H, parts));
-
-    const int tid = threadIdx.x;
-    const int tile0 = blockIdx.x * a.g.chunk;
-    const int tile1 = min(tile0 + a.g.chunk, a.g.total_tiles);
-    if (tile0 >= tile1) return;
-
-    if (NOISE == NOISE_TENSOR) {
-        if (tid == 0) {
-            mbar_init(bar, 1);
-            fence_mbar_init();
-        }
-        __syncthreads();
-    }
-
-    // running softmin state of the current solve (identical in every thread); E lives in shared memory
-    int cur = -1;
-    double beta_run = INFINITY, eta_run = 0.0;
-    R gs[NG];
-    R xinit[NS];
-    uint32_t phase = 0;
-    const V pert = V((R)a.pert);
-    const int items = H * parts, KP = TILE / parts;
-
-    auto flush = [&]() {
-        __syncthreads();  // every sE item of the last tile is written
-        const int first_block = (int)(((long long)cur * a.g.tiles_per_solve) / a.g.chunk);
-        const int slot = blockIdx.x - first_block;
-        double *rec = part + ((size_t)cur * a.g.max_parts + slot) * (PART_HDR + H);
-        if (tid == 0) {
-            rec[0] = beta_run;
-            rec[1] = eta_run;
-        }
-        for (int t = tid; t < H; t += NT) {
-            double e = 0.0;
-            for (int p = 0; p < parts; ++p) e += sE[p * H + t];
-            rec[PART_HDR + t] = e;
-        }
-    };
-
-    for (int tg = tile0; tg < tile1; ++tg) {
-        const int b = tg / a.g.tiles_per_solve;
-        const int kt = tg - b * a.g.tiles_per_solve;
-        if (b != cur) {
-            if (cur >= 0) flush();
-            cur = b;
-            beta_run = INFINITY;
-            eta_run = 0.0;
-            __syncthreads();  // nobody still reads sU / sE of the previous solve
-            for (int t = tid; t < H; t += NT) sU[t] = (R)Ug[(size_t)b * H + t];
-            for (int w = tid; w < items; w += NT) sE[w] = 0.0;
-            Env::prep_goal(ec, g_z + (size_t)b * H * NZ, gs);  // goal row 0 (model.py:34,38)
-#pragma unroll
-            for (int i = 0; i < NS; ++i) xinit[i] = (R)x0g[(size_t)b * NS + i];
-        }
-        // ---- stage the [H][TILE] noise tile ------------------------------------------------------------
-        if (NOISE == NOISE_TENSOR) {
-            __syncthreads();  // the previous tile's readers are done (generic proxy) ...
-            if (tid == 0) {
-                fence_proxy_async();  // ... before the async proxy overwrites it
-                const R *src = noise + (a.noise_batched ? (size_t)b * H * a.g.Kpad : 0) + (size_t)kt * TILE;
-                mbar_expect_tx(bar, (uint32_t)(H * TILE * sizeof(R)));
-                for (int t = 0; t < H; ++t)
-                    bulk_g2s(tile + (size_t)t * TS, src + (size_t)t * a.g.Kpad, TILE * sizeof(R), bar);
-            }
-        }
-        __syncthreads();  // sU visible; (PHILOX) the previous weighted-sum pass has finished reading the tile
-        const int kl = kt * TILE + tid * PACK;  // first local sample index of this thread
-        V x[NS];
-#pragma unroll
-        for (int i = 0; i < NS; ++i) x[i] = V(xinit[i]);
-        double S[PACK];
-#pragma unroll
-        for (int l = 0; l < PACK; ++l) S[l] = 0.0;
-        const R *col = tile + tid * PACK;
-        // one rollout step: noise lanes e -> u = U_t + e (mppi.py:39), cost + step (mppi.py:43-44), perturbation
-        // term lam * u * eps / sigma^2 (mppi.py:45-46)
-        auto one = [&](int t, const V &e, V &acc) {
-            const V u = V(sU[t]) + e;
-            const V c = Env::step(ec, x, u, gs);
-            acc = acc + vfma(u * e, pert, c);
-        };
-        auto fold = [&](const V &acc) {
-#pragma unroll
-            for (int l = 0; l < PACK; ++l) S[l] += (double)lane(acc, l);
-        };
-        if (NOISE == NOISE_TENSOR) {
-            mbar_wait(bar, phase);
-            phase ^= 1u;
-            int t = 0;
-            for (; t + CH <= H; t += CH) {
-                V acc = V((R)0);
-#pragma unroll
-                for (int i = 0; i < CH; ++i) one(t + i, load_lanes(col + (size_t)(t + i) * TS, (V *)nullptr), acc);
-                fold(acc);
-            }
-            for (; t < H; ++t) {
-                V acc = V((R)0);
-                one(t, load_lanes(col + (size_t)t * TS, (V *)nullptr), acc);
-                fold(acc);
-            }
-        } else {
-            // same chunking of the float32 cost sums as the tensor path (CH divides 4), so both noise modes give
-            // bit-identical costs for identical noise values
-            static_assert(4 % CH == 0, "CHUNK must divide the Philox group of 4 steps");
-            const R sig = (R)a.sigma;
-            for (int t4 = 0; t4 < H; t4 += 4) {
-                float z[PACK][4];
-#pragma unroll
-                for (int l = 0; l < PACK; ++l)
-                    philox_normal4(a.seed, 0u, a.draw, (uint32_t)(a.g.k_begin + kl + l), (uint32_t)(t4 >> 2), z[l]);
-                auto noise_at = [&](int i, int t) {
-                    R el[PACK];
-#pragma unroll
-                    for (int l = 0; l < PACK; ++l) {
-                        el[l] = sig * (R)z[l][i];
-                        tile[(size_t)t * TS + tid * PACK + l] = el[l];
-                    }
-                    if constexpr (PACK == 2)
-                        return V(el[0], el[PACK - 1]);
-                    else
-                        return V(el[0]);
-                };
-#pragma unroll
-                for (int c0 = 0; c0 < 4; c0 += CH) {
-                    const int t = t4 + c0;
-                    if (t + CH <= H) {
-                        V acc = V((R)0);
-#pragma unroll
-                        for (int i = 0; i < CH; ++i) one(t + i, noise_at(c0 + i, t + i), acc);
-                        fold(acc);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < CH; ++i) {
-                            if (t + i < H) {
-                                V acc = V((R)0);
-                                one(t + i, noise_at(c0 + i, t + i), acc);
-                                fold(acc);
-                            }
-                        }
-                    }
-                }
-            }
-        }
-        double Smin = INFINITY;
-#pragma unroll
-        for (int l = 0; l < PACK; ++l) {
-            const bool valid = kl + l < a.g.K_local;
-            if (!valid) S[l] = INFINITY;
-            if (valid) S_out[(size_t)b * a.g.Kpad + kl + l] = S[l];
-            Smin = fmin(Smin, S[l]);
-        }
-        // ---- online softmin: rescale the running sums to the new minimum (mppi.py:59-62) ------------------
-        const double beta_tile = block_reduce<true>(Smin, red);
-        const double beta_new = fmin(beta_run, beta_tile);
-        const double scale_old = (eta_run == 0.0) ? 0.0 : exp(a.neg_inv_lam * (beta_run - beta_new));
-        double wsum = 0.0;
-#pragma unroll
-        for (int l = 0; l < PACK; ++l) {
-            const double w = (S[l] == INFINITY) ? 0.0 : exp(a.neg_inv_lam * (S[l] - beta_new));
-            sw[tid * PACK + l] = (R)w;
-            wsum += w;
-        }
-        const double eta_tile = block_reduce<false>(wsum, red);  // its barriers also publish sw and the Philox tile
-        eta_run = eta_run * scale_old + eta_tile;
-        beta_run = beta_new;
-        // ---- E[t] += sum_k w_k eps[k][t]: item (part, t) = row t, k in [part*KP, (part+1)*KP) ------------------
-        for (int w = tid; w < items; w += NT) {
-            const int p = w / H, t = w - p * H;
-            const double acc = dot_row(tile + (size_t)t * TS + p * KP, sw + p * KP, KP);
-            sE[w] = sE[w] * scale_old + acc;
-        }
-    }
-    flush();
-}
-
-// ================================================================================================ MPPI finalize
-// One block of FIN_THREADS per solve.  src records [count][2+H] -> (beta, eta, E).  STAGE 0/2 apply, STAGE 1 writes a
-// rank record.  The merge is latency-bound (count x H doubles scattered over L2), so it is spread over all warps:
-// warp w owns records j = w, w + nw, ... (eight loads in flight per thread), lanes own time steps; the per-warp
-// sums meet in shared memory in a fixed order, so repeated solves are bit-identical.
-constexpr int FIN_THREADS = 1024;
-template <class Env>
-__global__ void __launch_bounds__(FIN_THREADS) mppi_finalize_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec,
-                                                                    const int stage, const double *__restrict__ part,
-                                                                    double *__restrict__ rank_part,
-                                                                    const double *__restrict__ x0g,
-                                                                    const double *__restrict__ g_z,
-                                                                    double *__restrict__ Ug, double *__restrict__ out) {
-    constexpr int NS = Env::NS, NZ = Env::NS + 1;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int H = a.g.H, b = blockIdx.x, tid = threadIdx.x;
-    const int lane = tid & 31, w = tid >> 5, nw = FIN_THREADS / 32;
-    const int rec_len = PART_HDR + H;
-    __shared__ double red[FIN_THREADS / 32];
-    const int cap = (stage == 2) ? a.world : a.g.max_parts;
-    double *sscale = reinterpret_cast<double *>(smem_raw);  // [cap]
-    double *sUc = sscale + cap;                             // [H] clipped plan
-    double *sE = sUc + H;                                   // [nw][H] per-warp sums
-
-    const double *src;
-    int count;
-    size_t stride;  // between records of the same solve
-    if (stage == 2) {
-        src = rank_part + (size_t)b * rec_len;
-        count = a.world;
-        stride = (size_t)a.g.B * rec_len;
-    } else {
-        const int first = (int)(((long long)b * a.g.tiles_per_solve) / a.g.chunk);
-        const int last = (int)((((long long)(b + 1)) * a.g.tiles_per_solve - 1) / a.g.chunk);
-        count = last - first + 1;
-        src = part + (size_t)b * a.g.max_parts * rec_len;
-        stride = rec_len;
-    }
-    double m = INFINITY;
-    for (int j = tid; j < count; j += FIN_THREADS) m = fmin(m, src[j * stride]);
-    const double beta = block_reduce<true>(m, red);
-    double es = 0.0;
-    for (int j = tid; j < count; j += FIN_THREADS) {
-        const double bj = src[j * stride];
-        const double sc = (bj == INFINITY) ? 0.0 : exp(a.neg_inv_lam * (bj - beta));
-        sscale[j] = sc;
-        es += sc * src[j * stride + 1];
-    }
-    const double eta = block_reduce<false>(es, red);  // barriers publish sscale
-    for (int t0 = 0; t0 < H; t0 += 32) {
-        const int t = t0 + lane;
-        double e[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) e[i] = 0.0;
-        if (t < H) {
-            const double *col = src + PART_HDR + t;
-            int j = w;
-            for (; j + 7 * nw < count; j += 8 * nw) {
-                double v[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = col[(size_t)(j + i * nw) * stride];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) e[i] += sscale[j + i * nw] * v[i];
-            }
-            for (; j < count; j += nw) e[0] += sscale[j] * col[(size_t)j * stride];
-            sE[w * H + t] = ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
-        }
-    }
-    __syncthreads();
-    double *U = Ug + (size_t)b * H;
-    double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
-    for (int t = tid; t < H; t += FIN_THREADS) {
-        double E = 0.0;
-        for (int i = 0; i < nw; ++i) E += sE[i * H + t];
-        if (stage == 1) {
-            rank_part[((size_t)a.rank * a.g.B + b) * rec_len + PART_HDR + t] = E;
-        } else {
-            const double un = U[t] + (1.0 / eta) * E;  // w = (1/eta)*tmp ; planned_us += erg   mppi.py:62,69
-            U[t] = un;
-            o[1 + t] = un;
-            sUc[t] = fmin(fmax(un, a.lo), a.hi);  // agent.py:64-65
-        }
-    }
-    if (stage == 1) {
-        if (tid == 0) {
-            double *rec = rank_part + ((size_t)a.rank * a.g.B + b) * rec_len;
-            rec[0] = beta;
-            rec[1] = eta;
-        }
-        return;
-    }
-    __syncthreads();
-    if (tid == 0) {
-        o[0] = U[0];  // u0 = planned_us[0]  (mppi.py:71)
-        if (a.want_traj) {
-            o[1 + H] = nominal_rollout<Env>(ec, H, x0g + (size_t)b * NS, sUc, g_z + (size_t)b * H * NZ, o + 2 + H);
-        }
-    }
-}
+}  // namespace mpc
+#include "mppi.cuh"
+namespace mpc {
 
 // ================================================================================================ noise utilities
 // [K_local][H] float64 (reference layout, du = 1) -> [H][Kpad] in the rollout dtype, padding zero-filled.
@@ -612,16 +290,19 @@ __global__ void cem_finish_kernel(const CemArgs a, const EnvConst<typename Env::
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double *sUc = reinterpret_cast<double *>(smem_raw);
     const int H = a.g.H;
+    double *sG = sUc + H;  // [H][NS + 1]
     for (int t = threadIdx.x; t < H; t += blockDim.x) {
         out[1 + t] = mu[t];
         sUc[t] = fmin(fmax(mu[t], a.lo), a.hi);
     }
+    if (a.want_traj)
+        for (int i = threadIdx.x; i < H * (NS + 1); i += blockDim.x) sG[i] = g_z[i];
     __syncthreads();
     if (threadIdx.x == 0) {
         out[0] = mu[0];
         out[2 + H + (H + 1) * NS] = (double)sel[SEL_ITERS];
         if (a.want_traj) {
-            out[1 + H] = nominal_rollout<Env>(ec, H, x0g, sUc, g_z, out + 2 + H);
+            out[1 + H] = nominal_rollout<Env>(ec, H, x0g, sUc, sG, NS + 1, out + 2 + H);
         }
     }
 }
@@ -633,10 +314,12 @@ __global__ void simulate_kernel(const EnvConst<typename Env::Vec> ec, int H, dou
                                 const double *__restrict__ g_z, double *__restrict__ xs, double *__restrict__ cost) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double *sU = reinterpret_cast<double *>(smem_raw);
+    double *sG = sU + H;  // [H][NS + 1]
     for (int t = threadIdx.x; t < H; t += blockDim.x) sU[t] = do_clip ? fmin(fmax(us[t], lo), hi) : us[t];
+    for (int i = threadIdx.x; i < H * (Env::NS + 1); i += blockDim.x) sG[i] = g_z[i];
     __syncthreads();
     if (threadIdx.x == 0) {
-        *cost = nominal_rollout<Env>(ec, H, x0, sU, g_z, xs);
+        *cost = nominal_rollout<Env>(ec, H, x0, sU, sG, Env::NS + 1, xs);
     }
 }
 
@@ -739,75 +422,75 @@ static void with_scalar_env(int env, bool fast, F &&f) {
 }
 
 template <class Env, int NOISE>
-static cudaError_t mppi_rollout_go(const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b, cudaStream_t s) {
+static cudaError_t mppi_solve_go(const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b, cudaStream_t s) {
     typedef typename Env::Vec V;
-    auto kern = mppi_rollout_kernel<Env, NOISE>;
-    const size_t smem = RolloutSmem<R_>::total(a.g.H, a.g.parts);
+    auto kern = mppi_solve_kernel<Env, NOISE>;
+    const size_t smem = a.g.smem_rollout;
     static size_t smem_set = 0;  // per instantiation: raise the dynamic shared memory limit only when it grows
     if (smem > smem_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         smem_set = smem;
     }
-    kern<<<a.g.grid, TILE / VT<V>::N, smem, s>>>(a, make_env<V>(ep), (const R_ *)b.noise, b.x0, b.g_z, b.U, b.S, b.part);
+    CUtensorMap map;
+    if (b.noise_map)
+        memcpy(&map, b.noise_map, sizeof map);
+    else
+        memset(&map, 0, sizeof map);  // PHILOX: never dereferenced
+    kern<<<a.g.grid, a.g.warps * 32, smem, s>>>(a, make_env<V>(ep), map, b.x0, b.g_z, b.U, b.S, b.part, b.rank_part,
+                                                 b.out, b.done_count);
     return cudaGetLastError();
 }
 
-template <class Env, int NOISE>
-static int mppi_rollout_occ(int H, int parts) {
-    auto kern = mppi_rollout_kernel<Env, NOISE>;
-    const size_t smem = RolloutSmem<R_>::total(H, parts);
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
-    int occ = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, TILE / VT<typename Env::Vec>::N, smem) != cudaSuccess)
-        return 0;
-    return occ;
+// shared-memory bytes of the solve kernel: ring (S stages, W warps) or the tail arena, whichever is larger
+template <typename V>
+static size_t mppi_smem_bytes(int H, int S, int W, int cap, int G, int nz) {
+    const size_t ring = RingSmem<V>::ring_total(H, S, W), tail = RingSmem<V>::tail_total(H, W, cap, G, nz);
+    return ring > tail ? ring : tail;
 }
 
-size_t FN(mppi_rollout_smem)(int H, int parts) { return RolloutSmem<R_>::total(H, parts); }
+size_t FN(mppi_solve_smem)(int variant, int H, int S, int W, int cap, int G, int nz) {
+    if constexpr (std::is_same<R_, double>::value)
+        return mppi_smem_bytes<double>(H, S, W, cap, G, nz);
+    else
+        return (variant & VAR_PACK2) ? mppi_smem_bytes<f2>(H, S, W, cap, G, nz) : mppi_smem_bytes<float>(H, S, W, cap, G, nz);
+}
 
-cudaError_t FN(launch_mppi_rollout)(int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
-                                    const MppiBuffers &b, cudaStream_t s) {
+size_t FN(mppi_stage_bytes)(int variant, int H) {
+    if constexpr (std::is_same<R_, double>::value)
+        return RingSmem<double>::stage_bytes(H);
+    else
+        return (variant & VAR_PACK2) ? RingSmem<f2>::stage_bytes(H) : RingSmem<float>::stage_bytes(H);
+}
+
+cudaError_t FN(launch_mppi_solve)(int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
+                                  const MppiBuffers &b, cudaStream_t s) {
     cudaError_t e = cudaSuccess;
     with_rollout_env(ep.env, variant, [&](auto env) {
         typedef decltype(env) E;
-        e = (noise == NOISE_TENSOR) ? mppi_rollout_go<E, NOISE_TENSOR>(a, ep, b, s)
-                                    : mppi_rollout_go<E, NOISE_PHILOX>(a, ep, b, s);
+        e = (noise == NOISE_TENSOR) ? mppi_solve_go<E, NOISE_TENSOR>(a, ep, b, s)
+                                    : mppi_solve_go<E, NOISE_PHILOX>(a, ep, b, s);
     });
     return e;
 }
 
-int FN(mppi_rollout_occupancy)(int noise, int variant, int env, int H, int parts) {
-    int occ = 0;
-    with_rollout_env(env, variant, [&](auto e) {
-        typedef decltype(e) E;
-        occ = (noise == NOISE_TENSOR) ? mppi_rollout_occ<E, NOISE_TENSOR>(H, parts)
-                                      : mppi_rollout_occ<E, NOISE_PHILOX>(H, parts);
-    });
-    return occ;
-}
-
-template <class Env>
-static cudaError_t mppi_finalize_go(int stage, const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b,
-                                    cudaStream_t s) {
-    auto kern = mppi_finalize_kernel<Env>;
-    const int cap = (stage == 2) ? a.world : a.g.max_parts;
-    const size_t smem = ((size_t)cap + a.g.H + (size_t)(FIN_THREADS / 32) * a.g.H) * sizeof(double);
-    static size_t smem_set = 48 * 1024;
-    if (smem > smem_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        smem_set = smem;
-    }
-    kern<<<a.g.B, FIN_THREADS, smem, s>>>(a, make_env<typename Env::Vec>(ep), stage, b.part, b.rank_part, b.x0, b.g_z,
-                                          b.U, b.out);
-    return cudaGetLastError();
-}
-
-cudaError_t FN(launch_mppi_finalize)(int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
-                                     cudaStream_t s) {
+cudaError_t FN(launch_mppi_rank_merge)(const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                       cudaStream_t s) {
     cudaError_t e = cudaSuccess;
-    with_scalar_env(ep.env, false, [&](auto env) { e = mppi_finalize_go<decltype(env)>(stage, a, ep, b, s); });
+    with_scalar_env(ep.env, false, [&](auto env) {
+        typedef decltype(env) E;
+        auto kern = mppi_rank_merge_kernel<E>;
+        const int H = a.g.H, nw = 256 / 32;
+        const size_t smem = ((size_t)a.world + H + (size_t)H * (a.g.ns + 1) + (size_t)nw * H + H) * sizeof(double);
+        static size_t smem_set = 48 * 1024;
+        if (smem > smem_set) {
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return;
+            smem_set = smem;
+        }
+        kern<<<a.g.B, 256, smem, s>>>(a, make_env<typename E::Vec>(ep), b.rank_part, b.x0, b.g_z, b.U, b.out);
+        e = cudaGetLastError();
+    });
     return e;
 }
 
@@ -826,7 +509,7 @@ cudaError_t FN(launch_philox_fill)(void *dst, int K_local, int k_begin, int Kpad
 cudaError_t FN(launch_cem_rollout)(int noise, int variant, const EnvParamsHost &ep, const CemArgs &a,
                                    const CemBuffers &b, cudaStream_t s) {
     const size_t smem = 2 * (size_t)a.g.H * sizeof(double);
-    const int grid = a.g.tiles_per_solve;
+    const int grid = a.g.Kpad / TILE;
     with_scalar_env(ep.env, (variant & VAR_FAST) != 0, [&](auto env) {
         typedef decltype(env) E;
         typedef typename E::Vec V;
@@ -849,7 +532,7 @@ cudaError_t FN(launch_cem_refit)(int noise, const CemArgs &a, const CemBuffers &
 }
 
 cudaError_t FN(launch_cem_finish)(const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
-    const size_t smem = (size_t)a.g.H * sizeof(double);
+    const size_t smem = (size_t)a.g.H * (2 + a.g.ns) * sizeof(double);
     with_scalar_env(ep.env, false, [&](auto env) {
         typedef decltype(env) E;
         cem_finish_kernel<E><<<1, 128, smem, s>>>(a, make_env<typename E::Vec>(ep), b.x0, b.g_z, b.mu, b.sel, b.out);
@@ -859,7 +542,7 @@ cudaError_t FN(launch_cem_finish)(const EnvParamsHost &ep, const CemArgs &a, con
 
 cudaError_t FN(launch_simulate)(const EnvParamsHost &ep, int H, double lo, double hi, int do_clip, const double *x0,
                                 const double *us, const double *g_z, double *xs, double *cost, cudaStream_t s) {
-    const size_t smem = (size_t)H * sizeof(double);
+    const size_t smem = (size_t)H * 6 * sizeof(double);
     with_scalar_env(ep.env, false, [&](auto env) {
         typedef decltype(env) E;
         simulate_kernel<E><<<1, 64, smem, s>>>(make_env<typename E::Vec>(ep), H, lo, hi, do_clip, x0, us, g_z, xs, cost);

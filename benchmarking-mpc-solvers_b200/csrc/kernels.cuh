@@ -5,7 +5,7 @@
 
 namespace mpc {
 
-constexpr int TILE = 128;       // samples per noise tile; rollout block = TILE / (samples per thread) threads
+constexpr int TILE = 128;       // padding unit of K (row stride of the noise tensor) and CEM block size
 constexpr int PART_HDR = 2;     // partial record = [beta, eta, E[0..H-1]]
 
 enum { NOISE_TENSOR = 0, NOISE_PHILOX = 1 };
@@ -17,22 +17,27 @@ struct EnvParamsHost {
     double f[24];  // folded constants, float32 throughput layout (narrowed when the kernel is launched)
 };
 
-// Geometry of one handle's shard; identical for every solve.
+// Geometry of one handle's shard; identical for every solve.  MPPI tiles are WARP tiles of wt samples (mppi.cuh).
 struct Geometry {
     int K_local;          // samples of each solve owned by this handle
     int k_begin;          // global index of the first one
     int Kpad;             // K_local rounded up to a multiple of TILE (row stride of the noise tensor)
     int H;
     int B;                // batch of independent solves
-    int tiles_per_solve;  // Kpad / TILE
+    int wt;               // samples per warp tile: 32 lanes x samples per thread
+    int tiles_per_solve;  // Kpad / wt
     int total_tiles;      // B * tiles_per_solve
-    int chunk;            // consecutive tiles per rollout block
-    int grid;             // rollout blocks = ceil(total_tiles / chunk)
-    int max_parts;        // partial records per solve (blocks that can overlap one solve)
-    int parts;            // k-range splits of the weighted-sum pass (power of two <= 8)
+    int warps;            // W: warps per solve-kernel block
+    int stages;           // S: shared-memory ring stages (S >= W; S - W tiles prefetched ahead)
+    int solves_per_block; // 0 = mode A (a solve is shared by blocks_per_solve blocks); > 0 = mode B (whole solves)
+    int blocks_per_solve; // mode A
+    int chunk;            // mode A: consecutive tiles per block
+    int grid;             // solve-kernel blocks
+    int max_parts;        // partial records per solve: blocks_per_solve (A) or warps (B)
+    int fin_group;        // mode B: solves finalised together (one thread per nominal rollout)
     int variant;          // rollout flavour: bit 0 fast_math (MUFU trig), bit 1 two samples per thread (f32x2)
     int ns;
-    size_t smem_rollout;  // dynamic shared memory of the rollout kernel
+    size_t smem_rollout;  // dynamic shared memory of the solve kernel
 };
 
 struct MppiArgs {
@@ -44,8 +49,10 @@ struct MppiArgs {
     uint64_t seed;
     uint32_t draw;        // Philox draw index
     int noise_batched;    // TENSOR: 1 = one tensor per solve of the batch, 0 = shared
-    int want_traj;        // compute the clipped nominal rollout in the finalize kernel
-    int world;            // >1: finalize writes a rank partial instead of applying
+    int want_traj;        // compute the clipped plan's nominal rollout in the tail of the solve kernel
+    int goal_zero;        // the goal trajectory is all zeros (what every reference script passes)
+    int record_only;      // the tail publishes this rank's (beta, eta, E) record instead of applying it
+    int world;            // ranks whose records the final merge combines
     int rank;
 };
 
@@ -60,6 +67,7 @@ struct CemArgs {
 
 struct MppiBuffers {
     const void *noise;     // R [Bn][H][Kpad]
+    const void *noise_map; // host copy of the CUtensorMap over `noise` (rank 3: Kpad, H, Bn; box wt x H x 1)
     const double *x0;      // [B][ns]
     const double *g_z;     // [B][H][nz]
     double *U;             // [B][H]   device-resident plan (in: before, out: after)
@@ -67,6 +75,7 @@ struct MppiBuffers {
     double *part;          // [B][max_parts][2+H]
     double *rank_part;     // [world][B][2+H]  (all-gather buffer; this rank writes slot `rank`)
     double *out;           // [B][out_stride]: u0, U[H], cost, xs[(H+1)*ns]
+    int *done_count;       // [B] arrival tickets of the solve kernel's blocks (self-cleaning)
 };
 
 struct CemBuffers {
@@ -83,13 +92,12 @@ struct CemBuffers {
 };
 
 // launches (kernels.cu); all return cudaGetLastError()
-cudaError_t launch_mppi_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
-                                cudaStream_t s);
-// stage: 0 = single GPU (merge block partials, apply, nominal rollout)
-//        1 = multi GPU first half  (merge block partials -> rank_part[rank])
-//        2 = multi GPU second half (merge rank partials, apply, nominal rollout)
-cudaError_t launch_mppi_finalize(int dtype, int stage, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
-                                 cudaStream_t s);
+// the whole solve (rollout + softmin update + plan update + nominal rollout); world > 1: up to this rank's record
+cudaError_t launch_mppi_solve(int dtype, int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
+                              const MppiBuffers &b, cudaStream_t s);
+// multi GPU second half: merge the gathered rank records, apply, nominal rollout
+cudaError_t launch_mppi_rank_merge(int dtype, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
+                                   cudaStream_t s);
 cudaError_t launch_transpose_noise(int dtype, const double *src_KH, void *dst_HK, int K_local, int Kpad, int H,
                                    cudaStream_t s);
 cudaError_t launch_philox_fill(int dtype, void *dst_HK, int K_local, int k_begin, int Kpad, int H, double scale,
@@ -110,7 +118,9 @@ cudaError_t launch_model_step(int dtype, const EnvParamsHost &ep, int n, const d
 cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaStream_t s);
 cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s);
 
-size_t mppi_rollout_smem(int dtype, int H, int parts);
-int mppi_rollout_occupancy(int dtype, int noise, int variant, int env, int H, int parts);
+size_t mppi_solve_smem(int dtype, int variant, int H, int S, int W, int cap, int G, int nz);
+size_t mppi_stage_bytes(int dtype, int variant, int H);
+constexpr int MPPI_MAX_WARPS = 16;   // == MAX_WARPS in mppi.cuh
+constexpr int MPPI_MAX_H = 256;      // 32 * MAX_ROWS
 
 }  // namespace mpc

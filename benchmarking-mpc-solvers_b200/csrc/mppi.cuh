@@ -1,0 +1,573 @@
+// mppi.cuh — the MPPI solve as ONE persistent sm_100a kernel (included by kernels.cu, compiled per dtype).
+//
+//   MPPI.f for every sample (mppi.py:35-48)  +  softmin weights and weighted noise sum (mppi.py:59-67)
+//   +  planned_us += erg (mppi.py:69)  +  the clipped plan's nominal rollout (agent.py:64-69,97-108)
+//
+// Shape: one block per SM, W warps, a ring of S shared-memory stages.  A stage holds the [H][WT] noise tile of one
+// WARP (WT = 32 lanes x PACK samples, dense rows of 128/256 B), filled by ONE TMA tensor copy
+// (cp.async.bulk.tensor.3d, box [H][WT] of the [H][Kpad] noise tensor) that completes on the stage's mbarrier.  Tile j of the block goes to warp j % W and stage j % S; the warp that finishes a tile
+// re-arms its stage with tile j + S, so S - W tiles are always in flight ahead of the consumers and no warp ever
+// waits on another warp: there is NO block barrier inside the tile loop.  Everything per tile is warp-local:
+//   rollout (state in registers, noise read from the stage) -> warp-shuffle min -> softmin weights -> the weighted
+//   sum sum_k w_k eps[k][t] from the SAME stage (the noise tensor is read from HBM once per solve), accumulated in
+//   registers with the running-minimum rescaling (lane owns rows t = lane, lane + 32, ...).
+// Tail: the warps' (beta, eta, E[H]) records meet in shared memory, one record per block goes to global memory and
+// the last block to arrive (atomic ticket per solve) merges them, updates the plan and rolls out the nominal
+// trajectory — no second launch.  With many small solves per launch (batch) a block owns whole solves, keeps
+// per-warp records and finalises its solves itself, one thread per nominal rollout.
+#pragma once
+
+namespace mpc {
+
+constexpr int MAX_WARPS = 16;   // warps per rollout block
+constexpr int MAX_ROWS = 8;     // time-step rows per lane in the weighted sum: H <= 32 * MAX_ROWS
+
+template <typename V>
+struct WarpTile {
+    typedef typename VT<V>::S R;
+    static constexpr int PACK = VT<V>::N;
+    static constexpr int WT = 32 * PACK;                 // samples per warp tile
+    static constexpr int CE = 16 / sizeof(R);            // elements per 16-byte chunk
+    static constexpr int NCHUNK = WT / CE;               // chunks per row (power of two)
+};
+
+// Shared-memory layout of the tile loop.  The tail reuses the arena from offset 0 after a block barrier.
+template <typename V>
+struct RingSmem {
+    typedef typename VT<V>::S R;
+    static constexpr int WT = WarpTile<V>::WT;
+    static __host__ __device__ size_t a16(size_t b) { return (b + 15) / 16 * 16; }
+    static __host__ __device__ size_t stage_bytes(int H) { return (size_t)H * WT * sizeof(R); }
+    static __host__ __device__ size_t off_sU(int H, int S) { return S * stage_bytes(H); }
+    static __host__ __device__ size_t off_sw(int H, int S, int W) { return off_sU(H, S) + a16((size_t)W * H * sizeof(R)); }
+    static __host__ __device__ size_t off_bar(int H, int S, int W) { return off_sw(H, S, W) + (size_t)W * WT * sizeof(R); }
+    static __host__ __device__ size_t off_gen(int H, int S, int W) { return off_bar(H, S, W) + (size_t)S * 8; }
+    static __host__ __device__ size_t ring_total(int H, int S, int W) { return off_gen(H, S, W) + (size_t)S * 4 + 16; }
+    // tail arena (doubles): warp records [W][2+H] | scale[cap] | clipped plans [G][H] | goals [G][H*NZ] | warp sums
+    // [W][H] ; G = solves finalised together
+    static __host__ __device__ size_t tail_total(int H, int W, int cap, int G, int nz) {
+        return ((size_t)W * (PART_HDR + H) + cap + (size_t)G * H + (size_t)G * H * nz + (size_t)W * H + H + 64) * sizeof(double);
+    }
+};
+
+// sum_k w[k] * row[k] over one dense row of WT elements, 16-byte chunks visited in an order rotated by the lane so
+// that the eight lanes of a quarter warp (eight different rows, same bank offset) hit eight different bank groups
+__device__ __forceinline__ double dot_row_rot(const float *row, const float *w, int lane, f2 *) {
+    f2 a0(0.f), a1(0.f);
+#pragma unroll
+    for (int it = 0; it < 16; ++it) {
+        const int c = ((it + lane) & 15) * 4;
+        const float4 e = *reinterpret_cast<const float4 *>(row + c);
+        const float4 q = *reinterpret_cast<const float4 *>(w + c);
+        a0 = vfma(f2(q.x, q.y), f2(e.x, e.y), a0);
+        a1 = vfma(f2(q.z, q.w), f2(e.z, e.w), a1);
+    }
+    const f2 a = a0 + a1;
+    return (double)(a.v.x + a.v.y);
+}
+__device__ __forceinline__ double dot_row_rot(const float *row, const float *w, int lane, float *) {
+    f2 a0(0.f), a1(0.f);
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int c = ((it + lane) & 7) * 4;
+        const float4 e = *reinterpret_cast<const float4 *>(row + c);
+        const float4 q = *reinterpret_cast<const float4 *>(w + c);
+        a0 = vfma(f2(q.x, q.y), f2(e.x, e.y), a0);
+        a1 = vfma(f2(q.z, q.w), f2(e.z, e.w), a1);
+    }
+    const f2 a = a0 + a1;
+    return (double)(a.v.x + a.v.y);
+}
+__device__ __forceinline__ double dot_row_rot(const double *row, const double *w, int lane, double *) {
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+    for (int it = 0; it < 16; ++it) {
+        const int c = ((it + lane) & 15) * 2;
+        const double2 e = *reinterpret_cast<const double2 *>(row + c);
+        const double2 q = *reinterpret_cast<const double2 *>(w + c);
+        a0 = fma(q.x, e.x, a0);
+        a1 = fma(q.y, e.y, a1);
+    }
+    return a0 + a1;
+}
+
+// softmin scale of a record with minimum bj relative to the merged minimum beta (empty records carry +inf)
+__device__ __forceinline__ double rec_scale(double neg_inv_lam, double bj, double beta) {
+    return (bj == INFINITY) ? 0.0 : exp(neg_inv_lam * (bj - beta));
+}
+
+// ------------------------------------------------------------------------------------------------ record merging
+// Block-wide merge of `count` records (beta_j, eta_j, E_j[H]) at src + j * stride: beta = min beta_j,
+// eta = sum s_j eta_j, Eout[t] = sum s_j E_j[t] with s_j = exp(-(beta_j - beta)/lam).  The records were written by
+// other blocks (or ranks): they are read through L2 (__ldcg).  Warp w owns records j = w, w + nw, ... (eight loads in
+// flight per thread), lanes own time steps; the per-warp sums meet in shared memory in a fixed order, so repeated
+// solves are bit-identical.  Scratch: sscale[count], sEw[nw][H], red[32].  All threads return beta / eta.
+__device__ __forceinline__ void block_merge(const double neg_inv_lam, const int H, const double *src, const int count,
+                                            const size_t stride, double *sscale, double *sEw, double *red,
+                                            double *Eout, double *beta_out, double *eta_out) {
+    const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, w = tid >> 5, nw = nt >> 5;
+    double m = INFINITY;
+    for (int j = tid; j < count; j += nt) m = fmin(m, __ldcg(src + j * stride));
+    const double beta = block_reduce<true>(m, red);
+    double es = 0.0;
+    for (int j = tid; j < count; j += nt) {
+        const double sc = rec_scale(neg_inv_lam, __ldcg(src + j * stride), beta);
+        sscale[j] = sc;
+        es += sc * __ldcg(src + j * stride + 1);
+    }
+    const double eta = block_reduce<false>(es, red);  // its barriers publish sscale
+    for (int t0 = 0; t0 < H; t0 += 32) {
+        const int t = t0 + lane;
+        double e[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) e[i] = 0.0;
+        if (t < H) {
+            const double *col = src + PART_HDR + t;
+            int j = w;
+            for (; j + 7 * nw < count; j += 8 * nw) {
+                double v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = __ldcg(col + (size_t)(j + i * nw) * stride);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) e[i] += sscale[j + i * nw] * v[i];
+            }
+            for (; j < count; j += nw) e[0] += sscale[j] * __ldcg(col + (size_t)j * stride);
+            sEw[w * H + t] = ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
+        }
+    }
+    __syncthreads();
+    for (int t = tid; t < H; t += nt) {
+        double E = 0.0;
+        for (int i = 0; i < nw; ++i) E += sEw[i * H + t];
+        Eout[t] = E;
+    }
+    __syncthreads();
+    *beta_out = beta;
+    *eta_out = eta;
+}
+
+// What follows the merge of one solve, by the whole block.  record_only (multi-GPU) and !final: publish this rank's record
+// (the exchange and the final merge follow); otherwise planned_us += erg (mppi.py:62,69), clip (agent.py:64-65),
+// outputs, and the nominal rollout of the clipped plan by thread 0 from shared memory (agent.py:97-108).
+// Scratch: sUc[H], sG[H * NZ] (only touched for a non-zero goal), zero[NZ].
+template <class Env>
+__device__ __forceinline__ void block_apply(const MppiArgs &a, const EnvConst<typename Env::Vec> &ec, const int b,
+                                            const bool final_stage, const double beta, const double eta,
+                                            const double *Eout, double *rank_part, const double *x0g,
+                                            const double *g_z, double *Ug, double *out, double *sUc, double *sG) {
+    constexpr int NS = Env::NS, NZ = Env::NS + 1;
+    const int H = a.g.H, tid = threadIdx.x, nt = blockDim.x, rec_len = PART_HDR + H;
+    if (a.record_only && !final_stage) {
+        double *rec = rank_part + ((size_t)a.rank * a.g.B + b) * rec_len;
+        for (int t = tid; t < H; t += nt) rec[PART_HDR + t] = Eout[t];
+        if (tid == 0) {
+            rec[0] = beta;
+            rec[1] = eta;
+        }
+        return;
+    }
+    double *U = Ug + (size_t)b * H;
+    double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
+    const double inv_eta = 1.0 / eta;
+    for (int t = tid; t < H; t += nt) {
+        const double un = U[t] + inv_eta * Eout[t];  // w = (1/eta)*tmp ; planned_us += erg   mppi.py:62,69
+        U[t] = un;
+        o[1 + t] = un;
+        if (t == 0) o[0] = un;                       // u0 = planned_us[0]  (mppi.py:71)
+        sUc[t] = fmin(fmax(un, a.lo), a.hi);         // agent.py:64-65
+    }
+    if (a.want_traj && !a.goal_zero)
+        for (int i = tid; i < H * NZ; i += nt) sG[i] = g_z[(size_t)b * H * NZ + i];
+    if (a.want_traj && a.goal_zero && tid < NZ) sG[tid] = 0.0;
+    __syncthreads();
+    if (tid == 0 && a.want_traj)
+        o[1 + H] = nominal_rollout<typename Env::Scalar>(scalar_consts(ec), H, x0g + (size_t)b * NS, sUc, sG,
+                                                         a.goal_zero ? 0 : NZ, o + 2 + H);
+}
+
+// ================================================================================================ the solve kernel
+// Geometry (capi.cu): tiles are WARP tiles.  mode A (solves_per_block == 0): blocks_per_solve blocks share one solve,
+// block blk works on solve blk / blocks_per_solve.  mode B: a block owns solves_per_block whole solves.
+template <class Env, int NOISE>
+__global__ void __launch_bounds__(MAX_WARPS * 32, 1)
+    mppi_solve_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec,
+                      const __grid_constant__ CUtensorMap noise_map, const double *__restrict__ x0g, const double *__restrict__ g_z, double *__restrict__ Ug,
+                      double *__restrict__ S_out, double *__restrict__ part, double *__restrict__ rank_part,
+                      double *__restrict__ out, int *__restrict__ done_count) {
+    typedef typename Env::Vec V;
+    typedef typename Env::S R;
+    constexpr int NS = Env::NS, NZ = Env::NS + 1, NG = Env::NG, PACK = VT<V>::N, CH = Env::CHUNK;
+    constexpr int WT = WarpTile<V>::WT;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int H = a.g.H, W = blockDim.x >> 5, S = a.g.stages, tps = a.g.tiles_per_solve;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const size_t stage_elems = (size_t)H * WT;
+    R *stages = reinterpret_cast<R *>(smem_raw);
+    R *sU = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sU(H, S)) + (size_t)w * H;
+    R *sw = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sw(H, S, W)) + (size_t)w * WT;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + RingSmem<V>::off_bar(H, S, W));
+    // gen[st] = tile whose load the stage's mbarrier currently tracks.  An mbarrier carries one bit of phase: a
+    // warp that ran a whole ring turn ahead of a slow warp would see the parity of an OLDER completed phase and
+    // read a stale tile.  Waiting for gen[st] == j first makes the wait exact for any interleaving of the warps.
+    volatile int *gen = reinterpret_cast<volatile int *>(smem_raw + RingSmem<V>::off_gen(H, S, W));
+    const int rec_len = PART_HDR + H;
+
+    // ---- this block's tile range ----------------------------------------------------------------------------
+    int tile0, tile1, b_lo, b_hi;
+    if (a.g.solves_per_block == 0) {
+        b_lo = b_hi = blockIdx.x / a.g.blocks_per_solve;
+        const int part_idx = blockIdx.x - b_lo * a.g.blocks_per_solve;
+        tile0 = b_lo * tps + part_idx * a.g.chunk;
+        tile1 = min(tile0 + a.g.chunk, (b_lo + 1) * tps);
+    } else {
+        b_lo = blockIdx.x * a.g.solves_per_block;
+        b_hi = min(b_lo + a.g.solves_per_block, a.g.B) - 1;
+        tile0 = b_lo * tps;
+        tile1 = (b_hi + 1) * tps;
+    }
+
+    // one TMA tensor copy (box [H][WT] of the [Bn][H][Kpad] noise tensor) of tile j into its stage, by lane 0;
+    // callers have passed a __syncwarp after the warp's last read of the stage
+    auto issue = [&](int j) {
+        if (lane == 0) {
+            const int st = (j - tile0) % S;
+            const int b = j / tps, kt = j - b * tps;
+            mbar_expect_tx(&bars[st], (uint32_t)(stage_elems * sizeof(R)));
+            __threadfence_block();
+            gen[st] = j;
+            fence_proxy_async();  // generic-proxy reads of the stage precede the async-proxy writes
+            tma_load_3d(stages + st * stage_elems, &noise_map, kt * WT, 0, a.noise_batched ? b : 0, &bars[st]);
+        }
+    };
+
+    if (NOISE == NOISE_TENSOR) {
+        if (tid == 0) {
+            for (int i = 0; i < S; ++i) {
+                mbar_init(&bars[i], 1);
+                gen[i] = -1;
+            }
+            fence_mbar_init();
+        }
+        __syncthreads();
+        for (int i = w; i < S && tile0 + i < tile1; i += W) issue(tile0 + i);
+    }
+
+    // ---- per-warp running softmin state of the current solve; E rows lane, lane + 32, ... in registers ---------
+    int cur = b_lo;
+    double beta_run = INFINITY, eta_run = 0.0;
+    double E[MAX_ROWS];
+#pragma unroll
+    for (int i = 0; i < MAX_ROWS; ++i) E[i] = 0.0;
+    R gs[NG];
+    R xinit[NS];
+    const V pert = V((R)a.pert);
+
+    auto load_solve = [&](int b) {
+        __syncwarp();
+        for (int t = lane; t < H; t += 32) sU[t] = (R)Ug[(size_t)b * H + t];
+        Env::prep_goal(ec, g_z + (size_t)b * H * NZ, gs);  // goal row 0 (model.py:34,38)
+#pragma unroll
+        for (int i = 0; i < NS; ++i) xinit[i] = (R)x0g[(size_t)b * NS + i];
+        __syncwarp();
+    };
+    // mode B only: the warp's record of solve `cur` goes to global memory (slot = warp)
+    auto flush_global = [&]() {
+        double *rec = part + ((size_t)cur * a.g.max_parts + w) * rec_len;
+        if (lane == 0) {
+            rec[0] = beta_run;
+            rec[1] = eta_run;
+        }
+#pragma unroll
+        for (int i = 0; i < MAX_ROWS; ++i)
+            if (lane + 32 * i < H) rec[PART_HDR + lane + 32 * i] = E[i];
+        beta_run = INFINITY;
+        eta_run = 0.0;
+#pragma unroll
+        for (int i = 0; i < MAX_ROWS; ++i) E[i] = 0.0;
+    };
+    load_solve(cur);
+
+    for (int j = tile0 + w; j < tile1; j += W) {
+        const int b = j / tps, kt = j - b * tps;
+        while (cur < b) {  // mode B: every warp leaves a record (possibly empty) for every solve of the block
+            flush_global();
+            ++cur;
+            if (cur == b) load_solve(cur);
+        }
+        const int jr = j - tile0, st = jr % S;
+        R *tile = (NOISE == NOISE_TENSOR) ? stages + st * stage_elems : stages + w * stage_elems;
+        const int kl = kt * WT + lane * PACK;  // first local sample index of this lane
+        V x[NS];
+#pragma unroll
+        for (int i = 0; i < NS; ++i) x[i] = V(xinit[i]);
+        double Sk[PACK];
+#pragma unroll
+        for (int l = 0; l < PACK; ++l) Sk[l] = 0.0;
+        const R *col = tile + lane * PACK;
+        // one rollout step: u = U_t + eps (mppi.py:39), cost + step (mppi.py:43-44), lam * u * eps / sigma^2 (:45-46)
+        auto one = [&](int t, const V &e, V &acc) {
+            const V u = V(sU[t]) + e;
+            const V c = Env::step(ec, x, u, gs);
+            acc = acc + vfma(u * e, pert, c);
+        };
+        auto fold = [&](const V &acc) {
+#pragma unroll
+            for (int l = 0; l < PACK; ++l) Sk[l] += (double)lane_of(acc, l);
+        };
+        if (NOISE == NOISE_TENSOR) {
+            while (gen[st] != j) {
+            }
+            __threadfence_block();
+            mbar_wait(&bars[st], (uint32_t)((jr / S) & 1));
+            int t = 0;
+            for (; t + CH <= H; t += CH) {
+                V acc = V((R)0);
+#pragma unroll
+                for (int i = 0; i < CH; ++i) one(t + i, load_lanes(col + (size_t)(t + i) * WT, (V *)nullptr), acc);
+                fold(acc);
+            }
+            for (; t < H; ++t) {
+                V acc = V((R)0);
+                one(t, load_lanes(col + (size_t)t * WT, (V *)nullptr), acc);
+                fold(acc);
+            }
+        } else {
+            // same chunking of the float32 cost sums as the tensor path (CH divides 4), so both noise modes give
+            // bit-identical costs for identical noise values
+            static_assert(4 % CH == 0, "CHUNK must divide the Philox group of 4 steps");
+            const R sig = (R)a.sigma;
+            __syncwarp();  // the previous tile's weighted sum has finished reading this warp's buffer
+            for (int t4 = 0; t4 < H; t4 += 4) {
+                float z[PACK][4];
+#pragma unroll
+                for (int l = 0; l < PACK; ++l)
+                    philox_normal4(a.seed, 0u, a.draw, (uint32_t)(a.g.k_begin + kl + l), (uint32_t)(t4 >> 2), z[l]);
+                auto noise_at = [&](int i, int t) {
+                    R el[PACK];
+#pragma unroll
+                    for (int l = 0; l < PACK; ++l) {
+                        el[l] = sig * (R)z[l][i];
+                        tile[(size_t)t * WT + lane * PACK + l] = el[l];
+                    }
+                    if constexpr (PACK == 2)
+                        return V(el[0], el[PACK - 1]);
+                    else
+                        return V(el[0]);
+                };
+#pragma unroll
+                for (int c0 = 0; c0 < 4; c0 += CH) {
+                    const int t = t4 + c0;
+                    if (t + CH <= H) {
+                        V acc = V((R)0);
+#pragma unroll
+                        for (int i = 0; i < CH; ++i) one(t + i, noise_at(c0 + i, t + i), acc);
+                        fold(acc);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < CH; ++i) {
+                            if (t + i < H) {
+                                V acc = V((R)0);
+                                one(t + i, noise_at(c0 + i, t + i), acc);
+                                fold(acc);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        double Smin = INFINITY;
+#pragma unroll
+        for (int l = 0; l < PACK; ++l) {
+            const bool valid = kl + l < a.g.K_local;
+            if (!valid) Sk[l] = INFINITY;
+            Smin = fmin(Smin, Sk[l]);
+        }
+        if (PACK == 2) {
+            if (kl + 1 < a.g.K_local)
+                *reinterpret_cast<double2 *>(S_out + (size_t)b * a.g.Kpad + kl) = make_double2(Sk[0], Sk[PACK - 1]);
+            else if (kl < a.g.K_local)
+                S_out[(size_t)b * a.g.Kpad + kl] = Sk[0];
+        } else if (kl < a.g.K_local) {
+            S_out[(size_t)b * a.g.Kpad + kl] = Sk[0];
+        }
+        // ---- online softmin: rescale the running sums to the new minimum (mppi.py:59-62) ------------------------
+        const double beta_new = fmin(beta_run, warp_min(Smin));
+        const double scale_old = (eta_run == 0.0) ? 0.0 : exp(a.neg_inv_lam * (beta_run - beta_new));
+        double wsum = 0.0;
+        R wl[PACK];
+#pragma unroll
+        for (int l = 0; l < PACK; ++l) {
+            const double wk = (Sk[l] == INFINITY) ? 0.0 : exp(a.neg_inv_lam * (Sk[l] - beta_new));
+            wl[l] = (R)wk;
+            wsum += wk;
+        }
+        if constexpr (PACK == 2)
+            *reinterpret_cast<float2 *>(sw + lane * 2) = make_float2(wl[0], wl[PACK - 1]);
+        else
+            sw[lane] = wl[0];
+        eta_run = eta_run * scale_old + warp_sum(wsum);
+        beta_run = beta_new;
+        __syncwarp();  // weights (and the Philox tile) visible to the whole warp
+        // ---- E[t] += sum_k w_k eps[k][t], lane owns rows t = lane + 32 i -----------------------------------------
+#pragma unroll
+        for (int i = 0; i < MAX_ROWS; ++i) {
+            if (32 * i < H) {
+                const int r = lane + 32 * i;
+                double acc = 0.0;
+                if (r < H) acc = dot_row_rot(tile + (size_t)r * WT, sw, lane, (V *)nullptr);
+                E[i] = E[i] * scale_old + acc;
+            }
+        }
+        // ---- re-arm the stage with the tile S places ahead -------------------------------------------------------
+        if (NOISE == NOISE_TENSOR) {
+            __syncwarp();
+            if (j + S < tile1) issue(j + S);
+        }
+    }
+    if (a.g.solves_per_block != 0) {
+        while (cur <= b_hi) {
+            flush_global();
+            ++cur;
+        }
+    }
+
+    // ---- tail: every stage is free after this barrier; the arena is reused from offset 0 -------------------------
+    __syncthreads();
+    __shared__ double red[32];
+    __shared__ int s_last;
+    double *arena = reinterpret_cast<double *>(smem_raw);
+    const int nt = blockDim.x;
+    if (a.g.solves_per_block == 0) {
+        // mode A: warp records -> shared memory -> one block record in global memory -> ticket -> last block merges
+        const int b = b_lo, nb = a.g.blocks_per_solve, part_idx = blockIdx.x - b * nb;
+        double *wrec = arena;                      // [W][rec_len]
+        double *sscale = wrec + (size_t)W * rec_len;  // [max(W, nb)]
+        double *sUc = sscale + max(W, nb);         // [H]
+        double *sG = sUc + H;                      // [H * NZ]
+        double *sEw = sG + (size_t)H * NZ;         // [W][H]
+        double *Eout = sEw + (size_t)W * H;        // [H]
+        {
+            double *rec = wrec + (size_t)w * rec_len;
+            if (lane == 0) {
+                rec[0] = beta_run;
+                rec[1] = eta_run;
+            }
+#pragma unroll
+            for (int i = 0; i < MAX_ROWS; ++i)
+                if (lane + 32 * i < H) rec[PART_HDR + lane + 32 * i] = E[i];
+        }
+        __syncthreads();
+        double bb = INFINITY;
+        for (int i = 0; i < W; ++i) bb = fmin(bb, wrec[(size_t)i * rec_len]);
+        if (tid < W) sscale[tid] = rec_scale(a.neg_inv_lam, wrec[(size_t)tid * rec_len], bb);
+        __syncthreads();
+        double *grec = part + ((size_t)b * a.g.max_parts + part_idx) * rec_len;
+        for (int t = tid; t < H; t += nt) {
+            double e = 0.0;
+            for (int i = 0; i < W; ++i) e += sscale[i] * wrec[(size_t)i * rec_len + PART_HDR + t];
+            grec[PART_HDR + t] = e;
+        }
+        if (tid == 0) {
+            double eta = 0.0;
+            for (int i = 0; i < W; ++i) eta += sscale[i] * wrec[(size_t)i * rec_len + 1];
+            grec[0] = bb;
+            grec[1] = eta;
+        }
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            const int ticket = atomicAdd(&done_count[b], 1);
+            s_last = (ticket == nb - 1);
+            if (s_last) done_count[b] = 0;  // self-cleaning: ready for the next solve on this stream
+        }
+        __syncthreads();
+        if (!s_last) return;
+        __threadfence();
+        double beta, eta;
+        block_merge(a.neg_inv_lam, H, part + (size_t)b * a.g.max_parts * rec_len, nb, (size_t)rec_len, sscale, sEw, red,
+                    Eout, &beta, &eta);
+        block_apply<Env>(a, ec, b, false, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG);
+    } else {
+        // mode B: this block owns whole solves; its warps' records are in global memory (slot = warp).  One warp
+        // merges one solve; then one THREAD per solve rolls out the nominal trajectory, G solves at a time.
+        const int nsolve = b_hi - b_lo + 1, G = a.g.fin_group;
+        double *sUc = arena;                       // [G][H]
+        double *sG = sUc + (size_t)G * H;          // [G][H * NZ], or one zero row
+        for (int g0 = 0; g0 < nsolve; g0 += G) {
+            const int ng = min(G, nsolve - g0);
+            for (int sl = w; sl < ng; sl += W) {
+                const int b = b_lo + g0 + sl;
+                const double *recs = part + (size_t)b * a.g.max_parts * rec_len;
+                const double bj = (lane < W) ? recs[(size_t)lane * rec_len] : INFINITY;
+                const double beta = warp_min(bj);
+                const double sc = rec_scale(a.neg_inv_lam, bj, beta);
+                const double eta = warp_sum((lane < W) ? sc * recs[(size_t)lane * rec_len + 1] : 0.0);
+                const double inv_eta = 1.0 / eta;
+                double *U = Ug + (size_t)b * H;
+                double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
+                for (int t0 = 0; t0 < H; t0 += 32) {
+                    const int t = t0 + lane;
+                    double e = 0.0;
+                    for (int i = 0; i < W; ++i) {
+                        const double si = __shfl_sync(0xffffffffu, sc, i);
+                        if (t < H) e += si * recs[(size_t)i * rec_len + PART_HDR + t];
+                    }
+                    if (t < H) {
+                        if (a.record_only) {
+                            rank_part[((size_t)a.rank * a.g.B + b) * rec_len + PART_HDR + t] = e;
+                        } else {
+                            const double un = U[t] + inv_eta * e;  // mppi.py:62,69
+                            U[t] = un;
+                            o[1 + t] = un;
+                            if (t == 0) o[0] = un;
+                            sUc[(size_t)sl * H + t] = fmin(fmax(un, a.lo), a.hi);
+                        }
+                    }
+                }
+                if (a.record_only && lane == 0) {
+                    double *rec = rank_part + ((size_t)a.rank * a.g.B + b) * rec_len;
+                    rec[0] = beta;
+                    rec[1] = eta;
+                }
+                if (!a.record_only && a.want_traj && !a.goal_zero)
+                    for (int i = lane; i < H * NZ; i += 32) sG[(size_t)sl * H * NZ + i] = g_z[(size_t)b * H * NZ + i];
+            }
+            if (a.goal_zero && tid < NZ) sG[tid] = 0.0;
+            __syncthreads();
+            if (!a.record_only && a.want_traj && tid < ng) {
+                const int b = b_lo + g0 + tid;
+                double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
+                o[1 + H] = nominal_rollout<typename Env::Scalar>(scalar_consts(ec), H, x0g + (size_t)b * NS, sUc + (size_t)tid * H,
+                                                a.goal_zero ? sG : sG + (size_t)tid * H * NZ, a.goal_zero ? 0 : NZ,
+                                                o + 2 + H);
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ================================================================================================ rank merge
+// Multi-GPU second half: one block per solve merges the `world` rank records gathered in rank_part
+// ([world][B][2+H]) and applies them exactly as the single-GPU tail does.
+template <class Env>
+__global__ void __launch_bounds__(256) mppi_rank_merge_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec,
+                                                              double *__restrict__ rank_part,
+                                                              const double *__restrict__ x0g,
+                                                              const double *__restrict__ g_z, double *Ug,
+                                                              double *__restrict__ out) {
+    constexpr int NZ = Env::NS + 1;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ double red[32];
+    const int H = a.g.H, b = blockIdx.x, rec_len = PART_HDR + H, nw = blockDim.x >> 5;
+    double *sscale = reinterpret_cast<double *>(smem_raw);  // [world]
+    double *sUc = sscale + a.world;                         // [H]
+    double *sG = sUc + H;                                   // [H * NZ]
+    double *sEw = sG + (size_t)H * NZ;                      // [nw][H]
+    double *Eout = sEw + (size_t)nw * H;                    // [H]
+    double beta, eta;
+    block_merge(a.neg_inv_lam, H, rank_part + (size_t)b * rec_len, a.world, (size_t)a.g.B * rec_len, sscale, sEw, red,
+                Eout, &beta, &eta);
+    block_apply<Env>(a, ec, b, true, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG);
+}
+
+}  // namespace mpc

@@ -48,6 +48,8 @@ struct VT<double> {
 __device__ __forceinline__ float lane(float a, int) { return a; }
 __device__ __forceinline__ double lane(double a, int) { return a; }
 __device__ __forceinline__ float lane(const f2 &a, int i) { return i ? a.v.y : a.v.x; }
+template <typename V>
+__device__ __forceinline__ typename VT<V>::S lane_of(const V &a, int i) { return lane(a, i); }  // where `lane` is taken
 
 // ---- arithmetic
 __device__ __forceinline__ float vfma(float a, float b, float c) { return fmaf(a, b, c); }
