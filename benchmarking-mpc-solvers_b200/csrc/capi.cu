@@ -206,6 +206,9 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         f[11] = sqrt(p[11]);
         f[12] = sqrt(p[15]);
         f[13] = p[12]; f[14] = p[13]; f[15] = p[14];
+        f[16] = p[0] / (2 * M_PI);  // the float flavour integrates the angles in half-turns (envs.cuh)
+        f[17] = p[0] / M_PI;
+        f[18] = p[0] / (6 * M_PI);
     } else {
         return -1;
     }

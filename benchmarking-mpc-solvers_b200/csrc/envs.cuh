@@ -66,6 +66,12 @@ struct Pendulum {
     typedef typename VT<V>::S S;
     typedef V Vec;
     typedef Pendulum<S, false> Scalar;  // one sample per thread, accurate trig: nominal rollouts
+    // reference units <-> the units step() keeps the state in (identity here)
+    static __device__ __forceinline__ void enter(const EnvConst<V> &, S *) {}
+    static __device__ __forceinline__ void leave(const EnvConst<V> &, const S *x, double *out) {
+#pragma unroll
+        for (int i = 0; i < NS; ++i) out[i] = (double)x[i];
+    }
     // cost = sum W_i (z_i - g_i)^2 with z = -[thn, om, u]  ==  sum (sW_i*[thn, om, u]_i + sW_i*g_i)^2
     static __device__ __forceinline__ void prep_goal(const EnvConst<V> &k, const double *g, S *gs) {
 #pragma unroll
@@ -97,6 +103,12 @@ struct Pendulum<double, FAST> {
     typedef double S;
     typedef double Vec;
     typedef Pendulum<double, FAST> Scalar;
+    // reference units <-> the units step() keeps the state in (identity here)
+    static __device__ __forceinline__ void enter(const EnvConst<double> &, double *) {}
+    static __device__ __forceinline__ void leave(const EnvConst<double> &, const double *x, double *out) {
+#pragma unroll
+        for (int i = 0; i < NS; ++i) out[i] = (double)x[i];
+    }
     static __device__ __forceinline__ void prep_goal(const EnvConst<double> &, const double *g, double *gs) {
 #pragma unroll
         for (int i = 0; i < 3; ++i) gs[i] = g[i];
@@ -134,6 +146,12 @@ struct CartPole {
     typedef typename VT<V>::S S;
     typedef V Vec;
     typedef CartPole<S, false> Scalar;  // one sample per thread, accurate trig: nominal rollouts
+    // reference units <-> the units step() keeps the state in (identity here)
+    static __device__ __forceinline__ void enter(const EnvConst<V> &, S *) {}
+    static __device__ __forceinline__ void leave(const EnvConst<V> &, const S *x, double *out) {
+#pragma unroll
+        for (int i = 0; i < NS; ++i) out[i] = (double)x[i];
+    }
     // z = [xc, pd, 1 - cos th, thd, u]; residual_i = sW_i (z_i - g_i)
     static __device__ __forceinline__ void prep_goal(const EnvConst<V> &k, const double *g, S *gs) {
         gs[0] = -k0(k, 13) * (S)g[0];
@@ -182,6 +200,12 @@ struct CartPole<double, FAST> {
     typedef double S;
     typedef double Vec;
     typedef CartPole<double, FAST> Scalar;
+    // reference units <-> the units step() keeps the state in (identity here)
+    static __device__ __forceinline__ void enter(const EnvConst<double> &, double *) {}
+    static __device__ __forceinline__ void leave(const EnvConst<double> &, const double *x, double *out) {
+#pragma unroll
+        for (int i = 0; i < NS; ++i) out[i] = (double)x[i];
+    }
     static __device__ __forceinline__ void prep_goal(const EnvConst<double> &, const double *g, double *gs) {
 #pragma unroll
         for (int i = 0; i < 5; ++i) gs[i] = g[i];
@@ -216,7 +240,7 @@ struct CartPole<double, FAST> {
 // float layout f: 0 h  1 A = m1 lc1^2 + m2 (l1^2 + lc2^2) + I1 + I2   2 B = 2 m2 l1 lc2     (d1 = A + B cos th2)
 //    3 C = m2 lc2^2 + I2   4 D = m2 l1 lc2                                                    (d2 = C + D cos th2)
 //    5 P1 = (m1 lc1 + m2 l1) g   6 P2 = m2 lc2 g   7 max_vel1  8 max_vel2   9 h/2  10 h/6  11 sqrt(W0)  12 sqrt(W4)
-//    13..15 W1..W3 (their residuals are constants of the solve)
+//    13..15 W1..W3 (their residuals are constants of the solve)   16 h/(2 pi)  17 h/pi  18 h/(6 pi)
 template <typename V, bool FAST>
 struct Acrobot {
     static constexpr int NS = 4, NG = 3, CHUNK = 2;
@@ -224,6 +248,17 @@ struct Acrobot {
     typedef typename VT<V>::S S;
     typedef V Vec;
     typedef Acrobot<S, false> Scalar;  // one sample per thread, accurate trig: nominal rollouts
+    // step() keeps the two angles in HALF-TURNS (theta / pi): range reductions become exact additions (vec.cuh)
+    static __device__ __forceinline__ void enter(const EnvConst<V> &, S *x) {
+        x[0] *= 0.318309886f;
+        x[1] *= 0.318309886f;
+    }
+    static __device__ __forceinline__ void leave(const EnvConst<V> &, const S *x, double *out) {
+        out[0] = (double)x[0] * D_PI;
+        out[1] = (double)x[1] * D_PI;
+        out[2] = (double)x[2];
+        out[3] = (double)x[3];
+    }
     // z = [-cos th1 - cos(th1+th2) - 2, 0, 0, 0, u]                                   acrobot_model.py:162-176
     static __device__ __forceinline__ void prep_goal(const EnvConst<V> &k, const double *g, S *gs) {
         gs[0] = k0(k, 11) * (S)(2.0 + g[0]);  // residual_0 = -(sW0 (c1 + c12) + gs0)
@@ -232,8 +267,10 @@ struct Acrobot {
     }
 
     // "book" _dsdt (acrobot_model.py:99-132) given sin/cos of both angles; returns the angular accelerations.
-    //   acc2 = (a + d2/d1 phi1 - D w1^2 s2 - phi2) / (C - d2^2/d1) = N / Dd,  N = (a - D w1^2 s2 - phi2) d1 + d2 phi1,
-    //   Dd = C d1 - d2^2;   acc1 = -(d2 acc2 + phi1) / d1;   with r = 1/(d1 Dd):  1/Dd = r d1,  1/d1 = r Dd
+    // The reference's two quotients are the solution of the 2x2 mass-matrix system
+    //     [d1 d2; d2 C] [acc1; acc2] = [-phi1; n1],   n1 = a - D w1^2 s2 - phi2,
+    // (substitute acc1 = -(d2 acc2 + phi1)/d1 into the second row), so with det = C d1 - d2^2 and ONE reciprocal
+    //     acc2 = (d1 n1 + d2 phi1) / det,     acc1 = -(C phi1 + d2 n1) / det.
     static __device__ __forceinline__ void accel(const EnvConst<V> &k, const V &s1, const V &c1, const V &s2,
                                                  const V &c2, const V &w1, const V &w2, const V &a, V *a1, V *a2) {
         const V d1 = vfma(k.c[2], c2, k.c[1]);
@@ -243,21 +280,18 @@ struct Acrobot {
         const V Ds2 = k.c[4] * s2;
         // phi1 = -D w2^2 s2 - 2 D w2 w1 s2 + P1 sin(th1) + phi2
         const V phi1 = vfma(-(Ds2 * w2), vfma(V(2.0f), w1, w2), vfma(k.c[5], s1, phi2));
-        const V Dd = vfma(k.c[3], d1, -(d2 * d2));
-        const V r = vrcp(d1 * Dd);
+        const V r = vrcp(vfma(k.c[3], d1, -(d2 * d2)));
         const V n1 = vfma(-Ds2, w1 * w1, a) - phi2;
-        const V N = vfma(d2, phi1, n1 * d1);
-        const V acc2 = N * (r * d1);
-        *a2 = acc2;
-        *a1 = -(vfma(d2, acc2, phi1) * (r * Dd));
+        *a2 = vfma(d2, phi1, n1 * d1) * r;
+        *a1 = vfma(k.c[3], phi1, d2 * n1) * (-r);
     }
 
     static __device__ __forceinline__ V step(const EnvConst<V> &k, V (&x)[NS], const V &u, const S *gs) {
-        const V th1 = x[0], th2 = x[1], w1 = x[2], w2 = x[3];
-        const V h = k.c[0], h2 = k.c[9], h6 = k.c[10];
+        const V p1 = x[0], p2 = x[1], w1 = x[2], w2 = x[3];  // p = theta / pi
+        const V h = k.c[0], h2 = k.c[9], h6 = k.c[10], hp = k.c[17], h2p = k.c[16], h6p = k.c[18];
         V s1, c1, s2, c2;
-        vsincos<FAST>(th1, &s1, &c1);
-        vsincos<FAST>(th2, &s2, &c2);
+        vsincospi<FAST>(p1, &s1, &c1);
+        vsincospi<FAST>(p2, &s2, &c2);
         const V c12 = vfma(c1, c2, -(s1 * s2));
         const V d0 = vfma(k.c[11], c1 + c12, V(gs[0])), d4 = vfma(k.c[12], u, V(gs[1]));
         const V cost = vfma(d0, d0, vfma(d4, d4, V(gs[2])));
@@ -265,23 +299,25 @@ struct Acrobot {
         V k1a, k1b, k2a, k2b, k3a, k3b, k4a, k4b;
         accel(k, s1, c1, s2, c2, w1, w2, u, &k1a, &k1b);
         const V k2w1 = vfma(h2, k1a, w1), k2w2 = vfma(h2, k1b, w2);
-        vsincos<FAST>(vfma(h2, w1, th1), &s1, &c1);
-        vsincos<FAST>(vfma(h2, w2, th2), &s2, &c2);
+        vsincospi<FAST>(vfma(h2p, w1, p1), &s1, &c1);
+        vsincospi<FAST>(vfma(h2p, w2, p2), &s2, &c2);
         accel(k, s1, c1, s2, c2, k2w1, k2w2, u, &k2a, &k2b);
         const V k3w1 = vfma(h2, k2a, w1), k3w2 = vfma(h2, k2b, w2);
-        vsincos<FAST>(vfma(h2, k2w1, th1), &s1, &c1);
-        vsincos<FAST>(vfma(h2, k2w2, th2), &s2, &c2);
+        vsincospi<FAST>(vfma(h2p, k2w1, p1), &s1, &c1);
+        vsincospi<FAST>(vfma(h2p, k2w2, p2), &s2, &c2);
         accel(k, s1, c1, s2, c2, k3w1, k3w2, u, &k3a, &k3b);
         const V k4w1 = vfma(h, k3a, w1), k4w2 = vfma(h, k3b, w2);
-        vsincos<FAST>(vfma(h, k3w1, th1), &s1, &c1);
-        vsincos<FAST>(vfma(h, k3w2, th2), &s2, &c2);
+        vsincospi<FAST>(vfma(hp, k3w1, p1), &s1, &c1);
+        vsincospi<FAST>(vfma(hp, k3w2, p2), &s2, &c2);
         accel(k, s1, c1, s2, c2, k4w1, k4w2, u, &k4a, &k4b);
-        const V n0 = vfma(h6, vfma(V(2.0f), k2w1 + k3w1, w1) + k4w1, th1);
-        const V n1 = vfma(h6, vfma(V(2.0f), k2w2 + k3w2, w2) + k4w2, th2);
-        const V n2 = vfma(h6, vfma(V(2.0f), k2a + k3a, k1a) + k4a, w1);
-        const V n3 = vfma(h6, vfma(V(2.0f), k2b + k3b, k1b) + k4b, w2);
-        x[0] = vwrap_pi(n0);   // wrap(.., -pi, pi) by repeated -+2pi  ==  nearest multiple of 2pi removed
-        x[1] = vwrap_pi(n1);
+        // y' = y + h/6 (k1 + 2 k2 + 2 k3 + k4): the velocity rows with the shared sum k2 + k3
+        const V m1 = k2w1 + k3w1, m2 = k2w2 + k3w2, ma = k2a + k3a, mb = k2b + k3b;
+        const V n0 = vfma(h6p, vfma(V(2.0f), m1, w1) + k4w1, p1);
+        const V n1 = vfma(h6p, vfma(V(2.0f), m2, w2) + k4w2, p2);
+        const V n2 = vfma(h6, vfma(V(2.0f), ma, k1a) + k4a, w1);
+        const V n3 = vfma(h6, vfma(V(2.0f), mb, k1b) + k4b, w2);
+        x[0] = vwrap_halfturns(n0);  // wrap(.., -pi, pi) by repeated -+2pi  ==  nearest multiple of 2pi removed
+        x[1] = vwrap_halfturns(n1);
         x[2] = vclip(n2, -k.c[7], k.c[7]);
         x[3] = vclip(n3, -k.c[8], k.c[8]);
         return cost;
@@ -297,6 +333,12 @@ struct Acrobot<double, FAST> {
     typedef double S;
     typedef double Vec;
     typedef Acrobot<double, FAST> Scalar;
+    // reference units <-> the units step() keeps the state in (identity here)
+    static __device__ __forceinline__ void enter(const EnvConst<double> &, double *) {}
+    static __device__ __forceinline__ void leave(const EnvConst<double> &, const double *x, double *out) {
+#pragma unroll
+        for (int i = 0; i < NS; ++i) out[i] = (double)x[i];
+    }
     static __device__ __forceinline__ void prep_goal(const EnvConst<double> &, const double *g, double *gs) {
 #pragma unroll
         for (int i = 0; i < 5; ++i) gs[i] = g[i];

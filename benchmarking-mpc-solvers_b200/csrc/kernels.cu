@@ -109,6 +109,7 @@ __device__ double nominal_rollout(const EnvConst<typename Env::Vec> &ec, int H, 
         x[i] = (R)x0[i];
         if (xs) xs[i] = x0[i];
     }
+    Env::enter(ec, x);
     double reward = 0.0;
     R gs[Env::NG];
     if (g_stride == 0) Env::prep_goal(ec, g_z, gs);
@@ -116,10 +117,7 @@ __device__ double nominal_rollout(const EnvConst<typename Env::Vec> &ec, int H, 
         if (g_stride != 0) Env::prep_goal(ec, g_z + t * g_stride, gs);
         const R c = Env::step(ec, x, (R)us[t], gs);
         reward += -(double)c;
-        if (xs) {
-#pragma unroll
-            for (int i = 0; i < NS; ++i) xs[(t + 1) * NS + i] = (double)x[i];
-        }
+        if (xs) Env::leave(ec, x, xs + (t + 1) * NS);
     }
     return -reward;
 }
@@ -201,6 +199,7 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
     Env::prep_goal(ec, g_z, gs);
 #pragma unroll
     for (int i = 0; i < NS; ++i) x[i] = (R)x0g[i];
+    Env::enter(ec, x);
     __syncthreads();
     const int k = blockIdx.x * TILE + tid;
     if (k >= a.g.K_local) return;
@@ -335,9 +334,9 @@ __global__ void model_step_kernel(const EnvConst<typename Env::Vec> ec, int n, c
 #pragma unroll
     for (int j = 0; j < NS; ++j) x[j] = (R)xg[(size_t)i * NS + j];
     Env::prep_goal(ec, gg + (size_t)i * NZ, gs);
+    Env::enter(ec, x);
     cost[i] = (double)Env::step(ec, x, (R)ug[i], gs);
-#pragma unroll
-    for (int j = 0; j < NS; ++j) xn[(size_t)i * NS + j] = (double)x[j];
+    Env::leave(ec, x, xn + (size_t)i * NS);
 }
 
 // FMA-pipe peak: 16 independent chains per thread, no memory traffic.

@@ -268,6 +268,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
         Env::prep_goal(ec, g_z + (size_t)b * H * NZ, gs);  // goal row 0 (model.py:34,38)
 #pragma unroll
         for (int i = 0; i < NS; ++i) xinit[i] = (R)x0g[(size_t)b * NS + i];
+        Env::enter(ec, xinit);
         __syncwarp();
     };
     // mode B only: the warp's record of solve `cur` goes to global memory (slot = warp)
