@@ -165,7 +165,11 @@ def make_solver(capi, orc_params, agent, env, K, H, prm, dist, dtype="f32", nois
                     device=dist.local_rank, rank=dist.rank if dist.world > 1 else 0, world=dist.world, seed=0,
                     **prm, **kw)
     if dist.world > 1:
-        s.comm_init(dist.comm_id(capi.Solver.comm_create_id))
+        if agent == "MPPI" and os.environ.get("MPC_B200_EXCHANGE", "p2p") == "p2p":
+            from mpc_b200 import parallel
+            parallel.connect_p2p(s)  # in-kernel all-gather over NVLink peer memory: one launch per solve
+        else:
+            s.comm_init(dist.comm_id(capi.Solver.comm_create_id))
     if agent == "MPPI" and noise == "tensor":
         s.fill_noise()  # synthetic N(0, sigma) tensor drawn on the device (Philox); resident like agent.delta_u
     return s
@@ -381,7 +385,10 @@ def run_ours(args, dist):
                    "fast_math": bool(args.fast_math), "K_per_gpu": s.K_local,
                    "cache": ("L2 flushed (256 MiB write) between timed steps" if flush else
                              "noise shard %.0f MB per GPU > L2 (126 MB): no flush" % (shard_bytes / 1e6)),
-                   "parallelism": "K-shard x%d, one all-gather of (beta, eta, E[H]) per solve" % dist.world},
+                   "parallelism": "K-shard x%d, one all-gather of (beta, eta, E[H]) per solve (%s)" % (
+                       dist.world, "single GPU" if dist.world == 1 else
+                       ("inside the solve kernel over NVLink peer memory"
+                        if os.environ.get("MPC_B200_EXCHANGE", "p2p") == "p2p" else "NCCL + merge kernel"))},
         "clocks": clk, "gpu_launches": launches,
         "e2e": {"value": e2e_value, "unit": "rollout-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "p50_solve_ms": round(1e3 * statistics.median(lat), 4)},

@@ -18,6 +18,7 @@ NOISE_TENSOR, NOISE_PHILOX = 0, 1
 COMM_ID_BYTES = 128
 MAX_ENV_PARAMS = 24
 
+P2P_HANDLE_BYTES = 64
 DTYPES = {"f64": F64, "float64": F64, "fp64": F64, "f32": F32, "float32": F32, "fp32": F32}
 NOISES = {"tensor": NOISE_TENSOR, "numpy": NOISE_TENSOR, "philox": NOISE_PHILOX}
 
@@ -28,7 +29,7 @@ SYMBOLS = [
     "mpc_cem_solve", "mpc_cem_get_rewards", "mpc_cem_get_elites", "mpc_cem_get_std", "mpc_simulate", "mpc_model_step",
     "mpc_comm_create_id", "mpc_comm_init", "mpc_mppi_rollout_partial", "mpc_mppi_apply_partials", "mpc_upload_inputs", "mpc_solve_enqueue", "mpc_download_outputs",
     "mpc_timer_start", "mpc_timer_stop", "mpc_sync", "mpc_set_profiling", "mpc_get_rollout_ms", "mpc_launch_count", "mpc_get_geometry", "mpc_measure_fma_peak",
-    "mpc_flush_l2",
+    "mpc_flush_l2", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace",
 ]
 
 
@@ -85,6 +86,10 @@ def load():
     L.mpc_model_step.argtypes = [hp, C.c_int32, _dp, _dp, _dp, _dp, _dp]
     L.mpc_comm_create_id.argtypes = [C.c_void_p]
     L.mpc_comm_init.argtypes = [hp, C.c_void_p]
+    L.mpc_p2p_export.argtypes = [hp, C.c_void_p]
+    L.mpc_p2p_import.argtypes = [hp, C.c_void_p]
+    L.mpc_p2p_link.argtypes = [C.POINTER(hp), C.c_int32]
+    L.mpc_get_trace.argtypes = [hp, C.POINTER(C.c_uint64)]
     L.mpc_mppi_rollout_partial.argtypes = [hp, _dp, _dp, _dp, _dp]
     L.mpc_mppi_apply_partials.argtypes = [hp, _dp, _dp, _dp, _dp, _dp]
     L.mpc_upload_inputs.argtypes = [hp, _dp, _dp, _dp]
@@ -147,6 +152,7 @@ class Solver:
         self.cfg = cfg
         self.L = L
         self.K, self.H, self.B = int(K), int(H), int(batch)
+        self.rank, self.world = int(rank), int(world)
         self.ns = 2 if cfg.env == ENV_PENDULUM else 4
         self.nz = self.ns + 1
         self.is_mppi = cfg.agent == AGENT_MPPI
@@ -307,6 +313,30 @@ class Solver:
         buf = C.create_string_buffer(bytes(id_bytes), COMM_ID_BYTES)
         self._ck(self.L.mpc_comm_init(self._h, buf))
 
+    def p2p_export(self):
+        """64-byte IPC handle of this rank's exchange buffer (in-kernel all-gather over NVLink peer memory)."""
+        buf = C.create_string_buffer(P2P_HANDLE_BYTES)
+        self._ck(self.L.mpc_p2p_export(self._h, buf))
+        return bytes(buf.raw)
+
+    def p2p_import(self, handles):
+        """handles: the ranks' exported handles, rank-major (bytes of length world * 64, or a list of bytes)."""
+        raw = b"".join(handles) if isinstance(handles, (list, tuple)) else bytes(handles)
+        if len(raw) != self.world * P2P_HANDLE_BYTES:
+            raise ValueError("expected %d handle bytes, got %d" % (self.world * P2P_HANDLE_BYTES, len(raw)))
+        buf = C.create_string_buffer(raw, len(raw))
+        self._ck(self.L.mpc_p2p_import(self._h, buf))
+
+    @staticmethod
+    def p2p_link(solvers):
+        """One process driving several GPUs: wire the rank-ordered solvers' exchange buffers to each other."""
+        L = load()
+        arr = (C.c_void_p * len(solvers))(*[s._h.value for s in solvers])
+        rc = L.mpc_p2p_link(arr, len(solvers))
+        if rc != MPC_OK:
+            msgs = [(L.mpc_last_error(s._h) or b"").decode() for s in solvers]
+            raise MpcError(rc, "; ".join(m for m in msgs if m))
+
     def mppi_rollout_partial(self, x, g_z=None, U_in=None):
         xa, xp = _in(x, (self.B, self.ns))
         ga, gp = self._gz(g_z)
@@ -360,6 +390,15 @@ class Solver:
         ms = C.c_float()
         self._ck(self.L.mpc_get_rollout_ms(self._h, C.byref(ms)))
         return ms.value
+
+    def trace(self):
+        """Phase stamps (ns) of the last solve's finalising block, relative to the kernel start (profiling on)."""
+        buf = (C.c_uint64 * 16)()
+        self._ck(self.L.mpc_get_trace(self._h, buf))
+        names = ["start", "tiles_done", "ticket", "merged", "published", "peers_in", "merged2", "applied", "end",
+                 "recs_in_smem", "rec_written", "fenced"]
+        t0 = buf[0]
+        return {n: (int(buf[i]) - int(t0)) if buf[i] else None for i, n in enumerate(names)}
 
     def sync(self):
         self._ck(self.L.mpc_sync(self._h))

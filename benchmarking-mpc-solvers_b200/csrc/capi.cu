@@ -81,6 +81,13 @@ struct mpc_handle {
     double *d_part = nullptr;     // [B][max_parts][2+H]
     double *d_rank_part = nullptr;  // [world][B][2+H]
     int *d_done = nullptr;        // [B] block arrival tickets of the solve kernel
+    // peer exchange (multi-GPU, in-kernel all-gather): this rank's buffer and every rank's mapped buffer
+    double *d_xchg = nullptr;     // [world][B][2+H] doubles | u64 flags [world][B]
+    double *peer_recs[16] = {nullptr};
+    bool peer_opened[16] = {false};  // mapped through cudaIpcOpenMemHandle (to be closed)
+    bool p2p_ready = false;
+    unsigned long long *d_trace = nullptr;  // phase stamps of the last solve's finalising block (when profiling)
+    unsigned long long epoch = 0;
     double *d_out = nullptr;      // [B][out_stride] (+1)
     double *d_scratch = nullptr;  // staging for uploads: max(K_local*H, misc)
     size_t scratch_elems = 0;
@@ -236,7 +243,11 @@ static MppiArgs mppi_args(const mpc_handle *h, int want_traj) {
     a.noise_batched = 0;
     a.want_traj = want_traj;
     a.goal_zero = h->g_zero_on_device ? 1 : 0;
-    a.record_only = h->cfg.world > 1 ? 1 : 0;
+    a.store_costs = getenv("MPC_B200_NOCOSTS") ? 0 : 1;  // experiment knob (tools/trace_probe.py)
+    a.p2p = (h->cfg.world > 1 && h->p2p_ready) ? 1 : 0;
+    a.record_only = (h->cfg.world > 1 && !a.p2p) ? 1 : 0;
+    a.epoch = h->epoch;
+    a.trace = h->profiling ? h->d_trace : nullptr;
     a.world = h->cfg.world;
     a.rank = h->cfg.rank;
     return a;
@@ -254,6 +265,7 @@ static MppiBuffers mppi_bufs(const mpc_handle *h) {
     b.rank_part = h->d_rank_part;
     b.out = h->d_out;
     b.done_count = h->d_done;
+    b.peer_recs = h->peer_recs;
     return b;
 }
 
@@ -335,6 +347,10 @@ int mpc_destroy(mpc_handle *h) {
     cudaFree(h->d_part);
     cudaFree(h->d_rank_part);
     cudaFree(h->d_done);
+    cudaFree(h->d_trace);
+    for (int r = 0; r < 16; ++r)
+        if (h->peer_opened[r] && h->peer_recs[r]) cudaIpcCloseMemHandle(h->peer_recs[r]);
+    cudaFree(h->d_xchg);
     cudaFree(h->d_out);
     cudaFree(h->d_scratch);
     cudaFree(h->d_sd);
@@ -535,6 +551,8 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         CUC(cudaMalloc(&h->d_S, (size_t)g.B * g.Kpad * sizeof(double)));
         CUC(cudaMalloc(&h->d_part, (size_t)g.B * g.max_parts * rec * sizeof(double)));
         CUC(cudaMalloc(&h->d_rank_part, (size_t)cfg->world * g.B * rec * sizeof(double)));
+        CUC(cudaMalloc(&h->d_trace, 16 * sizeof(unsigned long long)));
+        CUC(cudaMemsetAsync(h->d_trace, 0, 16 * sizeof(unsigned long long), h->stream));
         CUC(cudaMalloc(&h->d_done, (size_t)g.B * sizeof(int)));
         CUC(cudaMemsetAsync(h->d_done, 0, (size_t)g.B * sizeof(int), h->stream));
     } else {
@@ -657,7 +675,12 @@ static int fetch_outputs(mpc_handle *h, int want_traj, double *u0, double *U_out
         CU(h, cudaMemcpy2DAsync(h->h_out, h->out_stride * sizeof(double), h->d_out, h->out_stride * sizeof(double),
                                 per * sizeof(double), g.B, cudaMemcpyDeviceToHost, h->stream));
     }
+    if (h->p2p_ready)  // the peer wait's error word lives behind the last solve's outputs
+        CU(h, cudaMemcpyAsync(h->h_out + (size_t)g.B * h->out_stride, h->d_out + (size_t)g.B * h->out_stride,
+                              sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
+    if (h->p2p_ready && h->h_out[(size_t)g.B * h->out_stride] != 0.0)
+        return fail(h, MPC_ENCCL, "peer exchange timed out: a rank did not deliver its record within 4 s");
     for (int b = 0; b < g.B; ++b) {
         const double *o = h->h_out + (size_t)b * h->out_stride;
         if (u0) u0[b] = o[0];
@@ -674,14 +697,16 @@ static int fetch_outputs(mpc_handle *h, int want_traj, double *u0, double *U_out
 static int mppi_enqueue(mpc_handle *h, int want_traj) {
     if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "not an MPPI handle");
     if (!h->noise_ready) return fail(h, MPC_ESTATE, "noise tensor not set: call mpc_set_noise or mpc_fill_noise first");
-    if (h->cfg.world > 1 && !h->comm) return fail(h, MPC_ESTATE, "world > 1 but mpc_comm_init was not called");
+    if (h->cfg.world > 1 && !h->comm && !h->p2p_ready)
+        return fail(h, MPC_ESTATE, "world > 1 but neither mpc_p2p_import/mpc_p2p_link nor mpc_comm_init was called");
+    if (h->p2p_ready) h->epoch++;
     const MppiArgs a = mppi_args(h, want_traj);
     const MppiBuffers b = mppi_bufs(h);
     if (h->profiling) CU(h, cudaEventRecord(h->evr0, h->stream));
     CU(h, launch_mppi_solve(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
     if (h->profiling) CU(h, cudaEventRecord(h->evr1, h->stream));
     h->launches++;
-    if (h->cfg.world > 1) {
+    if (h->cfg.world > 1 && !a.p2p) {
         const size_t cnt = (size_t)h->g.B * (PART_HDR + h->g.H);
         ncclResult_t r = g_nccl.AllGather(h->d_rank_part + (size_t)h->cfg.rank * cnt, h->d_rank_part, cnt, ncclFloat64,
                                           h->comm, h->stream);
@@ -949,6 +974,88 @@ int mpc_comm_init(mpc_handle *h, const void *id_bytes) {
     return MPC_OK;
 }
 
+// Peer exchange: the in-kernel all-gather of the solve kernel (mppi.cuh) needs every rank's exchange buffer mapped
+// into every rank.  One process per GPU: export -> host all-gather of the 64-byte handles -> import.  One process
+// driving several GPUs: mpc_p2p_link.
+static int xchg_alloc(mpc_handle *h) {
+    if (h->d_xchg) return MPC_OK;
+    if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "peer exchange is an MPPI feature");
+    if (h->cfg.world > 16) return fail(h, MPC_EINVAL, "peer exchange supports up to 16 ranks");
+    // mode A blocks wait for their peers while holding an SM: every block of the grid must be resident
+    if (h->g.solves_per_block == 0 && h->g.grid > h->num_sms)
+        return fail(h, MPC_ESTATE, "peer exchange needs the whole grid resident (batch %d too large for K %d); use NCCL",
+                    h->g.B, h->cfg.K);
+    CU(h, cudaSetDevice(h->cfg.device));
+    const size_t slots = (size_t)h->cfg.world * h->g.B;
+    const size_t bytes = slots * (PART_HDR + h->g.H) * sizeof(double) + slots * sizeof(unsigned long long);
+    CU(h, cudaMalloc(&h->d_xchg, bytes));
+    CU(h, cudaMemset(h->d_xchg, 0, bytes));
+    return MPC_OK;
+}
+
+int mpc_p2p_export(mpc_handle *h, void *handle_out) {
+    if (!h || !handle_out) return fail(h, MPC_EINVAL, "null argument");
+    int rc = xchg_alloc(h);
+    if (rc) return rc;
+    static_assert(sizeof(cudaIpcMemHandle_t) == MPC_P2P_HANDLE_BYTES, "ipc handle size");
+    cudaIpcMemHandle_t ih;
+    CU(h, cudaIpcGetMemHandle(&ih, h->d_xchg));
+    memcpy(handle_out, &ih, sizeof ih);
+    return MPC_OK;
+}
+
+int mpc_p2p_import(mpc_handle *h, const void *handles) {
+    if (!h || !handles) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.world == 1) return MPC_OK;
+    int rc = xchg_alloc(h);
+    if (rc) return rc;
+    CU(h, cudaSetDevice(h->cfg.device));
+    for (int r = 0; r < h->cfg.world; ++r) {
+        if (r == h->cfg.rank) {
+            h->peer_recs[r] = h->d_xchg;
+            continue;
+        }
+        cudaIpcMemHandle_t ih;
+        memcpy(&ih, (const char *)handles + (size_t)r * MPC_P2P_HANDLE_BYTES, sizeof ih);
+        void *p = nullptr;
+        CU(h, cudaIpcOpenMemHandle(&p, ih, cudaIpcMemLazyEnablePeerAccess));
+        h->peer_recs[r] = (double *)p;
+        h->peer_opened[r] = true;
+    }
+    h->p2p_ready = true;
+    return MPC_OK;
+}
+
+int mpc_p2p_link(mpc_handle *const *hs, int32_t world) {
+    if (!hs || world < 1) return MPC_EINVAL;
+    for (int r = 0; r < world; ++r) {
+        if (!hs[r]) return MPC_EINVAL;
+        if (hs[r]->cfg.world != world || hs[r]->cfg.rank != r)
+            return fail(hs[r], MPC_EINVAL, "mpc_p2p_link: handle %d has rank %d of %d", r, hs[r]->cfg.rank, hs[r]->cfg.world);
+        int rc = xchg_alloc(hs[r]);
+        if (rc) return rc;
+    }
+    for (int r = 0; r < world; ++r) {
+        mpc_handle *h = hs[r];
+        CU(h, cudaSetDevice(h->cfg.device));
+        for (int q = 0; q < world; ++q) {
+            if (q != r && hs[q]->cfg.device != h->cfg.device) {
+                int can = 0;
+                CU(h, cudaDeviceCanAccessPeer(&can, h->cfg.device, hs[q]->cfg.device));
+                if (!can) return fail(h, MPC_ECUDA, "device %d cannot access device %d", h->cfg.device, hs[q]->cfg.device);
+                cudaError_t e = cudaDeviceEnablePeerAccess(hs[q]->cfg.device, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled)
+                    cudaGetLastError();
+                else if (e != cudaSuccess)
+                    return fail(h, MPC_ECUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+            }
+            h->peer_recs[q] = hs[q]->d_xchg;
+        }
+        h->p2p_ready = true;
+    }
+    return MPC_OK;
+}
+
 // ---------------------------------------------------------------------------------------------- measurement
 int mpc_upload_inputs(mpc_handle *h, const double *x, const double *g_z, const double *U_in) {
     if (!h) return MPC_EINVAL;
@@ -1010,6 +1117,15 @@ int mpc_get_rollout_ms(mpc_handle *h, float *ms_out) {
     CU(h, cudaSetDevice(h->cfg.device));
     CU(h, cudaEventSynchronize(h->evr1));
     CU(h, cudaEventElapsedTime(ms_out, h->evr0, h->evr1));
+    return MPC_OK;
+}
+
+int mpc_get_trace(mpc_handle *h, uint64_t out[16]) {
+    if (!h || !out) return MPC_EINVAL;
+    if (!h->d_trace) return fail(h, MPC_ESTATE, "no trace buffer (MPPI handles only)");
+    CU(h, cudaSetDevice(h->cfg.device));
+    CU(h, cudaMemcpyAsync(out, h->d_trace, 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
     return MPC_OK;
 }
 

@@ -425,19 +425,27 @@ static cudaError_t mppi_solve_go(const MppiArgs &a, const EnvParamsHost &ep, con
     typedef typename Env::Vec V;
     auto kern = mppi_solve_kernel<Env, NOISE>;
     const size_t smem = a.g.smem_rollout;
-    static size_t smem_set = 0;  // per instantiation: raise the dynamic shared memory limit only when it grows
-    if (smem > smem_set) {
+    // per instantiation AND per device (the attribute is a per-device function property): raise the dynamic
+    // shared memory limit only when it grows
+    static size_t smem_set[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (smem > smem_set[dev & 63]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        smem_set = smem;
+        smem_set[dev & 63] = smem;
     }
     CUtensorMap map;
     if (b.noise_map)
         memcpy(&map, b.noise_map, sizeof map);
     else
         memset(&map, 0, sizeof map);  // PHILOX: never dereferenced
+    PeerTable pt;
+    memset(&pt, 0, sizeof pt);
+    if (a.p2p)
+        for (int r = 0; r < a.world && r < MAX_WORLD; ++r) pt.recs[r] = b.peer_recs[r];
     kern<<<a.g.grid, a.g.warps * 32, smem, s>>>(a, make_env<V>(ep), map, b.x0, b.g_z, b.U, b.S, b.part, b.rank_part,
-                                                 b.out, b.done_count);
+                                                 b.out, b.done_count, pt);
     return cudaGetLastError();
 }
 
@@ -481,11 +489,13 @@ cudaError_t FN(launch_mppi_rank_merge)(const EnvParamsHost &ep, const MppiArgs &
         auto kern = mppi_rank_merge_kernel<E>;
         const int H = a.g.H, nw = 256 / 32;
         const size_t smem = ((size_t)a.world + H + (size_t)H * (a.g.ns + 1) + (size_t)nw * H + H) * sizeof(double);
-        static size_t smem_set = 48 * 1024;
-        if (smem > smem_set) {
+        static size_t smem_set[64] = {0};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (smem > 48 * 1024 && smem > smem_set[dev & 63]) {
             e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             if (e != cudaSuccess) return;
-            smem_set = smem;
+            smem_set[dev & 63] = smem;
         }
         kern<<<a.g.B, 256, smem, s>>>(a, make_env<typename E::Vec>(ep), b.rank_part, b.x0, b.g_z, b.U, b.out);
         e = cudaGetLastError();

@@ -50,8 +50,12 @@ struct MppiArgs {
     uint32_t draw;        // Philox draw index
     int noise_batched;    // TENSOR: 1 = one tensor per solve of the batch, 0 = shared
     int want_traj;        // compute the clipped plan's nominal rollout in the tail of the solve kernel
+    int store_costs;      // write the per-sample costs S[k] (agent.sample_costs before mppi.py:73 zeroes them)
     int goal_zero;        // the goal trajectory is all zeros (what every reference script passes)
     int record_only;      // the tail publishes this rank's (beta, eta, E) record instead of applying it
+    int p2p;              // multi-GPU: all-gather the rank records inside the kernel over peer memory, then apply
+    unsigned long long epoch;  // p2p: flag value of this solve (monotonic per handle, equal on all ranks)
+    unsigned long long *trace; // null, or 16 words for the finalising block's phase stamps (mpc_get_trace)
     int world;            // ranks whose records the final merge combines
     int rank;
 };
@@ -76,6 +80,7 @@ struct MppiBuffers {
     double *rank_part;     // [world][B][2+H]  (all-gather buffer; this rank writes slot `rank`)
     double *out;           // [B][out_stride]: u0, U[H], cost, xs[(H+1)*ns]
     int *done_count;       // [B] arrival tickets of the solve kernel's blocks (self-cleaning)
+    double *const *peer_recs;  // host array [world] of the ranks' exchange buffers (p2p), else null
 };
 
 struct CemBuffers {

@@ -96,6 +96,56 @@ __device__ __forceinline__ double rec_scale(double neg_inv_lam, double bj, doubl
     return (bj == INFINITY) ? 0.0 : exp(neg_inv_lam * (bj - beta));
 }
 
+// ------------------------------------------------------------------------------------------------ peer exchange
+// Multi-GPU: every rank's solve kernel writes its (beta, eta, E[H]) record straight into the exchange buffer of EVERY
+// rank over NVLink (peer-mapped pointers), raises that rank's flag for (writer, solve) to the solve's epoch with a
+// system-scope release store, then waits for the flags of all writers in its own buffer: an all-gather inside the
+// kernel, no NCCL launch and no second kernel.  The wait is bounded (PEER_TIMEOUT_NS) and reports through an error
+// word instead of hanging.
+constexpr int MAX_WORLD = 16;
+struct PeerTable {
+    double *recs[MAX_WORLD];  // recs[r]: rank r's exchange buffer [world][B][2+H] doubles, then u64 flags [world][B]
+};
+constexpr unsigned long long PEER_TIMEOUT_NS = 4000000000ull;
+
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned long long *peer_flags(double *recs, int world, int B, int rec_len) {
+    return reinterpret_cast<unsigned long long *>(recs + (size_t)world * B * rec_len);
+}
+// phase stamps of the finalising block (nanoseconds of %globaltimer), read back with mpc_get_trace
+enum { TR_START = 0, TR_TILES_DONE = 1, TR_TICKET = 2, TR_MERGED = 3, TR_PUBLISHED = 4, TR_PEERS_IN = 5,
+       TR_MERGED2 = 6, TR_APPLIED = 7, TR_END = 8, TR_WORDS = 16 };
+__device__ __forceinline__ void stamp(unsigned long long *trace, int i) {
+    if (trace && threadIdx.x == 0) trace[i] = global_ns();
+}
+
+// thread q < world: raise flag (rank, b) in rank q's buffer; then wait until writer q has raised (q, b) in ours
+__device__ __forceinline__ void peer_signal_and_wait(const PeerTable &pt, const MppiArgs &a, int b, int q, int rec_len,
+                                                     double *err_word) {
+    const size_t slot = (size_t)a.rank * a.g.B + b;
+    st_release_sys(peer_flags(pt.recs[q], a.world, a.g.B, rec_len) + slot, a.epoch);
+    const unsigned long long *mine = peer_flags(pt.recs[a.rank], a.world, a.g.B, rec_len) + (size_t)q * a.g.B + b;
+    const unsigned long long t0 = global_ns();
+    while (ld_acquire_sys(mine) < a.epoch) {
+        if (global_ns() - t0 > PEER_TIMEOUT_NS) {
+            *err_word = 1.0;  // rank q never delivered: the host turns this into MPC_ENCCL
+            break;
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ record merging
 // Block-wide merge of `count` records (beta_j, eta_j, E_j[H]) at src + j * stride: beta = min beta_j,
 // eta = sum s_j eta_j, Eout[t] = sum s_j E_j[t] with s_j = exp(-(beta_j - beta)/lam).  The records were written by
@@ -180,6 +230,7 @@ __device__ __forceinline__ void block_apply(const MppiArgs &a, const EnvConst<ty
         for (int i = tid; i < H * NZ; i += nt) sG[i] = g_z[(size_t)b * H * NZ + i];
     if (a.want_traj && a.goal_zero && tid < NZ) sG[tid] = 0.0;
     __syncthreads();
+    stamp(a.trace, TR_APPLIED);
     if (tid == 0 && a.want_traj)
         o[1 + H] = nominal_rollout<typename Env::Scalar>(scalar_consts(ec), H, x0g + (size_t)b * NS, sUc, sG,
                                                          a.goal_zero ? 0 : NZ, o + 2 + H);
@@ -193,7 +244,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
     mppi_solve_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec,
                       const __grid_constant__ CUtensorMap noise_map, const double *__restrict__ x0g, const double *__restrict__ g_z, double *__restrict__ Ug,
                       double *__restrict__ S_out, double *__restrict__ part, double *__restrict__ rank_part,
-                      double *__restrict__ out, int *__restrict__ done_count) {
+                      double *__restrict__ out, int *__restrict__ done_count, const PeerTable pt) {
     typedef typename Env::Vec V;
     typedef typename Env::S R;
     constexpr int NS = Env::NS, NZ = Env::NS + 1, NG = Env::NG, PACK = VT<V>::N, CH = Env::CHUNK;
@@ -212,6 +263,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
     volatile int *gen = reinterpret_cast<volatile int *>(smem_raw + RingSmem<V>::off_gen(H, S, W));
     const int rec_len = PART_HDR + H;
 
+    if (blockIdx.x == 0) stamp(a.trace, TR_START);
     // ---- this block's tile range ----------------------------------------------------------------------------
     int tile0, tile1, b_lo, b_hi;
     if (a.g.solves_per_block == 0) {
@@ -383,7 +435,8 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             if (!valid) Sk[l] = INFINITY;
             Smin = fmin(Smin, Sk[l]);
         }
-        if (PACK == 2) {
+        if (!a.store_costs) {
+        } else if (PACK == 2) {
             if (kl + 1 < a.g.K_local)
                 *reinterpret_cast<double2 *>(S_out + (size_t)b * a.g.Kpad + kl) = make_double2(Sk[0], Sk[PACK - 1]);
             else if (kl < a.g.K_local)
@@ -434,6 +487,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
 
     // ---- tail: every stage is free after this barrier; the arena is reused from offset 0 -------------------------
     __syncthreads();
+    const unsigned long long t_tiles_done = a.trace ? global_ns() : 0ull;
     __shared__ double red[32];
     __shared__ int s_last;
     double *arena = reinterpret_cast<double *>(smem_raw);
@@ -458,6 +512,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                 if (lane + 32 * i < H) rec[PART_HDR + lane + 32 * i] = E[i];
         }
         __syncthreads();
+        const unsigned long long t_a = a.trace ? global_ns() : 0ull;
         double bb = INFINITY;
         for (int i = 0; i < W; ++i) bb = fmin(bb, wrec[(size_t)i * rec_len]);
         if (tid < W) sscale[tid] = rec_scale(a.neg_inv_lam, wrec[(size_t)tid * rec_len], bb);
@@ -474,8 +529,10 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             grec[0] = bb;
             grec[1] = eta;
         }
+        const unsigned long long t_b = a.trace ? global_ns() : 0ull;
         __threadfence();
         __syncthreads();
+        const unsigned long long t_c = a.trace ? global_ns() : 0ull;
         if (tid == 0) {
             const int ticket = atomicAdd(&done_count[b], 1);
             s_last = (ticket == nb - 1);
@@ -483,11 +540,42 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
         }
         __syncthreads();
         if (!s_last) return;
+        if (a.trace && tid == 0) {
+            a.trace[TR_TILES_DONE] = t_tiles_done;
+            a.trace[9] = t_a;
+            a.trace[10] = t_b;
+            a.trace[11] = t_c;
+        }
+        stamp(a.trace, TR_TICKET);
         __threadfence();
         double beta, eta;
         block_merge(a.neg_inv_lam, H, part + (size_t)b * a.g.max_parts * rec_len, nb, (size_t)rec_len, sscale, sEw, red,
                     Eout, &beta, &eta);
-        block_apply<Env>(a, ec, b, false, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG);
+        stamp(a.trace, TR_MERGED);
+        if (a.p2p) {
+            // in-kernel all-gather of the rank records over NVLink, then the same merge over `world` records
+            for (int q = 0; q < a.world; ++q) {
+                double *dst = pt.recs[q] + ((size_t)a.rank * a.g.B + b) * rec_len;
+                for (int t = tid; t < H; t += nt) dst[PART_HDR + t] = Eout[t];
+                if (tid == 0) {
+                    dst[0] = beta;
+                    dst[1] = eta;
+                }
+            }
+            __threadfence_system();
+            __syncthreads();
+            stamp(a.trace, TR_PUBLISHED);
+            if (tid < a.world) peer_signal_and_wait(pt, a, b, tid, rec_len, out + (size_t)a.g.B * (2 + H + (H + 1) * NS));
+            __syncthreads();
+            stamp(a.trace, TR_PEERS_IN);
+            block_merge(a.neg_inv_lam, H, pt.recs[a.rank] + (size_t)b * rec_len, a.world, (size_t)a.g.B * rec_len, sscale,
+                        sEw, red, Eout, &beta, &eta);
+            stamp(a.trace, TR_MERGED2);
+            block_apply<Env>(a, ec, b, true, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG);
+        } else {
+            block_apply<Env>(a, ec, b, false, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG);
+        }
+        stamp(a.trace, TR_END);
     } else {
         // mode B: this block owns whole solves; its warps' records are in global memory (slot = warp).  One warp
         // merges one solve; then one THREAD per solve rolls out the nominal trajectory, G solves at a time.
@@ -498,25 +586,60 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             const int ng = min(G, nsolve - g0);
             for (int sl = w; sl < ng; sl += W) {
                 const int b = b_lo + g0 + sl;
+                // one warp, one solve: merge `cnt` (<= 32) records, lane j holds record j's scale
                 const double *recs = part + (size_t)b * a.g.max_parts * rec_len;
-                const double bj = (lane < W) ? recs[(size_t)lane * rec_len] : INFINITY;
-                const double beta = warp_min(bj);
-                const double sc = rec_scale(a.neg_inv_lam, bj, beta);
-                const double eta = warp_sum((lane < W) ? sc * recs[(size_t)lane * rec_len + 1] : 0.0);
-                const double inv_eta = 1.0 / eta;
-                double *U = Ug + (size_t)b * H;
-                double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
-                for (int t0 = 0; t0 < H; t0 += 32) {
-                    const int t = t0 + lane;
+                size_t rstride = rec_len;
+                int cnt = W;
+                double bj = (lane < cnt) ? recs[(size_t)lane * rstride] : INFINITY;
+                double beta = warp_min(bj);
+                double sc = rec_scale(a.neg_inv_lam, bj, beta);
+                double eta = warp_sum((lane < cnt) ? sc * recs[(size_t)lane * rstride + 1] : 0.0);
+                auto merged_row = [&](int t) {
                     double e = 0.0;
-                    for (int i = 0; i < W; ++i) {
+                    for (int i = 0; i < cnt; ++i) {
                         const double si = __shfl_sync(0xffffffffu, sc, i);
-                        if (t < H) e += si * recs[(size_t)i * rec_len + PART_HDR + t];
+                        if (t < H) e += si * __ldcg(recs + (size_t)i * rstride + PART_HDR + t);
                     }
-                    if (t < H) {
-                        if (a.record_only) {
-                            rank_part[((size_t)a.rank * a.g.B + b) * rec_len + PART_HDR + t] = e;
-                        } else {
+                    return e;
+                };
+                if (a.p2p || a.record_only) {
+                    // publish this rank's record: into every rank's exchange buffer (p2p) or into rank_part
+                    const int nq = a.p2p ? a.world : 1;
+                    for (int t0 = 0; t0 < H; t0 += 32) {
+                        const int t = t0 + lane;
+                        const double e = merged_row(t);
+                        for (int q = 0; q < nq; ++q) {
+                            double *dst = (a.p2p ? pt.recs[q] : rank_part) + ((size_t)a.rank * a.g.B + b) * rec_len;
+                            if (t < H) dst[PART_HDR + t] = e;
+                            if (t0 == 0 && lane == 0) {
+                                dst[0] = beta;
+                                dst[1] = eta;
+                            }
+                        }
+                    }
+                }
+                if (a.p2p) {
+                    __threadfence_system();
+                    __syncwarp();
+                    if (lane < a.world)
+                        peer_signal_and_wait(pt, a, b, lane, rec_len, out + (size_t)a.g.B * (2 + H + (H + 1) * NS));
+                    __syncwarp();
+                    recs = pt.recs[a.rank] + (size_t)b * rec_len;
+                    rstride = (size_t)a.g.B * rec_len;
+                    cnt = a.world;
+                    bj = (lane < cnt) ? __ldcg(recs + (size_t)lane * rstride) : INFINITY;
+                    beta = warp_min(bj);
+                    sc = rec_scale(a.neg_inv_lam, bj, beta);
+                    eta = warp_sum((lane < cnt) ? sc * __ldcg(recs + (size_t)lane * rstride + 1) : 0.0);
+                }
+                if (!a.record_only) {
+                    const double inv_eta = 1.0 / eta;
+                    double *U = Ug + (size_t)b * H;
+                    double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
+                    for (int t0 = 0; t0 < H; t0 += 32) {
+                        const int t = t0 + lane;
+                        const double e = merged_row(t);
+                        if (t < H) {
                             const double un = U[t] + inv_eta * e;  // mppi.py:62,69
                             U[t] = un;
                             o[1 + t] = un;
@@ -524,11 +647,6 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                             sUc[(size_t)sl * H + t] = fmin(fmax(un, a.lo), a.hi);
                         }
                     }
-                }
-                if (a.record_only && lane == 0) {
-                    double *rec = rank_part + ((size_t)a.rank * a.g.B + b) * rec_len;
-                    rec[0] = beta;
-                    rec[1] = eta;
                 }
                 if (!a.record_only && a.want_traj && !a.goal_zero)
                     for (int i = lane; i < H * NZ; i += 32) sG[(size_t)sl * H * NZ + i] = g_z[(size_t)b * H * NZ + i];

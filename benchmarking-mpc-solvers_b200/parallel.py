@@ -5,9 +5,11 @@ Exchange record per rank and solve (float64, length 2 + H):
     rec[0]   beta_r = min_k S_k over the rank's shard
     rec[1]   eta_r  = sum_k exp(-(S_k - beta_r) / lam)
     rec[2+t] E_r[t] = sum_k exp(-(S_k - beta_r) / lam) * eps[k][t]
-`merge_partials` is the specification of what the device does with the gathered records (mppi_finalize_kernel,
-stage 2); the transport is NCCL all-gather on the solver's stream (mpc_comm_init) or anything the caller has
-(mpc_mppi_rollout_partial / mpc_mppi_apply_partials).
+`merge_partials` is the specification of what the device does with the gathered records.  Transports, fastest first:
+  * peer memory (default): the solve kernel itself stores the record into every rank's exchange buffer over NVLink and
+    waits on flags — `connect_p2p` exchanges the buffers' IPC handles once (mpc_p2p_export / mpc_p2p_import);
+  * NCCL all-gather on the solver's stream + a merge kernel (mpc_comm_init);
+  * anything the caller has (mpc_mppi_rollout_partial / mpc_mppi_apply_partials).
 """
 import numpy as np
 
@@ -41,3 +43,19 @@ def broadcast_comm_id(create_id, group=None, src=0):
         buf = buf.to(dev)
     dist.broadcast(buf, src=src, group=group)
     return bytes(buf.cpu().tolist())
+
+
+def connect_p2p(solver, group=None):
+    """One process per GPU: all-gather the 64-byte IPC handles of the ranks' exchange buffers through
+    torch.distributed (any backend) and map them (mpc_p2p_import).  After this every solve is ONE kernel launch per
+    rank; the all-gather of the rank records happens inside it over NVLink peer memory."""
+    import torch
+    import torch.distributed as dist
+    mine = torch.tensor(list(solver.p2p_export()), dtype=torch.uint8)
+    world = dist.get_world_size(group)
+    if dist.get_backend(group) == "nccl":
+        mine = mine.to(torch.device("cuda", torch.cuda.current_device()))
+    out = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine, group=group)
+    solver.p2p_import([bytes(t.cpu().tolist()) for t in out])
+    dist.barrier(group)

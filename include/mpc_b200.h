@@ -165,6 +165,16 @@ int mpc_model_step(mpc_handle *h, int32_t n, const double *x, const double *u, c
 #define MPC_COMM_ID_BYTES 128
 int mpc_comm_create_id(void *id_out);
 int mpc_comm_init(mpc_handle *h, const void *id);
+/* The same exchange INSIDE the solve kernel, over NVLink peer memory: each rank's kernel stores its record into every
+ * rank's exchange buffer, raises a flag with a system-scope release and waits (bounded, 4 s) for the others' flags —
+ * one launch per solve, no NCCL call, no second kernel.  One process per GPU: every rank exports the 64-byte IPC
+ * handle of its buffer, the host side all-gathers them (rank-major) and every rank imports.  One process driving
+ * several GPUs: mpc_p2p_link over the `world` handles (rank-ordered).  Takes precedence over mpc_comm_init.
+ * Requires the whole grid resident (always true for batch = 1). */
+#define MPC_P2P_HANDLE_BYTES 64
+int mpc_p2p_export(mpc_handle *h, void *handle_out);
+int mpc_p2p_import(mpc_handle *h, const void *handles);
+int mpc_p2p_link(mpc_handle *const *handles, int32_t world);
 /* The same exchange with a caller-supplied transport (MPI, gloo, sockets ...), in two halves:
  * rollout_partial: rollout of this handle's K shard, block partials merged into ONE record per solve,
  *                  rec_out [batch][2+H] = (min cost, sum w, sum w*eps[0..H-1]) relative to the shard's own minimum;
@@ -188,6 +198,10 @@ int mpc_sync(mpc_handle *h);
  * mpc_get_rollout_ms returns that kernel's device time for the last solve. */
 int mpc_set_profiling(mpc_handle *h, int32_t on);
 int mpc_get_rollout_ms(mpc_handle *h, float *ms_out);
+/* With profiling on, the block that finalises an MPPI solve stamps its phases with %globaltimer (ns): out[0] kernel
+ * start, [1] all tiles done, [2] last block's ticket, [3] block records merged, [4] rank record published to the
+ * peers, [5] peers' records in, [6] rank records merged, [7] plan applied, [8] nominal rollout done (batch = 1). */
+int mpc_get_trace(mpc_handle *h, uint64_t out[16]);
 /* Number of kernel launches issued by this handle so far. */
 int64_t mpc_launch_count(const mpc_handle *h);
 /* Geometry chosen for the rollout kernel: out[0]=grid, out[1]=block, out[2]=dynamic smem bytes, out[3]=tiles,

@@ -195,6 +195,72 @@ def test_mppi_batch_of_independent_solves():
     sb.close()
 
 
+def test_mppi_batch_block_owns_solves():
+    """More solves than SMs: the solve kernel switches to 'a block owns whole solves' (per-warp records, one warp
+    merges a solve, one THREAD per nominal rollout).  Same answers as single solves and as the oracle."""
+    env, B, K, H, lam = "cartpole", 300, 200, 12, 0.5
+    rng = np.random.RandomState(5)
+    eps = rng.normal(0, 1, (K, H))
+    xs0 = START[env] + rng.normal(0, 0.2, (B, 4))
+    Us = rng.uniform(-0.3, 0.3, (B, H))
+    sb = _solver("MPPI", env, K, H, dtype="f64", lam=lam, batch=B)
+    sb.set_noise(eps)
+    u0b, Ub, xsb, cb = sb.mppi_solve(xs0, None, Us)
+    Sb = sb.mppi_costs()
+    one = _solver("MPPI", env, K, H, dtype="f64", lam=lam)
+    one.set_noise(eps)
+    m = orc.model(env)
+    for b in (0, 1, 149, 150, 299):
+        S_ref, U_ref, _ = orc.mppi_solve(m, xs0[b], Us[b], eps, lam, 1.0)
+        np.testing.assert_allclose(Sb[b], S_ref, rtol=F64_COST_RTOL)
+        tol = _plan_tol(S_ref, lam, F64_COST_RTOL)
+        np.testing.assert_allclose(Ub[b], U_ref, rtol=tol, atol=tol)
+        u1, U1, xs1, c1 = one.mppi_solve(xs0[b], None, Us[b])
+        np.testing.assert_allclose(Ub[b], U1[0], rtol=tol, atol=tol)
+        np.testing.assert_allclose(xsb[b], xs1[0], rtol=1e-9, atol=1e-9)
+        np.testing.assert_allclose(cb[b], c1[0], rtol=1e-9)
+    sb.close()
+    one.close()
+
+
+def _device_count():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.skipif(_device_count() < 2, reason="needs two GPUs (run under gpurun --gpus 2)")
+@pytest.mark.parametrize("batch", [1, 160])
+def test_mppi_peer_exchange_two_gpus(batch):
+    """K sharded over two GPUs with the all-gather of the rank records INSIDE the solve kernel (NVLink peer memory,
+    mpc_p2p_link): both ranks end with the same plan, equal to the single-GPU plan."""
+    env, K, H, lam = "pendulum", 4096 if batch == 1 else 256, 30, 0.5
+    rng = np.random.RandomState(9)
+    eps = rng.normal(0, 1, (K, H))
+    x = START[env] + rng.normal(0, 0.2, (batch, 2))
+    U = rng.uniform(-0.5, 0.5, (batch, H))
+    ref = _solver("MPPI", env, K, H, dtype="f64", lam=lam, batch=batch)
+    ref.set_noise(eps)
+    _, U_ref, xs_ref, c_ref = ref.mppi_solve(x, None, U)
+    ranks = [_solver("MPPI", env, K, H, dtype="f64", lam=lam, batch=batch, device=r, rank=r, world=2) for r in range(2)]
+    capi.Solver.p2p_link(ranks)
+    for s in ranks:
+        s.set_noise(eps)
+    for rep in range(3):  # epochs advance; plans restart from the same U
+        for s in ranks:
+            s.upload_inputs(x, None, U)
+        for s in ranks:
+            s.solve_enqueue()
+        outs = [s.download_outputs() for s in ranks]
+        assert np.array_equal(outs[0][1], outs[1][1])
+        np.testing.assert_allclose(outs[0][1], U_ref, rtol=1e-11, atol=1e-11)
+        np.testing.assert_allclose(outs[0][2], xs_ref, rtol=1e-9, atol=1e-9)
+    for s in ranks + [ref]:
+        s.close()
+
+
 def test_mppi_full_size_properties():
     """BASELINE full size (K = 2^20, H = 50, float32, Philox): size-independent properties.
        (1) sample k's cost depends only on (seed, k): the first 4096 costs equal a K = 4096 solve's costs bit for bit;
