@@ -105,7 +105,11 @@ class _GpuAgent(Agent):
             seed=params.get("seed", 0), resample=params.get("resample", False),
             fast_math=params.get("fast_math", False), lanes=params.get("lanes", 0), **kw)
         if params.get("world", 1) > 1:
-            self._solver.comm_init(params["comm_id"])
+            if "comm_id" in params:   # NCCL all-gather + merge kernel (MPPI)
+                self._solver.comm_init(params["comm_id"])
+            else:                     # exchange inside the kernels over NVLink peer memory (MPPI and CEM)
+                from . import parallel
+                parallel.connect_p2p(self._solver)
         self._traj = None  # (x, clipped plan, g_z) -> (xs, cost) produced by the last solve
 
     def _remember_trajectory(self, x, U, g_z, xs, cost):

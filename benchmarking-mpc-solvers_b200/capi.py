@@ -232,8 +232,11 @@ class Solver:
         ua, up = _in(U_in, (self.H,))
         self._ck(self.L.mpc_cem_begin(self._h, xp, gp, up))
 
-    def cem_iterate(self, z=None):
+    def cem_iterate(self, z=None, wait=True):
         za, zp = _in(z, (self.K, self.H))
+        if not wait:  # enqueue only (several ranks driven by one thread)
+            self._ck(self.L.mpc_cem_iterate(self._h, zp, None))
+            return None
         done = C.c_int32(0)
         self._ck(self.L.mpc_cem_iterate(self._h, zp, C.byref(done)))
         return bool(done.value)

@@ -97,6 +97,8 @@ struct mpc_handle {
     int *d_elite = nullptr, *d_sel = nullptr;
     int cem_iter = 0;
     bool cem_open = false;
+    int cem_n_cand = 0;           // candidates per rank and iteration (multi-GPU)
+    int cem_z_stride = 0;         // row stride of the standard-normal tensor
     // host (pinned)
     double *h_in = nullptr, *h_out = nullptr;
     size_t in_elems = 0, out_elems = 0, out_stride = 0;
@@ -282,6 +284,12 @@ static CemArgs cem_args(const mpc_handle *h, int iter, int want_traj) {
     a.iter = iter;
     a.seed = h->cfg.seed + 0x9E3779B97F4A7C15ull * (h->cfg.resample ? h->solves : 0);
     a.want_traj = want_traj;
+    a.world = h->cfg.world;
+    a.rank = h->cfg.rank;
+    a.n_cand = h->cem_n_cand;
+    a.z_stride = h->cem_z_stride;
+    a.z_off = h->cfg.world > 1 ? h->g.k_begin : 0;
+    a.epoch = h->epoch;
     return a;
 }
 
@@ -297,6 +305,8 @@ static CemBuffers cem_bufs(const mpc_handle *h) {
     b.elite_idx = h->d_elite;
     b.sel = h->d_sel;
     b.out = h->d_out;
+    b.peer_recs = h->peer_recs;
+    b.err_word = h->d_out + (size_t)h->g.B * h->out_stride + 1;
     return b;
 }
 
@@ -391,7 +401,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     if (cfg->agent == MPC_AGENT_MPPI && !(cfg->lam > 0)) return fail(nullptr, MPC_EINVAL, "lam must be > 0");
     if (cfg->agent == MPC_AGENT_CEM) {
         if (cfg->batch != 1) return fail(nullptr, MPC_EINVAL, "CEM supports batch = 1");
-        if (cfg->world != 1) return fail(nullptr, MPC_EINVAL, "CEM is single-GPU in this version");
+        if (cfg->world > 16) return fail(nullptr, MPC_EINVAL, "CEM shards over at most 16 GPUs");
         if (cfg->n_elite < 1 || cfg->n_elite > cfg->K)
             return fail(nullptr, MPC_EINVAL, "n_elite = %d must be in [1, K]", cfg->n_elite);
         if (cfg->max_iter < 1) return fail(nullptr, MPC_EINVAL, "max_iter must be >= 1");
@@ -527,7 +537,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     const size_t rec = PART_HDR + g.H;
     h->out_stride = 2 + g.H + (size_t)(g.H + 1) * h->ns;
     h->in_elems = off_U(h) + (size_t)g.B * g.H;
-    h->out_elems = (size_t)g.B * h->out_stride + 1;
+    h->out_elems = (size_t)g.B * h->out_stride + 2;  // + CEM iterations / MPPI peer error, + CEM peer error
     CUC(cudaMalloc(&h->d_in, h->in_elems * sizeof(double)));
     CUC(cudaMemsetAsync(h->d_in, 0, h->in_elems * sizeof(double), h->stream));  // planned_us = zeros (mppi.py:14)
     CUC(cudaMalloc(&h->d_out, h->out_elems * sizeof(double)));
@@ -536,9 +546,18 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     CUC(cudaMallocHost(&h->h_out, h->out_elems * sizeof(double)));
     memset(h->h_in, 0, h->in_elems * sizeof(double));
     h->g_zero_on_device = true;
+    // CEM over several GPUs: elites are global, so the standard normals of an iteration (TENSOR noise) are resident in
+    // full on every rank; candidates per rank and iteration = min(n_elite, largest shard)
+    h->cem_z_stride = g.Kpad;
+    if (cfg->agent == MPC_AGENT_CEM && cfg->world > 1) {
+        h->cem_z_stride = (cfg->K + TILE - 1) / TILE * TILE;
+        const int shard_max = (cfg->K + cfg->world - 1) / cfg->world;
+        h->cem_n_cand = cfg->n_elite < shard_max ? cfg->n_elite : shard_max;
+    }
     if (cfg->noise == MPC_NOISE_TENSOR) {
-        CUC(cudaMalloc(&h->d_noise, (size_t)g.H * g.Kpad * esz));
-        CUC(cudaMemsetAsync(h->d_noise, 0, (size_t)g.H * g.Kpad * esz, h->stream));
+        const size_t cols = cfg->agent == MPC_AGENT_CEM ? (size_t)h->cem_z_stride : (size_t)g.Kpad;
+        CUC(cudaMalloc(&h->d_noise, (size_t)g.H * cols * esz));
+        CUC(cudaMemsetAsync(h->d_noise, 0, (size_t)g.H * cols * esz, h->stream));
         if (cfg->agent == MPC_AGENT_MPPI) {
             const int rc = encode_noise_map(h);
             if (rc) {
@@ -675,11 +694,12 @@ static int fetch_outputs(mpc_handle *h, int want_traj, double *u0, double *U_out
         CU(h, cudaMemcpy2DAsync(h->h_out, h->out_stride * sizeof(double), h->d_out, h->out_stride * sizeof(double),
                                 per * sizeof(double), g.B, cudaMemcpyDeviceToHost, h->stream));
     }
-    if (h->p2p_ready)  // the peer wait's error word lives behind the last solve's outputs
-        CU(h, cudaMemcpyAsync(h->h_out + (size_t)g.B * h->out_stride, h->d_out + (size_t)g.B * h->out_stride,
-                              sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    // the peer waits' error words live behind the last solve's outputs: slot 0 MPPI (CEM: iterations), slot 1 CEM
+    const size_t err_at = (size_t)g.B * h->out_stride + (h->cfg.agent == MPC_AGENT_CEM ? 1 : 0);
+    if (h->p2p_ready)
+        CU(h, cudaMemcpyAsync(h->h_out + err_at, h->d_out + err_at, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
-    if (h->p2p_ready && h->h_out[(size_t)g.B * h->out_stride] != 0.0)
+    if (h->p2p_ready && h->h_out[err_at] != 0.0)
         return fail(h, MPC_ENCCL, "peer exchange timed out: a rank did not deliver its record within 4 s");
     for (int b = 0; b < g.B; ++b) {
         const double *o = h->h_out + (size_t)b * h->out_stride;
@@ -776,6 +796,11 @@ int mpc_mppi_get_costs(mpc_handle *h, double *S_out) {
 
 // ---------------------------------------------------------------------------------------------- CEM
 static int cem_enqueue_iter(mpc_handle *h, int iter) {
+    if (h->cfg.world > 1) {
+        if (!h->p2p_ready)
+            return fail(h, MPC_ESTATE, "world > 1: connect the ranks' exchange buffers first (mpc_p2p_import / mpc_p2p_link)");
+        h->epoch++;
+    }
     const CemArgs a = cem_args(h, iter, 0);
     const CemBuffers b = cem_bufs(h);
     CU(h, launch_cem_rollout(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
@@ -806,21 +831,24 @@ int mpc_cem_iterate(mpc_handle *h, const double *z_KH, int32_t *done) {
     const Geometry &g = h->g;
     if (h->cfg.noise == MPC_NOISE_TENSOR) {
         if (!z_KH) return fail(h, MPC_EINVAL, "TENSOR noise mode needs the standard normals of this iteration");
-        const size_t n = (size_t)g.K_local * g.H;
+        // one GPU: this handle's shard; several GPUs: all K samples (the elite refit reads any sample's normals)
+        const int cols = h->cfg.world > 1 ? h->cfg.K : g.K_local;
+        const size_t n = (size_t)cols * g.H;
         int rc = ensure_scratch(h, n);
         if (rc) return rc;
-        CU(h, cudaMemcpyAsync(h->d_scratch, z_KH + (size_t)g.k_begin * g.H, n * sizeof(double), cudaMemcpyHostToDevice,
-                              h->stream));
-        CU(h, launch_transpose_noise(h->cfg.dtype, h->d_scratch, h->d_noise, g.K_local, g.Kpad, g.H, h->stream));
+        CU(h, cudaMemcpyAsync(h->d_scratch, z_KH + (h->cfg.world > 1 ? 0 : (size_t)g.k_begin * g.H), n * sizeof(double),
+                              cudaMemcpyHostToDevice, h->stream));
+        CU(h, launch_transpose_noise(h->cfg.dtype, h->d_scratch, h->d_noise, cols, h->cem_z_stride, g.H, h->stream));
         h->launches++;
     }
     int rc = cem_enqueue_iter(h, h->cem_iter);
     if (rc) return rc;
     h->cem_iter++;
+    if (!done) return MPC_OK;  // enqueue only: the caller synchronises later (ranks driven by one thread)
     int sel[2] = {0, 0};
     CU(h, cudaMemcpyAsync(sel, h->d_sel, sizeof sel, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
-    if (done) *done = sel[0];
+    *done = sel[0];
     return MPC_OK;
 }
 
@@ -840,6 +868,8 @@ static int cem_finish(mpc_handle *h, int want_traj, double *u0, double *U_out, d
     }
     h->last_iters = (int)o[h->out_stride];
     if (iters_out) *iters_out = h->last_iters;
+    if (o[h->out_stride + 1] != 0.0)
+        return fail(h, MPC_ENCCL, "peer exchange timed out: a rank did not deliver its elite candidates within 4 s");
     h->cem_open = false;
     h->solves++;
     return MPC_OK;
@@ -979,8 +1009,16 @@ int mpc_comm_init(mpc_handle *h, const void *id_bytes) {
 // driving several GPUs: mpc_p2p_link.
 static int xchg_alloc(mpc_handle *h) {
     if (h->d_xchg) return MPC_OK;
-    if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "peer exchange is an MPPI feature");
     if (h->cfg.world > 16) return fail(h, MPC_EINVAL, "peer exchange supports up to 16 ranks");
+    if (h->cfg.agent == MPC_AGENT_CEM) {
+        // candidate pairs [world][n_cand] of (u64 key, u64 global index), then u64 flags [world]
+        CU(h, cudaSetDevice(h->cfg.device));
+        const size_t n = (size_t)h->cfg.world * (h->cem_n_cand > 0 ? h->cem_n_cand : 1);
+        const size_t bytes = n * 16 + (size_t)h->cfg.world * 8;
+        CU(h, cudaMalloc(&h->d_xchg, bytes));
+        CU(h, cudaMemset(h->d_xchg, 0, bytes));
+        return MPC_OK;
+    }
     // mode A blocks wait for their peers while holding an SM: every block of the grid must be resident
     if (h->g.solves_per_block == 0 && h->g.grid > h->num_sms)
         return fail(h, MPC_ESTATE, "peer exchange needs the whole grid resident (batch %d too large for K %d); use NCCL",

@@ -2,6 +2,7 @@
 // float32 / float64 switch over the two compilations of kernels.cu.
 #include "kernels.cuh"
 #include "philox.cuh"
+#include "peer.cuh"
 
 namespace mpc {
 
@@ -47,29 +48,27 @@ __device__ __forceinline__ int block_scan_excl(int v, int *swarp, int *total) {
     return base + inc - v;
 }
 
-// Radix select of the n_elite largest keys (np.argsort(-rewards)[:n_elite], cem.py:67) by one block:
-// 8 passes of 8 bits from the top find the n_elite-th largest key T; then an ordered compaction emits, ascending by
-// index, every k with key > T plus the lowest-index keys equal to T needed to reach n_elite.
-__global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const unsigned long long *__restrict__ keys,
-                                                         int *__restrict__ elite_hist, int *__restrict__ sel) {
-    if (sel[SEL_DONE]) return;
-    __shared__ int hist[256];
-    __shared__ int swarp[64];
-    __shared__ unsigned long long s_prefix;
-    __shared__ int s_want;
-    const int K = a.g.K_local, tid = threadIdx.x;
+// Radix select of the `want` largest of n keys by one block of 1024 threads (np.argsort(-rewards)[:n_elite],
+// cem.py:67): 8 passes of 8 bits from the top find the want-th largest key T; then an ordered compaction emits, in
+// ascending position, every key > T plus the lowest-position keys equal to T needed to reach `want`.
+// key(i) reads key i; emit(pos, i) receives output slot pos for input position i.  Returns the number emitted.
+template <class KeyFn, class EmitFn>
+__device__ __forceinline__ void radix_select_block(const int n, const int want_total, KeyFn key_at, EmitFn emit, int *hist,
+                                                   int *swarp, unsigned long long *s_prefix, int *s_want) {
+    const int tid = threadIdx.x;
+    __syncthreads();
     if (tid == 0) {
-        s_prefix = 0ull;
-        s_want = a.n_elite;
+        *s_prefix = 0ull;
+        *s_want = want_total;
     }
     unsigned long long mask = 0ull;
     for (int shift = 56; shift >= 0; shift -= 8) {
         if (tid < 256) hist[tid] = 0;
         __syncthreads();
-        const unsigned long long prefix = s_prefix;
-        const int want = s_want;
-        for (int k = tid; k < K; k += blockDim.x) {
-            const unsigned long long key = keys[k];
+        const unsigned long long prefix = *s_prefix;
+        const int want = *s_want;
+        for (int k = tid; k < n; k += blockDim.x) {
+            const unsigned long long key = key_at(k);
             if ((key & mask) == prefix) atomicAdd(&hist[(int)((key >> shift) & 0xffull)], 1);
         }
         __syncthreads();
@@ -78,29 +77,85 @@ __global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const
         int total;
         const int excl = block_scan_excl(v, swarp, &total);
         if (tid < 256 && excl < want && excl + v >= want) {
-            s_prefix = prefix | ((unsigned long long)(255 - tid) << shift);
-            s_want = want - excl;
+            *s_prefix = prefix | ((unsigned long long)(255 - tid) << shift);
+            *s_want = want - excl;
         }
         mask |= 0xffull << shift;
         __syncthreads();
     }
-    const unsigned long long T = s_prefix;
-    const int want_ties = s_want;  // how many keys == T belong to the elite set
-    int *elite = elite_hist + (size_t)a.iter * a.n_elite;
+    const unsigned long long T = *s_prefix;
+    const int want_ties = *s_want;  // how many keys == T belong to the selection
     int tie_base = 0, sel_base = 0;
-    for (int k0 = 0; k0 < K; k0 += blockDim.x) {
+    for (int k0 = 0; k0 < n; k0 += blockDim.x) {
         const int k = k0 + tid;
-        const unsigned long long key = (k < K) ? keys[k] : 0ull;
-        const int is_tie = (k < K && key == T) ? 1 : 0;
-        const int is_gt = (k < K && key > T) ? 1 : 0;
+        const unsigned long long key = (k < n) ? key_at(k) : 0ull;
+        const int is_tie = (k < n && key == T) ? 1 : 0;
+        const int is_gt = (k < n && key > T) ? 1 : 0;
         int tot_tie, tot_sel;
         const int tie_rank = tie_base + block_scan_excl(is_tie, swarp, &tot_tie);
         const int chosen = is_gt | (is_tie && tie_rank < want_ties);
         const int pos = sel_base + block_scan_excl(chosen, swarp, &tot_sel);
-        if (chosen && pos < a.n_elite) elite[pos] = k;
+        if (chosen && pos < want_total) emit(pos, k);
         tie_base += tot_tie;
         sel_base += tot_sel;
     }
+    __syncthreads();
+}
+
+// Elite selection of one CEM iteration.  Single GPU: the n_elite best of this handle's K keys.
+// K sharded over `world` GPUs: (1) the n_cand = min(n_elite, K_local) best LOCAL samples become candidates
+// (key, global index), (2) the candidate lists are all-gathered INSIDE this kernel over NVLink peer memory (peer.cuh:
+// store into every rank's exchange buffer, flag, bounded wait), (3) every rank selects the same global n_elite from
+// the world * n_cand candidates.  Candidate lists are ascending in global index and ranks own ascending shards, so
+// "ties by lowest position" is "ties by lowest global index" in both cases.
+// Exchange buffer of a rank: pairs [world][n_cand] of (u64 key, u64 global index), then u64 flags [world].
+__global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const unsigned long long *__restrict__ keys,
+                                                         int *__restrict__ elite_hist, int *__restrict__ sel,
+                                                         const PeerTable pt, double *__restrict__ err_word) {
+    if (sel[SEL_DONE]) return;
+    __shared__ int hist[256];
+    __shared__ int swarp[64];
+    __shared__ unsigned long long s_prefix;
+    __shared__ int s_want;
+    const int tid = threadIdx.x;
+    int *elite = elite_hist + (size_t)a.iter * a.n_elite;
+    if (a.world == 1) {
+        radix_select_block(a.g.K_local, a.n_elite, [&](int k) { return keys[k]; },
+                           [&](int pos, int k) { elite[pos] = k; }, hist, swarp, &s_prefix, &s_want);
+        return;
+    }
+    const int n_cand = a.n_cand;
+    unsigned long long *mine = reinterpret_cast<unsigned long long *>(pt.recs[a.rank]);
+    unsigned long long *my_slot = mine + (size_t)a.rank * n_cand * 2;
+    const int n_local = min(a.n_elite, a.g.K_local);
+    for (int i = n_local + tid; i < n_cand; i += blockDim.x) {  // padding: sorts below everything
+        my_slot[2 * i] = 0ull;
+        my_slot[2 * i + 1] = 0x7fffffffull;
+    }
+    radix_select_block(a.g.K_local, n_local, [&](int k) { return keys[k]; },
+                       [&](int pos, int k) {
+                           my_slot[2 * pos] = keys[k];
+                           my_slot[2 * pos + 1] = (unsigned long long)(a.g.k_begin + k);
+                       },
+                       hist, swarp, &s_prefix, &s_want);
+    // all-gather: copy my candidate list into every peer's slot [rank]
+    for (int q = 0; q < a.world; ++q) {
+        if (q == a.rank) continue;
+        unsigned long long *dst = reinterpret_cast<unsigned long long *>(pt.recs[q]) + (size_t)a.rank * n_cand * 2;
+        for (int i = tid; i < 2 * n_cand; i += blockDim.x) dst[i] = my_slot[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < a.world) {
+        unsigned long long *theirs =
+            reinterpret_cast<unsigned long long *>(pt.recs[tid]) + (size_t)a.world * n_cand * 2 + a.rank;
+        peer_flag_exchange(theirs, mine + (size_t)a.world * n_cand * 2 + tid, a.epoch, err_word);
+    }
+    __syncthreads();
+    const int n_all = a.world * n_cand;
+    radix_select_block(n_all, a.n_elite, [&](int i) { return __ldcg(mine + 2 * i); },
+                       [&](int pos, int i) { elite[pos] = (int)__ldcg(mine + 2 * i + 1); }, hist, swarp, &s_prefix,
+                       &s_want);
 }
 
 __global__ void cem_reset_kernel(const CemArgs a, double *__restrict__ sd, int *__restrict__ sel) {
@@ -165,7 +220,9 @@ cudaError_t launch_cem_rollout(int dtype, int noise, int variant, const EnvParam
     return BY_DTYPE(launch_cem_rollout, noise, variant, ep, a, b, s);
 }
 cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
-    cem_select_kernel<<<1, 1024, 0, s>>>(a, b.keys, b.elite_idx, b.sel);
+    PeerTable pt;
+    for (int r = 0; r < MAX_WORLD; ++r) pt.recs[r] = (a.world > 1 && r < a.world) ? b.peer_recs[r] : nullptr;
+    cem_select_kernel<<<1, 1024, 0, s>>>(a, b.keys, b.elite_idx, b.sel, pt, b.err_word);
     return cudaGetLastError();
 }
 cudaError_t launch_cem_refit(int dtype, int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {

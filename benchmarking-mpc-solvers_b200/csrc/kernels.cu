@@ -9,6 +9,7 @@
 #include "kernels.cuh"
 #include "envs.cuh"
 #include "philox.cuh"
+#include "peer.cuh"
 
 #include <cuda.h>  // CUtensorMap (type only; the encoder is resolved at run time in capi.cu)
 #include <float.h>
@@ -207,7 +208,7 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
     double reward = 0.0;
     if (NOISE == NOISE_TENSOR) {
         for (int t = 0; t < H; ++t) {
-            const R z = zt[(size_t)t * a.g.Kpad + k];
+            const R z = zt[(size_t)t * a.z_stride + a.z_off + k];
             const R u = vclip(vfma(ssd[t], z, smu[t]), lo, hi);
             reward += -(double)Env::step(ec, x, u, gs);
         }
@@ -241,13 +242,13 @@ __global__ void __launch_bounds__(128) cem_refit_kernel(const CemArgs a, const R
     const int *elite = elite_hist + (size_t)a.iter * n;
     const R m0 = (R)mu[t], s0 = (R)sd[t], lo = (R)a.lo, hi = (R)a.hi;
     auto sample = [&](int e) -> double {
-        const int k = elite[e];
+        const int k = elite[e];  // GLOBAL sample index (== local index on one GPU)
         R z;
         if (NOISE == NOISE_TENSOR) {
-            z = zt[(size_t)t * a.g.Kpad + k];
+            z = zt[(size_t)t * a.z_stride + (a.world > 1 ? k : a.z_off + k)];
         } else {
             float z4[4];
-            philox_normal4(a.seed, 1u, (uint32_t)a.iter, (uint32_t)(a.g.k_begin + k), (uint32_t)(t >> 2), z4);
+            philox_normal4(a.seed, 1u, (uint32_t)a.iter, (uint32_t)(a.world > 1 ? k : a.g.k_begin + k), (uint32_t)(t >> 2), z4);
             z = (R)z4[t & 3];
         }
         return (double)vclip(vfma(s0, z, m0), lo, hi);  // identical expression to the rollout's

@@ -67,6 +67,12 @@ struct CemArgs {
     int iter;             // iteration index (Philox draw, history slot)
     uint64_t seed;
     int want_traj;
+    // K sharded over several GPUs: elite indices are GLOBAL sample indices
+    int world, rank;
+    int n_cand;           // candidates a rank contributes per iteration: min(n_elite, largest K_local)
+    int z_stride;         // row stride of the standard-normal tensor (TENSOR noise): Kpad, or the padded FULL K
+    int z_off;            // column of this rank's first sample in it: 0, or k_begin
+    unsigned long long epoch;  // flag value of this iteration's candidate exchange
 };
 
 struct MppiBuffers {
@@ -94,6 +100,8 @@ struct CemBuffers {
     int *elite_idx;        // [max_iter][n_elite]
     int *sel;              // scratch: [0]=done flag, [1]=iters executed, [2]=elite counter, ...
     double *out;           // u0, U[H], cost, xs
+    double *const *peer_recs;  // host array [world] of the ranks' exchange buffers (world > 1)
+    double *err_word;      // set when a peer did not deliver in time
 };
 
 // launches (kernels.cu); all return cudaGetLastError()

@@ -97,30 +97,10 @@ __device__ __forceinline__ double rec_scale(double neg_inv_lam, double bj, doubl
 }
 
 // ------------------------------------------------------------------------------------------------ peer exchange
-// Multi-GPU: every rank's solve kernel writes its (beta, eta, E[H]) record straight into the exchange buffer of EVERY
-// rank over NVLink (peer-mapped pointers), raises that rank's flag for (writer, solve) to the solve's epoch with a
-// system-scope release store, then waits for the flags of all writers in its own buffer: an all-gather inside the
-// kernel, no NCCL launch and no second kernel.  The wait is bounded (PEER_TIMEOUT_NS) and reports through an error
-// word instead of hanging.
-constexpr int MAX_WORLD = 16;
-struct PeerTable {
-    double *recs[MAX_WORLD];  // recs[r]: rank r's exchange buffer [world][B][2+H] doubles, then u64 flags [world][B]
-};
-constexpr unsigned long long PEER_TIMEOUT_NS = 4000000000ull;
-
-__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned long long global_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    return t;
-}
+// Multi-GPU (peer.cuh): every rank's solve kernel writes its (beta, eta, E[H]) record straight into the exchange
+// buffer of EVERY rank over NVLink, raises that rank's flag for (writer, solve) to the solve's epoch and waits for the
+// flags of all writers in its own buffer: an all-gather inside the kernel, no NCCL launch and no second kernel.
+// Buffer layout: records [world][B][2+H] doubles, then u64 flags [world][B].
 __device__ __forceinline__ unsigned long long *peer_flags(double *recs, int world, int B, int rec_len) {
     return reinterpret_cast<unsigned long long *>(recs + (size_t)world * B * rec_len);
 }
@@ -135,15 +115,8 @@ __device__ __forceinline__ void stamp(unsigned long long *trace, int i) {
 __device__ __forceinline__ void peer_signal_and_wait(const PeerTable &pt, const MppiArgs &a, int b, int q, int rec_len,
                                                      double *err_word) {
     const size_t slot = (size_t)a.rank * a.g.B + b;
-    st_release_sys(peer_flags(pt.recs[q], a.world, a.g.B, rec_len) + slot, a.epoch);
-    const unsigned long long *mine = peer_flags(pt.recs[a.rank], a.world, a.g.B, rec_len) + (size_t)q * a.g.B + b;
-    const unsigned long long t0 = global_ns();
-    while (ld_acquire_sys(mine) < a.epoch) {
-        if (global_ns() - t0 > PEER_TIMEOUT_NS) {
-            *err_word = 1.0;  // rank q never delivered: the host turns this into MPC_ENCCL
-            break;
-        }
-    }
+    peer_flag_exchange(peer_flags(pt.recs[q], a.world, a.g.B, rec_len) + slot,
+                       peer_flags(pt.recs[a.rank], a.world, a.g.B, rec_len) + (size_t)q * a.g.B + b, a.epoch, err_word);
 }
 
 // ------------------------------------------------------------------------------------------------ record merging

@@ -29,6 +29,25 @@ def merge_partials(recs, lam):
     return beta, eta, erg
 
 
+def local_candidates(rewards, k_begin, n_elite):
+    """CEM over shards, step 1 (specification of cem_select_kernel's first half): a rank's min(n_elite, K_local) best
+    samples as (reward, global index) pairs, ascending in global index; ties at the threshold go to the lowest index."""
+    rewards = np.asarray(rewards, dtype=np.float64)
+    n = min(n_elite, len(rewards))
+    order = np.lexsort((np.arange(len(rewards)), -rewards))[:n]   # by reward descending, then index ascending
+    order.sort()
+    return rewards[order], order + k_begin
+
+
+def select_global_elites(cand_rewards, cand_index, n_elite):
+    """Step 2, identical on every rank after the all-gather (rank-major concatenation): the n_elite best candidates,
+    ties by lowest global index; returns their global indices in ascending order."""
+    r = np.concatenate([np.asarray(c, dtype=np.float64) for c in cand_rewards])
+    idx = np.concatenate([np.asarray(c, dtype=np.int64) for c in cand_index])
+    order = np.lexsort((idx, -r))[:n_elite]
+    return np.sort(idx[order])
+
+
 def broadcast_comm_id(create_id, group=None, src=0):
     """Rank `src` creates the communicator id (bytes), everybody receives it through torch.distributed (any backend)."""
     import torch

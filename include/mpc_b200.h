@@ -134,7 +134,10 @@ int mpc_mppi_get_costs(mpc_handle *h, double *S_out);
  * begin: std = self.std.copy() (cem.py:56); mean = planned_us (U_in [batch][H], NULL = device-resident). */
 int mpc_cem_begin(mpc_handle *h, const double *x, const double *g_z, const double *U_in);
 /* One refit iteration (cem.py:58-76).  z_KH: TENSOR mode, standard normals [K][H] float64 such that
- * np.random.normal(mean, std) == mean + std*z; NULL in PHILOX mode.  *done = 1 when every std < epsilon. */
+ * np.random.normal(mean, std) == mean + std*z; NULL in PHILOX mode.  *done = 1 when every std < epsilon;
+ * done == NULL only enqueues the iteration (no synchronisation; later iterations are no-ops once the device-side
+ * flag is set).  With world > 1 (K sharded, mpc_p2p_* connected) pass the FULL [K][H] array on every rank: elites
+ * are global and the refit reads any sample's normals; elite indices reported by mpc_cem_get_elites are global. */
 int mpc_cem_iterate(mpc_handle *h, const double *z_KH, int32_t *done);
 /* Result: u0 = planned_us[0] (cem.py:77), U_out = planned_us, xs/cost as for MPPI. */
 int mpc_cem_end(mpc_handle *h, double *u0, double *U_out, double *xs_out, double *cost_out);

@@ -261,6 +261,51 @@ def test_mppi_peer_exchange_two_gpus(batch):
         s.close()
 
 
+@pytest.mark.skipif(_device_count() < 2, reason="needs two GPUs (run under gpurun --gpus 2)")
+@pytest.mark.parametrize("noise", ["tensor", "philox"])
+def test_cem_sharded_two_gpus(noise):
+    """CEM with K sharded over two GPUs: local candidates, all-gather inside the select kernel (peer memory), the
+    same global elite set and refit on both ranks == the single-GPU solve (and the oracle for host noise)."""
+    env, K, H, iters, n_elite = "cartpole", 1000, 20, 4, 100
+    rng = np.random.RandomState(21)
+    x = START[env] + rng.normal(0, 0.1, 4)
+    z = rng.standard_normal((iters, K, H))
+    kw = dict(dtype="f64", noise=noise, sigma=1.0, max_iter=iters, n_elite=n_elite, epsilon=1e-5, alpha=0.2, seed=3)
+    one = _solver("CEM", env, K, H, **kw)
+    ranks = [_solver("CEM", env, K, H, device=r, rank=r, world=2, **kw) for r in range(2)]
+    capi.Solver.p2p_link(ranks)
+    if noise == "tensor":
+        one.cem_begin(x, None, np.zeros(H))
+        for s in ranks:
+            s.cem_begin(x, None, np.zeros(H))
+        for it in range(iters):
+            one.cem_iterate(z[it])
+            for s in ranks:
+                s.cem_iterate(z[it], wait=False)
+        ref_out = one.cem_end()
+        outs = [s.cem_end() for s in ranks]
+        ref = orc.cem_solve(orc.model(env), x, np.zeros(H), z, n_elite, 1e-5, 0.2, 1.0)
+        np.testing.assert_allclose(outs[0][1], ref["mu"], rtol=1e-10, atol=1e-12)
+        for it in range(iters):
+            assert np.array_equal(np.sort(ranks[0].cem_elites(it)), ref["elites"][it])
+    else:
+        one.upload_inputs(x, None, np.zeros(H))
+        one.solve_enqueue()
+        ref_out = one.download_outputs()
+        for s in ranks:
+            s.upload_inputs(x, None, np.zeros(H))
+        for s in ranks:
+            s.solve_enqueue()
+        outs = [s.download_outputs() for s in ranks]
+    assert np.array_equal(outs[0][1], outs[1][1])                      # both ranks: the same plan, bit for bit
+    np.testing.assert_allclose(np.ravel(outs[0][1]), np.ravel(ref_out[1]), rtol=1e-12, atol=1e-12)
+    for it in range(iters):
+        assert np.array_equal(np.sort(ranks[0].cem_elites(it)), np.sort(one.cem_elites(it)))
+        assert np.array_equal(ranks[0].cem_elites(it), ranks[1].cem_elites(it))
+    for s in ranks + [one]:
+        s.close()
+
+
 def test_mppi_full_size_properties():
     """BASELINE full size (K = 2^20, H = 50, float32, Philox): size-independent properties.
        (1) sample k's cost depends only on (seed, k): the first 4096 costs equal a K = 4096 solve's costs bit for bit;

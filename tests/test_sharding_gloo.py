@@ -75,3 +75,51 @@ def test_two_rank_exchange_reproduces_single_solve(env, K, H, lam):
     for _, _, _, U_rank in results:
         np.testing.assert_allclose(U_rank, U_ref, rtol=1e-10, atol=1e-12)
     np.testing.assert_array_equal(results[0][3], results[1][3])   # every rank ends with the same plan
+
+
+def _cem_worker(rank, world, port, K, n_elite, out_q):
+    import sys
+    sys.path.insert(0, ROOT)
+    import mpc_b200  # noqa: F401
+    from mpc_b200 import parallel
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.RandomState(1)
+    rewards = np.round(rng.normal(0, 1, K), 1)          # rounded: plenty of ties, also at the threshold
+    k0, k1 = parallel.shard_range(K, rank, world)
+    r, idx = parallel.local_candidates(rewards[k0:k1], k0, n_elite)
+    n_cand = min(n_elite, -(-K // world))                # equal-sized contributions: pad like the kernel does
+    rp = np.full(n_cand, -np.inf)
+    ip = np.full(n_cand, np.iinfo(np.int32).max, dtype=np.int64)
+    rp[:len(r)], ip[:len(idx)] = r, idx
+    gr = [torch.zeros(n_cand, dtype=torch.float64) for _ in range(world)]
+    gi = [torch.zeros(n_cand, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(gr, torch.from_numpy(rp))
+    dist.all_gather(gi, torch.from_numpy(ip))
+    elites = parallel.select_global_elites([t.numpy() for t in gr], [t.numpy() for t in gi], n_elite)
+    out_q.put((rank, elites))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("K,n_elite", [(1001, 100), (64, 64), (300, 200)])
+def test_two_rank_cem_candidates_reproduce_global_topk(K, n_elite):
+    """The CEM exchange protocol (local candidates -> all-gather -> identical global select) picks exactly the
+    n_elite best samples of the whole population with ties broken by lowest index, on every rank."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_cem_worker, args=(r, world, port, K, n_elite, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    rng = np.random.RandomState(1)
+    rewards = np.round(rng.normal(0, 1, K), 1)
+    want = np.sort(np.lexsort((np.arange(K), -rewards))[:n_elite])
+    for _, elites in results:
+        np.testing.assert_array_equal(elites, want)
