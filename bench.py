@@ -39,7 +39,23 @@ WORKLOADS = {
     "mppi_pendulum_h50_k65536": ("MPPI", "pendulum", 65536, 50, dict(lam=0.5, sigma=1.0)),
 }
 DEFAULT_WORKLOAD = "mppi_acrobot_h100_k1m"
+# float32 rollout flavour quoted per env: (fast_math, lanes).  fast_math = MUFU.SIN/COS instead of the polynomial sincos;
+# it is used where EVERY per-sample cost stays within the north_star's rel 1e-5 of the float64 oracle
+# (tests/test_gpu_parity.py::test_mppi_mufu_trig_flavour_meets_the_float32_bar, tools/variant_probe.py): Pendulum and
+# Acrobot.  CartPole keeps the polynomial (its chaotic tail leaves no margin).  lanes: Acrobot's MUFU flavour is XU-pipe
+# bound and runs best one sample per thread with 16 warps; the others use packed f32x2.
+FLAVOUR = {"acrobot": (1, 1), "pendulum": (1, 2), "cartpole": (0, 2)}
 L2_BYTES = 126 << 20
+
+
+def ncu_evidence(workload, fast_math, lanes):
+    """Per-launch DRAM traffic and pipe utilisation of the solve kernel from the committed ncu --set full captures
+    (profiles/ncu_evidence.json, written from the raw pages by tools/ncu_summary.py); None when this flavour has none."""
+    try:
+        table = json.load(open(os.path.join(ROOT, "profiles", "ncu_evidence.json")))
+        return table.get("%s|fast%d|lanes%d" % (workload, int(fast_math), int(lanes)))
+    except Exception:
+        return None
 
 
 def measured_peaks():
@@ -158,6 +174,13 @@ class Dist:
 # --------------------------------------------------------------------------------------------- our arm
 def make_solver(capi, orc_params, agent, env, K, H, prm, dist, dtype="f32", noise="tensor", **kw):
     from mpc_b200.models import ENV_NAMES, env_spec
+    if dtype == "f32" and agent == "MPPI":
+        if kw.get("fast_math", -1) < 0:
+            kw["fast_math"] = FLAVOUR[env][0]
+        if not kw.get("lanes"):
+            kw["lanes"] = FLAVOUR[env][1]
+    else:
+        kw["fast_math"] = max(0, kw.get("fast_math", 0))
     model = ENV_NAMES[env]()
     env_id, env_params = env_spec(model)
     lo, hi = float(model.bounds_low[0]), float(model.bounds_high[0])
@@ -365,15 +388,21 @@ def run_ours(args, dist):
     local_steps = float(s.K_local) * H
     fma_peak = capi.measure_fma_peak(dist.local_rank, args.dtype) if dist.rank == 0 else 0.0
     ach_tflops = local_steps * ALG_FLOPS[env] / roll_s / 1e12
-    roofline = {"bound": "fp32_pipe" if args.dtype == "f32" else "fp64_pipe", "kernel": "mppi_rollout_kernel",
+    roofline = {"bound": "fp32_pipe" if args.dtype == "f32" else "fp64_pipe", "kernel": "mppi_solve_kernel",
                 "achieved": ach_tflops, "peak": fma_peak, "unit": "TFLOP/s",
                 "frac": ach_tflops / fma_peak if fma_peak else None, "traffic": None,
                 "peak_source": "FMA-chain microbenchmark run live (mpc_measure_fma_peak); MEASURED_PEAKS.json has no "
                                "CUDA-core figure", "alg_flops_per_step": ALG_FLOPS[env],
                 "kernel_ms": roll_ms / args.steps}
+    ev = ncu_evidence(args.workload, s.fast_math, s.lanes) if (args.noise == "tensor" and dist.world == 1) else None
+    if ev:
+        roofline["traffic"] = ev["dram_bytes_per_launch"]
+        roofline["traffic_over_algorithmic"] = ev["dram_bytes_per_launch"] / (local_steps * esz)
+        roofline["ncu"] = {k: ev[k] for k in ev if k != "dram_bytes_per_launch"}
     hbm_ach = local_steps * esz / roll_s / 1e9 if args.noise == "tensor" else 0.0
     roofline_hbm = {"bound": "hbm", "achieved": hbm_ach, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                    "frac": hbm_ach / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks_src,
+                    "frac": hbm_ach / peaks["hbm_gbs"], "traffic": ev["dram_bytes_per_launch"] if ev else None,
+                    "peak_source": peaks_src,
                     "alg_bytes_per_step": esz if args.noise == "tensor" else 0}
 
     line = {
@@ -381,8 +410,7 @@ def run_ours(args, dist):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": args.workload, "agent": agent, "env": env, "K": K, "H": H, **prm,
-                   "noise": args.noise, "lanes_per_thread": args.lanes or (2 if args.dtype == "f32" else 1),
-                   "fast_math": bool(args.fast_math), "K_per_gpu": s.K_local,
+                   "noise": args.noise, "lanes_per_thread": s.lanes, "fast_math": bool(s.fast_math), "K_per_gpu": s.K_local,
                    "cache": ("L2 flushed (256 MiB write) between timed steps" if flush else
                              "noise shard %.0f MB per GPU > L2 (126 MB): no flush" % (shard_bytes / 1e6)),
                    "parallelism": "K-shard x%d, one all-gather of (beta, eta, E[H]) per solve (%s)" % (
@@ -436,7 +464,8 @@ def main():
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
     ap.add_argument("--noise", default="tensor", choices=["tensor", "philox"])
     ap.add_argument("--lanes", type=int, default=0, choices=[0, 1, 2], help="f32 samples per thread (0 = default 2)")
-    ap.add_argument("--fast-math", type=int, default=0, choices=[0, 1], help="f32: MUFU trig instead of polynomial")
+    ap.add_argument("--fast-math", type=int, default=-1, choices=[-1, 0, 1],
+                    help="f32: MUFU trig instead of polynomial (-1: per-env flavour that meets the 1e-5 parity bar)")
     ap.add_argument("--no-extra", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

@@ -157,14 +157,17 @@ class Solver:
         self.nz = self.ns + 1
         self.is_mppi = cfg.agent == AGENT_MPPI
         self.tensor_noise = cfg.noise == NOISE_TENSOR
+        self.fast_math = bool(cfg.fast_math)
+        self.lanes = int(lanes) if lanes else (2 if (dtype == "f32" and self.is_mppi) else 1)
         h = C.c_void_p()
         rc = L.mpc_create(C.byref(cfg), C.byref(h))
         if rc != MPC_OK:
             raise MpcError(rc, (L.mpc_last_error(None) or b"").decode())
         self._h = h
-        geo = (C.c_int32 * 6)()
+        geo = (C.c_int32 * 8)()
         self._ck(L.mpc_get_geometry(self._h, geo))
-        self.geometry = dict(grid=geo[0], block=geo[1], smem=geo[2], tiles=geo[3], K_local=geo[4], k_begin=geo[5])
+        self.geometry = dict(grid=geo[0], block=geo[1], smem=geo[2], tiles=geo[3], K_local=geo[4], k_begin=geo[5],
+                             stages=geo[6], stream_rows=geo[7])
         self.K_local, self.k_begin = geo[4], geo[5]
 
     # -- plumbing

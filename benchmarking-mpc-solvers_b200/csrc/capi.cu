@@ -330,7 +330,7 @@ static int encode_noise_map(mpc_handle *h) {
     const cuuint64_t esz = f32 ? 4 : 8;
     const cuuint64_t gdim[3] = {(cuuint64_t)g.Kpad, (cuuint64_t)g.H, 1};
     const cuuint64_t gstride[2] = {(cuuint64_t)g.Kpad * esz, (cuuint64_t)g.Kpad * esz * g.H};
-    const cuuint32_t box[3] = {(cuuint32_t)g.wt, (cuuint32_t)g.H, 1};
+    const cuuint32_t box[3] = {(cuuint32_t)g.wt, (cuuint32_t)(g.stream_rows ? g.stream_rows : g.H), 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     CUresult r = encode(&h->noise_map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3,
                         h->d_noise, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
@@ -490,6 +490,25 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
             W = S < MPPI_MAX_WARPS ? S : MPPI_MAX_WARPS;
             if (W >= 8) W -= W % 4;
         }
+        // STREAM (mppi.cuh): when whole [H][wt] tiles leave room for fewer than 8 warps (long horizons, H > ~100), the
+        // rollout reads the noise through small per-warp chunk rings instead and the weighted sum re-reads the rows
+        // from L2: 16 resident warps for any H, at the price of touching the tensor twice (HBM has the headroom:
+        // the rollout is pipe bound).  MPC_B200_STREAM=0|1 overrides (profiling).
+        g.stream_rows = g.stream_depth = 0;
+        if (cfg->noise == MPC_NOISE_TENSOR) {
+            bool stream = s_cap < 8;  // measured (tools/stream_probe.py): at 8+ whole-tile warps the two flavours tie
+            if (const char *e = getenv("MPC_B200_STREAM")) stream = atoi(e) != 0;
+            if (stream) {
+                g.stream_rows = 8;
+                g.stream_depth = 4;
+                if (const char *e = getenv("MPC_B200_STREAM_ROWS")) { int v = atoi(e); if (v >= 4 && v <= 64 && v % 4 == 0) g.stream_rows = v; }
+                if (const char *e = getenv("MPC_B200_STREAM_DEPTH")) { int v = atoi(e); if (v >= 2 && v <= 16) g.stream_depth = v; }
+                const size_t cstage = mppi_stage_bytes(cfg->dtype, g.variant, g.stream_rows);
+                W = MPPI_MAX_WARPS;
+                while (W > 1 && fixed + (long long)W * g.stream_depth * (long long)cstage > max_smem) --W;
+                s_cap = MPPI_MAX_WARPS;
+            }
+        }
         // tuning knobs (profiling only): MPC_B200_WARPS, MPC_B200_STAGES
         if (const char *e = getenv("MPC_B200_WARPS")) { int v = atoi(e); if (v >= 1 && v <= MPPI_MAX_WARPS && v <= s_cap) W = v; }
         if (const char *e = getenv("MPC_B200_STAGES")) { int v = atoi(e); if (v >= W && v <= s_cap) S = v; }
@@ -520,10 +539,12 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
             g.max_parts = nb;
             g.fin_group = 1;
         }
+        if (g.stream_rows) S = W * g.stream_depth;
         g.warps = W;
         g.stages = S;
         const int cap = g.max_parts > W ? g.max_parts : W;
-        g.smem_rollout = mppi_solve_smem(cfg->dtype, g.variant, cfg->H, S, W, cap, g.fin_group, h->nz);
+        g.smem_rollout = mppi_solve_smem(cfg->dtype, g.variant, cfg->H, g.stream_rows ? g.stream_rows : cfg->H, S, W, cap,
+                                         g.fin_group, h->nz);
         if (g.smem_rollout > (size_t)max_smem) {
             int rc = fail(nullptr, MPC_EINVAL, "solve kernel needs %zu B of shared memory (limit %d)", g.smem_rollout,
                           max_smem);
@@ -1176,7 +1197,7 @@ int mpc_sync(mpc_handle *h) {
 
 int64_t mpc_launch_count(const mpc_handle *h) { return h ? h->launches : 0; }
 
-int mpc_get_geometry(const mpc_handle *h, int32_t out[6]) {
+int mpc_get_geometry(const mpc_handle *h, int32_t out[8]) {
     if (!h || !out) return MPC_EINVAL;
     out[0] = h->g.grid;
     out[1] = h->g.warps * 32;
@@ -1184,6 +1205,8 @@ int mpc_get_geometry(const mpc_handle *h, int32_t out[6]) {
     out[3] = h->g.total_tiles;
     out[4] = h->g.K_local;
     out[5] = h->g.k_begin;
+    out[6] = h->g.stages;
+    out[7] = h->g.stream_rows;
     return MPC_OK;
 }
 

@@ -171,7 +171,7 @@ __global__ void fill_kernel(float *p, size_t n, float v) {
 
 
 #define DECL2(ret, name, ...) ret name##_f32(__VA_ARGS__); ret name##_f64(__VA_ARGS__);
-DECL2(size_t, mppi_solve_smem, int, int, int, int, int, int, int)
+DECL2(size_t, mppi_solve_smem, int, int, int, int, int, int, int, int)
 DECL2(size_t, mppi_stage_bytes, int, int)
 DECL2(cudaError_t, launch_mppi_solve, int, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
 DECL2(cudaError_t, launch_mppi_rank_merge, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
@@ -188,10 +188,10 @@ DECL2(cudaError_t, launch_fma_peak, float *, int, int, cudaStream_t)
 #undef DECL2
 #define BY_DTYPE(name, ...) ((dtype) == DT_F32 ? name##_f32(__VA_ARGS__) : name##_f64(__VA_ARGS__))
 
-size_t mppi_solve_smem(int dtype, int variant, int H, int S, int W, int cap, int G, int nz) {
-    return BY_DTYPE(mppi_solve_smem, variant, H, S, W, cap, G, nz);
+size_t mppi_solve_smem(int dtype, int variant, int H, int rows, int S, int W, int cap, int G, int nz) {
+    return BY_DTYPE(mppi_solve_smem, variant, H, rows, S, W, cap, G, nz);
 }
-size_t mppi_stage_bytes(int dtype, int variant, int H) { return BY_DTYPE(mppi_stage_bytes, variant, H); }
+size_t mppi_stage_bytes(int dtype, int variant, int rows) { return BY_DTYPE(mppi_stage_bytes, variant, rows); }
 cudaError_t launch_mppi_solve(int dtype, int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
                               const MppiBuffers &b, cudaStream_t s) {
     return BY_DTYPE(launch_mppi_solve, noise, variant, ep, a, b, s);

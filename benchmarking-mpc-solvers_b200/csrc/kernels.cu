@@ -445,30 +445,32 @@ static cudaError_t mppi_solve_go(const MppiArgs &a, const EnvParamsHost &ep, con
     memset(&pt, 0, sizeof pt);
     if (a.p2p)
         for (int r = 0; r < a.world && r < MAX_WORLD; ++r) pt.recs[r] = b.peer_recs[r];
-    kern<<<a.g.grid, a.g.warps * 32, smem, s>>>(a, make_env<V>(ep), map, b.x0, b.g_z, b.U, b.S, b.part, b.rank_part,
-                                                 b.out, b.done_count, pt);
+    kern<<<a.g.grid, a.g.warps * 32, smem, s>>>(a, make_env<V>(ep), map, (const typename Env::S *)b.noise, b.x0, b.g_z, b.U,
+                                                 b.S, b.part, b.rank_part, b.out, b.done_count, pt);
     return cudaGetLastError();
 }
 
-// shared-memory bytes of the solve kernel: ring (S stages, W warps) or the tail arena, whichever is larger
+// shared-memory bytes of the solve kernel: ring (S stages of `rows` time steps, W warps) or the tail arena, whichever
+// is larger
 template <typename V>
-static size_t mppi_smem_bytes(int H, int S, int W, int cap, int G, int nz) {
-    const size_t ring = RingSmem<V>::ring_total(H, S, W), tail = RingSmem<V>::tail_total(H, W, cap, G, nz);
+static size_t mppi_smem_bytes(int H, int rows, int S, int W, int cap, int G, int nz) {
+    const size_t ring = RingSmem<V>::ring_total(H, rows, S, W), tail = RingSmem<V>::tail_total(H, W, cap, G, nz);
     return ring > tail ? ring : tail;
 }
 
-size_t FN(mppi_solve_smem)(int variant, int H, int S, int W, int cap, int G, int nz) {
+size_t FN(mppi_solve_smem)(int variant, int H, int rows, int S, int W, int cap, int G, int nz) {
     if constexpr (std::is_same<R_, double>::value)
-        return mppi_smem_bytes<double>(H, S, W, cap, G, nz);
+        return mppi_smem_bytes<double>(H, rows, S, W, cap, G, nz);
     else
-        return (variant & VAR_PACK2) ? mppi_smem_bytes<f2>(H, S, W, cap, G, nz) : mppi_smem_bytes<float>(H, S, W, cap, G, nz);
+        return (variant & VAR_PACK2) ? mppi_smem_bytes<f2>(H, rows, S, W, cap, G, nz)
+                                     : mppi_smem_bytes<float>(H, rows, S, W, cap, G, nz);
 }
 
-size_t FN(mppi_stage_bytes)(int variant, int H) {
+size_t FN(mppi_stage_bytes)(int variant, int rows) {
     if constexpr (std::is_same<R_, double>::value)
-        return RingSmem<double>::stage_bytes(H);
+        return RingSmem<double>::stage_bytes(rows);
     else
-        return (variant & VAR_PACK2) ? RingSmem<f2>::stage_bytes(H) : RingSmem<float>::stage_bytes(H);
+        return (variant & VAR_PACK2) ? RingSmem<f2>::stage_bytes(rows) : RingSmem<float>::stage_bytes(rows);
 }
 
 cudaError_t FN(launch_mppi_solve)(int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
@@ -476,8 +478,12 @@ cudaError_t FN(launch_mppi_solve)(int noise, int variant, const EnvParamsHost &e
     cudaError_t e = cudaSuccess;
     with_rollout_env(ep.env, variant, [&](auto env) {
         typedef decltype(env) E;
-        e = (noise == NOISE_TENSOR) ? mppi_solve_go<E, NOISE_TENSOR>(a, ep, b, s)
-                                    : mppi_solve_go<E, NOISE_PHILOX>(a, ep, b, s);
+        if (noise == NOISE_PHILOX)
+            e = mppi_solve_go<E, NOISE_PHILOX>(a, ep, b, s);
+        else if (a.g.stream_rows > 0)
+            e = mppi_solve_go<E, NOISE_STREAM>(a, ep, b, s);
+        else
+            e = mppi_solve_go<E, NOISE_TENSOR>(a, ep, b, s);
     });
     return e;
 }

@@ -8,7 +8,8 @@ namespace mpc {
 constexpr int TILE = 128;       // padding unit of K (row stride of the noise tensor) and CEM block size
 constexpr int PART_HDR = 2;     // partial record = [beta, eta, E[0..H-1]]
 
-enum { NOISE_TENSOR = 0, NOISE_PHILOX = 1 };
+// NOISE_STREAM: the resident tensor again, but staged in small per-warp chunk rings and re-read (L2) by the weighted sum
+enum { NOISE_TENSOR = 0, NOISE_PHILOX = 1, NOISE_STREAM = 2 };
 enum { DT_F64 = 0, DT_F32 = 1 };
 
 struct EnvParamsHost {
@@ -35,6 +36,8 @@ struct Geometry {
     int grid;             // solve-kernel blocks
     int max_parts;        // partial records per solve: blocks_per_solve (A) or warps (B)
     int fin_group;        // mode B: solves finalised together (one thread per nominal rollout)
+    int stream_rows;      // 0 = whole [H][wt] tiles in the ring; > 0 = STREAM: time steps per chunk of a warp's private ring
+    int stream_depth;     // STREAM: chunk stages per warp
     int variant;          // rollout flavour: bit 0 fast_math (MUFU trig), bit 1 two samples per thread (f32x2)
     int ns;
     size_t smem_rollout;  // dynamic shared memory of the solve kernel
@@ -131,8 +134,9 @@ cudaError_t launch_model_step(int dtype, const EnvParamsHost &ep, int n, const d
 cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaStream_t s);
 cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s);
 
-size_t mppi_solve_smem(int dtype, int variant, int H, int S, int W, int cap, int G, int nz);
-size_t mppi_stage_bytes(int dtype, int variant, int H);
+// rows = time steps per ring stage (H, or the STREAM chunk); S = ring stages of the block (STREAM: W * depth)
+size_t mppi_solve_smem(int dtype, int variant, int H, int rows, int S, int W, int cap, int G, int nz);
+size_t mppi_stage_bytes(int dtype, int variant, int rows);
 constexpr int MPPI_MAX_WARPS = 16;   // == MAX_WARPS in mppi.cuh
 constexpr int MPPI_MAX_H = 256;      // 32 * MAX_ROWS
 

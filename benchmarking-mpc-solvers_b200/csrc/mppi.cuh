@@ -37,12 +37,13 @@ struct RingSmem {
     typedef typename VT<V>::S R;
     static constexpr int WT = WarpTile<V>::WT;
     static __host__ __device__ size_t a16(size_t b) { return (b + 15) / 16 * 16; }
-    static __host__ __device__ size_t stage_bytes(int H) { return (size_t)H * WT * sizeof(R); }
-    static __host__ __device__ size_t off_sU(int H, int S) { return S * stage_bytes(H); }
-    static __host__ __device__ size_t off_sw(int H, int S, int W) { return off_sU(H, S) + a16((size_t)W * H * sizeof(R)); }
-    static __host__ __device__ size_t off_bar(int H, int S, int W) { return off_sw(H, S, W) + (size_t)W * WT * sizeof(R); }
-    static __host__ __device__ size_t off_gen(int H, int S, int W) { return off_bar(H, S, W) + (size_t)S * 8; }
-    static __host__ __device__ size_t ring_total(int H, int S, int W) { return off_gen(H, S, W) + (size_t)S * 4 + 16; }
+    // a stage holds `rows` time steps of one warp tile: rows = H (whole tiles), or the STREAM chunk
+    static __host__ __device__ size_t stage_bytes(int rows) { return (size_t)rows * WT * sizeof(R); }
+    static __host__ __device__ size_t off_sU(int rows, int S) { return S * stage_bytes(rows); }
+    static __host__ __device__ size_t off_sw(int H, int rows, int S, int W) { return off_sU(rows, S) + a16((size_t)W * H * sizeof(R)); }
+    static __host__ __device__ size_t off_bar(int H, int rows, int S, int W) { return off_sw(H, rows, S, W) + (size_t)W * WT * sizeof(R); }
+    static __host__ __device__ size_t off_gen(int H, int rows, int S, int W) { return off_bar(H, rows, S, W) + (size_t)S * 8; }
+    static __host__ __device__ size_t ring_total(int H, int rows, int S, int W) { return off_gen(H, rows, S, W) + (size_t)S * 4 + 16; }
     // tail arena (doubles): warp records [W][2+H] | scale[cap] | clipped plans [G][H] | goals [G][H*NZ] | warp sums
     // [W][H] ; G = solves finalised together
     static __host__ __device__ size_t tail_total(int H, int W, int cap, int G, int nz) {
@@ -89,6 +90,27 @@ __device__ __forceinline__ double dot_row_rot(const double *row, const double *w
         a1 = fma(q.y, e.y, a1);
     }
     return a0 + a1;
+}
+
+// ---- STREAM flavour of the weighted sum: rows come straight from the (L2-resident) noise tensor, one coalesced row
+// per load, weights stay in registers.  v[r] = this lane's share of row r; the butterfly below is a reduce-scatter
+// over the warp: 31 shuffles for 32 rows, and lane l ends up with the complete sum of row l in v[0].
+__device__ __forceinline__ float lane_dot(const f2 &w, const f2 &e) { return fmaf(w.v.y, e.v.y, w.v.x * e.v.x); }
+__device__ __forceinline__ float lane_dot(float w, float e) { return w * e; }
+__device__ __forceinline__ double lane_dot(double w, double e) { return w * e; }
+template <typename R>
+__device__ __forceinline__ R warp_rows_reduce_scatter(R (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+            const R keep = up ? v[i + off] : v[i];
+            const R send = up ? v[i] : v[i + off];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return v[0];
 }
 
 // softmin scale of a record with minimum bj relative to the merged minimum beta (empty records carry +inf)
@@ -215,7 +237,8 @@ __device__ __forceinline__ void block_apply(const MppiArgs &a, const EnvConst<ty
 template <class Env, int NOISE>
 __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
     mppi_solve_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec,
-                      const __grid_constant__ CUtensorMap noise_map, const double *__restrict__ x0g, const double *__restrict__ g_z, double *__restrict__ Ug,
+                      const __grid_constant__ CUtensorMap noise_map, const typename Env::S *__restrict__ noise_g,
+                      const double *__restrict__ x0g, const double *__restrict__ g_z, double *__restrict__ Ug,
                       double *__restrict__ S_out, double *__restrict__ part, double *__restrict__ rank_part,
                       double *__restrict__ out, int *__restrict__ done_count, const PeerTable pt) {
     typedef typename Env::Vec V;
@@ -223,17 +246,21 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
     constexpr int NS = Env::NS, NZ = Env::NS + 1, NG = Env::NG, PACK = VT<V>::N, CH = Env::CHUNK;
     constexpr int WT = WarpTile<V>::WT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr bool STREAM = NOISE == NOISE_STREAM;
     const int H = a.g.H, W = blockDim.x >> 5, S = a.g.stages, tps = a.g.tiles_per_solve;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const size_t stage_elems = (size_t)H * WT;
+    // STREAM: the ring is W private rings of `depth` chunk stages of `rows` time steps (S = W * depth)
+    const int rows = STREAM ? a.g.stream_rows : H, depth = STREAM ? a.g.stream_depth : 0;
+    const int nchunk = STREAM ? (H + rows - 1) / rows : 1;
+    const size_t stage_elems = (size_t)rows * WT;
     R *stages = reinterpret_cast<R *>(smem_raw);
-    R *sU = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sU(H, S)) + (size_t)w * H;
-    R *sw = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sw(H, S, W)) + (size_t)w * WT;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + RingSmem<V>::off_bar(H, S, W));
+    R *sU = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sU(rows, S)) + (size_t)w * H;
+    R *sw = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sw(H, rows, S, W)) + (size_t)w * WT;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + RingSmem<V>::off_bar(H, rows, S, W));
     // gen[st] = tile whose load the stage's mbarrier currently tracks.  An mbarrier carries one bit of phase: a
     // warp that ran a whole ring turn ahead of a slow warp would see the parity of an OLDER completed phase and
     // read a stale tile.  Waiting for gen[st] == j first makes the wait exact for any interleaving of the warps.
-    volatile int *gen = reinterpret_cast<volatile int *>(smem_raw + RingSmem<V>::off_gen(H, S, W));
+    volatile int *gen = reinterpret_cast<volatile int *>(smem_raw + RingSmem<V>::off_gen(H, rows, S, W));
     const int rec_len = PART_HDR + H;
 
     if (blockIdx.x == 0) stamp(a.trace, TR_START);
@@ -265,7 +292,33 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
         }
     };
 
-    if (NOISE == NOISE_TENSOR) {
+    // STREAM: chunk q of this warp's sequence (tile tile0 + w + (q / nchunk) W, rows (q % nchunk) * rows ...) goes to
+    // stage q % depth of the warp's private ring; the same warp issues and consumes in order, so the phase parity of
+    // a stage is (q / depth) & 1 and no cross-warp bookkeeping is needed
+    R *wring = stages + (size_t)w * depth * stage_elems;
+    uint64_t *wbars = bars + (size_t)w * depth;
+    int iss_st = 0, use_st = 0;           // ring stage of the next issue / the next use
+    uint32_t use_phase = 0;               // phase parity of the next use: flips each time use_st wraps
+    int iss_tile = tile0 + w, iss_c = 0;  // tile and chunk the next issue loads (kept incrementally: no divisions)
+    int iss_kt = iss_tile % tps;
+    auto issue_chunk = [&]() {
+        if (iss_tile < tile1) {
+            if (lane == 0) {
+                mbar_expect_tx(&wbars[iss_st], (uint32_t)(stage_elems * sizeof(R)));  // rows past H: zero-filled, counted
+                fence_proxy_async();
+                tma_load_3d(wring + (size_t)iss_st * stage_elems, &noise_map, iss_kt * WT, iss_c * rows, 0, &wbars[iss_st]);
+            }
+            if (++iss_c == nchunk) {
+                iss_c = 0;
+                iss_tile += W;
+                iss_kt += W;
+                while (iss_kt >= tps) iss_kt -= tps;
+            }
+        }
+        if (++iss_st == depth) iss_st = 0;
+    };
+
+    if (NOISE == NOISE_TENSOR || STREAM) {
         if (tid == 0) {
             for (int i = 0; i < S; ++i) {
                 mbar_init(&bars[i], 1);
@@ -274,7 +327,11 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             fence_mbar_init();
         }
         __syncthreads();
-        for (int i = w; i < S && tile0 + i < tile1; i += W) issue(tile0 + i);
+        if (STREAM) {
+            for (int i = 0; i < depth; ++i) issue_chunk();
+        } else {
+            for (int i = w; i < S && tile0 + i < tile1; i += W) issue(tile0 + i);
+        }
     }
 
     // ---- per-warp running softmin state of the current solve; E rows lane, lane + 32, ... in registers ---------
@@ -321,7 +378,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             if (cur == b) load_solve(cur);
         }
         const int jr = j - tile0, st = jr % S;
-        R *tile = (NOISE == NOISE_TENSOR) ? stages + st * stage_elems : stages + w * stage_elems;
+        R *tile = (NOISE == NOISE_TENSOR) ? stages + st * stage_elems : stages + w * stage_elems;  // STREAM: unused
         const int kl = kt * WT + lane * PACK;  // first local sample index of this lane
         V x[NS];
 #pragma unroll
@@ -356,6 +413,32 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                 V acc = V((R)0);
                 one(t, load_lanes(col + (size_t)t * WT, (V *)nullptr), acc);
                 fold(acc);
+            }
+        } else if (STREAM) {
+            // chunk by chunk through the warp's private ring; the grouping of the float32 cost sums is the tensor
+            // path's (rows is a multiple of CH), so both flavours give bit-identical costs
+            for (int c = 0; c < nchunk; ++c) {
+                mbar_wait(&wbars[use_st], use_phase);
+                const R *ccol = wring + (size_t)use_st * stage_elems + lane * PACK;
+                const int t0 = c * rows, n = min(rows, H - t0);
+                int r = 0;
+                for (; r + CH <= n; r += CH) {
+                    V acc = V((R)0);
+#pragma unroll
+                    for (int i = 0; i < CH; ++i) one(t0 + r + i, load_lanes(ccol + (size_t)(r + i) * WT, (V *)nullptr), acc);
+                    fold(acc);
+                }
+                for (; r < n; ++r) {
+                    V acc = V((R)0);
+                    one(t0 + r, load_lanes(ccol + (size_t)r * WT, (V *)nullptr), acc);
+                    fold(acc);
+                }
+                if (++use_st == depth) {
+                    use_st = 0;
+                    use_phase ^= 1u;
+                }
+                __syncwarp();    // every lane has read the stage
+                issue_chunk();   // re-arm it with the chunk `depth` places ahead (possibly of the warp's next tile)
             }
         } else {
             // same chunking of the float32 cost sums as the tensor path (CH divides 4), so both noise modes give
@@ -428,6 +511,30 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             wl[l] = (R)wk;
             wsum += wk;
         }
+        if constexpr (STREAM) {
+            // ---- E[t] += sum_k w_k eps[k][t] with the rows re-read from the noise tensor (L2; the tile went through
+            // this SM a tile time ago), weights in registers, 32 rows per reduce-scatter --------------------------
+            eta_run = eta_run * scale_old + warp_sum(wsum);
+            beta_run = beta_new;
+            V wv;
+            if constexpr (PACK == 2)
+                wv = V(wl[0], wl[PACK - 1]);
+            else
+                wv = V(wl[0]);
+            const R *grow = noise_g + (size_t)kt * WT + lane * PACK;
+#pragma unroll
+            for (int i = 0; i < MAX_ROWS; ++i) {
+                if (32 * i < H) {
+                    R v[32];
+#pragma unroll
+                    for (int r = 0; r < 32; ++r) {
+                        const int t = 32 * i + r;
+                        v[r] = (t < H) ? lane_dot(wv, load_lanes(grow + (size_t)t * a.g.Kpad, (V *)nullptr)) : (R)0;
+                    }
+                    E[i] = E[i] * scale_old + (double)warp_rows_reduce_scatter(v, lane);
+                }
+            }
+        } else {
         if constexpr (PACK == 2)
             *reinterpret_cast<float2 *>(sw + lane * 2) = make_float2(wl[0], wl[PACK - 1]);
         else
@@ -444,6 +551,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                 if (r < H) acc = dot_row_rot(tile + (size_t)r * WT, sw, lane, (V *)nullptr);
                 E[i] = E[i] * scale_old + acc;
             }
+        }
         }
         // ---- re-arm the stage with the tile S places ahead -------------------------------------------------------
         if (NOISE == NOISE_TENSOR) {

@@ -208,8 +208,9 @@ int mpc_get_trace(mpc_handle *h, uint64_t out[16]);
 /* Number of kernel launches issued by this handle so far. */
 int64_t mpc_launch_count(const mpc_handle *h);
 /* Geometry chosen for the rollout kernel: out[0]=grid, out[1]=block, out[2]=dynamic smem bytes, out[3]=tiles,
- * out[4]=K_local, out[5]=k_begin. */
-int mpc_get_geometry(const mpc_handle *h, int32_t out[6]);
+ * out[4]=K_local, out[5]=k_begin, out[6]=ring stages, out[7]=time steps per stage of the STREAM flavour (0: whole
+ * [H][tile] stages). */
+int mpc_get_geometry(const mpc_handle *h, int32_t out[8]);
 /* FP32 / FP64 FMA-pipe peak of the device measured with a dependent-free FMA chain (TFLOP/s, 2 flops per FMA). */
 int mpc_measure_fma_peak(int32_t device, int32_t dtype, double *tflops_out);
 /* Flush L2 by writing a buffer larger than it. */

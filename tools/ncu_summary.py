@@ -53,7 +53,32 @@ def num(s):
         return None
 
 
+def evidence(path):
+    """The few numbers bench.py attaches to its roofline object."""
+    d = load(path)
+    mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    rd, wr = d["dram__bytes_read.sum"], d["dram__bytes_write.sum"]
+    g = lambda k: num(d[k][0]) if k in d else None
+    return {"dram_bytes_per_launch": num(rd[0]) * mult[rd[1]] + num(wr[0]) * mult[wr[1]],
+            "gpu_time_us": g("gpu__time_duration.sum"),
+            "fma_pipe_cycles_active_pct": g("sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active"),
+            "xu_pipe_pct": g("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
+            "alu_pipe_pct": g("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+            "issue_active_pct": g("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+            "registers_per_thread": g("launch__registers_per_thread"), "source": path.split("/")[-1]}
+
+
 def main():
+    if sys.argv[1] == "--json":  # --json out.json key:raw.csv [...]  (merges into out.json)
+        import json
+        import os
+        out = sys.argv[2]
+        table = json.load(open(out)) if os.path.exists(out) else {}
+        for spec in sys.argv[3:]:
+            key, path = spec.split(":", 1)
+            table[key] = evidence(path)
+        json.dump(table, open(out, "w"), indent=1, sort_keys=True)
+        return
     print("# %s\n" % sys.argv[1])
     for spec in sys.argv[2:]:
         steps, path = spec.split(":", 1)
