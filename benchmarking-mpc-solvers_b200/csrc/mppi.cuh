@@ -240,13 +240,16 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                       const __grid_constant__ CUtensorMap noise_map, const typename Env::S *__restrict__ noise_g,
                       const double *__restrict__ x0g, const double *__restrict__ g_z, double *__restrict__ Ug,
                       double *__restrict__ S_out, double *__restrict__ part, double *__restrict__ rank_part,
-                      double *__restrict__ out, int *__restrict__ done_count, const PeerTable pt) {
+                      double *__restrict__ out, int *__restrict__ done_count,
+                      const __grid_constant__ PeerTable pt) {  // indexed by rank at run time: stays in parameter space
     typedef typename Env::Vec V;
     typedef typename Env::S R;
     constexpr int NS = Env::NS, NZ = Env::NS + 1, NG = Env::NG, PACK = VT<V>::N, CH = Env::CHUNK;
     constexpr int WT = WarpTile<V>::WT;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr bool STREAM = NOISE == NOISE_STREAM;
+    // the descriptor's address in parameter space (the lambdas below capture the pointer, not the 128-byte object)
+    const CUtensorMap *const map_ptr = &noise_map;
     const int H = a.g.H, W = blockDim.x >> 5, S = a.g.stages, tps = a.g.tiles_per_solve;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     // STREAM: the ring is W private rings of `depth` chunk stages of `rows` time steps (S = W * depth)
@@ -288,7 +291,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             __threadfence_block();
             gen[st] = j;
             fence_proxy_async();  // generic-proxy reads of the stage precede the async-proxy writes
-            tma_load_3d(stages + st * stage_elems, &noise_map, kt * WT, 0, a.noise_batched ? b : 0, &bars[st]);
+            tma_load_3d(stages + st * stage_elems, map_ptr, kt * WT, 0, a.noise_batched ? b : 0, &bars[st]);
         }
     };
 
@@ -306,7 +309,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             if (lane == 0) {
                 mbar_expect_tx(&wbars[iss_st], (uint32_t)(stage_elems * sizeof(R)));  // rows past H: zero-filled, counted
                 fence_proxy_async();
-                tma_load_3d(wring + (size_t)iss_st * stage_elems, &noise_map, iss_kt * WT, iss_c * rows, 0, &wbars[iss_st]);
+                tma_load_3d(wring + (size_t)iss_st * stage_elems, map_ptr, iss_kt * WT, iss_c * rows, 0, &wbars[iss_st]);
             }
             if (++iss_c == nchunk) {
                 iss_c = 0;

@@ -24,7 +24,7 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 }
 __device__ __forceinline__ unsigned long long global_ns() {
     unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)::"memory");  // pinned: a phase stamp must not float past barriers
     return t;
 }
 // raise `theirs` (a flag in a peer's buffer) to `epoch`, then wait until the peer has raised `mine` (in our buffer)
