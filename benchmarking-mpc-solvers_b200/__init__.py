@@ -10,6 +10,9 @@ from . import capi
 from .agents import CEM, CEMB200, MPPI, MPPIB200, Agent
 from .build import build as build_library
 from .models import ENV_NAMES, AcrobotModel, CartPoleSwingUpModel, Model, PendulumModel, env_spec
+from .envs import AcrobotEnv, CartPoleSwingUpEnv, Environment, PendulumEnv
+from .experiment import Experiment, ResultSink, noise_sweep, sample_sweep, temperature_sweep
 
 __all__ = ["capi", "Agent", "MPPI", "CEM", "MPPIB200", "CEMB200", "Model", "PendulumModel", "CartPoleSwingUpModel",
-           "AcrobotModel", "env_spec", "ENV_NAMES", "build_library"]
+           "AcrobotModel", "env_spec", "ENV_NAMES", "build_library", "Environment", "PendulumEnv", "CartPoleSwingUpEnv",
+           "AcrobotEnv", "Experiment", "ResultSink", "sample_sweep", "temperature_sweep", "noise_sweep"]

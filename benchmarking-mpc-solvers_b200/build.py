@@ -17,7 +17,7 @@ COMMON = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
 # (object name, source, extra flags)
 UNITS = [
     ("kernels_f32.o", "kernels.cu", ["-DMPC_REAL=float", "-DMPC_SUFFIX=_f32"]),
-    ("kernels_f64.o", "kernels.cu", ["-DMPC_REAL=double", "-DMPC_SUFFIX=_f64", "-fmad=false"]),
+    ("kernels_f64.o", "kernels.cu", ["-DMPC_REAL=double", "-DMPC_SUFFIX=_f64", "-DMPC_IS_F64", "-fmad=false"]),
     ("dispatch.o", "dispatch.cu", []),
     ("capi.o", "capi.cu", []),
 ]

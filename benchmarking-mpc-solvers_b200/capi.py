@@ -29,7 +29,7 @@ SYMBOLS = [
     "mpc_cem_solve", "mpc_cem_get_rewards", "mpc_cem_get_elites", "mpc_cem_get_std", "mpc_simulate", "mpc_model_step",
     "mpc_comm_create_id", "mpc_comm_init", "mpc_mppi_rollout_partial", "mpc_mppi_apply_partials", "mpc_upload_inputs", "mpc_solve_enqueue", "mpc_download_outputs",
     "mpc_timer_start", "mpc_timer_stop", "mpc_sync", "mpc_set_profiling", "mpc_get_rollout_ms", "mpc_launch_count", "mpc_get_geometry", "mpc_measure_fma_peak",
-    "mpc_flush_l2", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace",
+    "mpc_flush_l2", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace", "mpc_episode_run",
 ]
 
 
@@ -43,6 +43,11 @@ class MpcConfig(C.Structure):
         ("bounds_low", C.c_double), ("bounds_high", C.c_double), ("seed", C.c_uint64),
         ("env_params", C.c_double * MAX_ENV_PARAMS),
     ]
+
+
+class MpcEpisodeOpts(C.Structure):  # include/mpc_b200.h: mpc_episode_opts
+    _fields_ = [("struct_size", C.c_uint32), ("n_steps", C.c_int32), ("warm_start_iters", C.c_int32),
+                ("shift", C.c_int32), ("actuation_std", C.c_double), ("sensor_std", C.c_double), ("seed", C.c_uint64)]
 
 
 class MpcError(RuntimeError):
@@ -90,6 +95,7 @@ def load():
     L.mpc_p2p_import.argtypes = [hp, C.c_void_p]
     L.mpc_p2p_link.argtypes = [C.POINTER(hp), C.c_int32]
     L.mpc_get_trace.argtypes = [hp, C.POINTER(C.c_uint64)]
+    L.mpc_episode_run.argtypes = [hp, _dp, _dp, C.POINTER(MpcEpisodeOpts)] + [_dp] * 8
     L.mpc_mppi_rollout_partial.argtypes = [hp, _dp, _dp, _dp, _dp]
     L.mpc_mppi_apply_partials.argtypes = [hp, _dp, _dp, _dp, _dp, _dp]
     L.mpc_upload_inputs.argtypes = [hp, _dp, _dp, _dp]
@@ -295,6 +301,31 @@ class Solver:
         self._ck(self.L.mpc_simulate(self._h, xp, up, gp, xsp, C.byref(cost)))
         return xs, cost.value
 
+    # -- closed loop resident on the device (Experiment.py:67-90 without the host in the loop)
+    def episode_run(self, x0, n_steps, U_in=None, warm_start=0, shift=True, actuation_std=0.0, sensor_std=0.0, seed=0,
+                    want_plans=True):
+        """Returns a dict: states [n+1][ns] (observations), true_states, actions [n], costs [n], U_final [H] and, when
+        want_plans, plan_us [n][H], plan_xs [n][H+1][ns], plan_costs [n] (the agent's planning histories)."""
+        n = int(n_steps)
+        opts = MpcEpisodeOpts(C.sizeof(MpcEpisodeOpts), n, int(warm_start), int(bool(shift)), float(actuation_std),
+                              float(sensor_std), int(seed))
+        xa, xp = _in(x0, (self.ns,))
+        ua, up = _in(U_in, (self.H,)) if U_in is not None else (None, None)
+        states, sp = _out((n + 1, self.ns))
+        true_states, tp = _out((n + 1, self.ns))
+        actions, ap = _out((n,))
+        costs, cp = _out((n,))
+        Uf, ufp = _out((self.H,))
+        pus = pxs = pcs = None
+        pup = pxp = pcp = None
+        if want_plans:
+            pus, pup = _out((n, self.H))
+            pxs, pxp = _out((n, self.H + 1, self.ns))
+            pcs, pcp = _out((n,))
+        self._ck(self.L.mpc_episode_run(self._h, xp, up, C.byref(opts), sp, tp, ap, cp, pup, pxp, pcp, ufp))
+        return dict(states=states, true_states=true_states, actions=actions, costs=costs, U_final=Uf, plan_us=pus,
+                    plan_xs=pxs, plan_costs=pcs)
+
     def model_step(self, x, u, g=None):
         x = np.ascontiguousarray(x, dtype=np.float64).reshape(-1, self.ns)
         n = x.shape[0]
@@ -402,7 +433,7 @@ class Solver:
         buf = (C.c_uint64 * 16)()
         self._ck(self.L.mpc_get_trace(self._h, buf))
         names = ["start", "tiles_done", "ticket", "merged", "published", "peers_in", "merged2", "applied", "end",
-                 "recs_in_smem", "rec_written", "fenced"]
+                 "recs_in_smem", "rec_written", "fenced", "first_warp_out", "last_warp_out", "recs_stored"]
         t0 = buf[0]
         return {n: (int(buf[i]) - int(t0)) if buf[i] else None for i, n in enumerate(names)}
 

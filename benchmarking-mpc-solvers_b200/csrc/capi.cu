@@ -103,6 +103,8 @@ struct mpc_handle {
     double *h_in = nullptr, *h_out = nullptr;
     size_t in_elems = 0, out_elems = 0, out_stride = 0;
     float *d_flush = nullptr;
+    double *d_episode = nullptr;  // histories of mpc_episode_run
+    size_t ep_elems = 0;
     size_t flush_elems = 0;
     // state
     bool noise_ready = false;
@@ -369,6 +371,7 @@ int mpc_destroy(mpc_handle *h) {
     cudaFree(h->d_elite);
     cudaFree(h->d_sel);
     cudaFree(h->d_flush);
+    cudaFree(h->d_episode);
     if (h->h_in) cudaFreeHost(h->h_in);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -951,6 +954,111 @@ int mpc_cem_get_std(mpc_handle *h, double *std_out) {
 }
 
 // ---------------------------------------------------------------------------------------------- nominal rollout
+// ---------------------------------------------------------------------------------------------- closed-loop episode
+int mpc_episode_run(mpc_handle *h, const double *x0, const double *U_in, const mpc_episode_opts *opts, double *states,
+                    double *true_states, double *actions, double *costs, double *plan_us, double *plan_xs,
+                    double *plan_costs, double *U_final) {
+    if (!h) return MPC_EINVAL;
+    if (!opts || opts->struct_size != sizeof(mpc_episode_opts))
+        return fail(h, MPC_EINVAL, "mpc_episode_opts.struct_size mismatch (header/library versions differ)");
+    if (!x0 || !states || !true_states || !actions || !costs) return fail(h, MPC_EINVAL, "null output or state pointer");
+    if (opts->n_steps < 1 || opts->warm_start_iters < 0) return fail(h, MPC_EINVAL, "n_steps >= 1, warm_start_iters >= 0");
+    if (h->g.B != 1 || h->cfg.world != 1) return fail(h, MPC_ESTATE, "episodes run on batch = 1, world = 1 handles");
+    const bool mppi = h->cfg.agent == MPC_AGENT_MPPI;
+    if (mppi && !h->noise_ready) return fail(h, MPC_ESTATE, "noise tensor not set: call mpc_set_noise or mpc_fill_noise first");
+    if (!mppi && h->cfg.noise != MPC_NOISE_PHILOX)
+        return fail(h, MPC_ESTATE, "a device-resident CEM episode needs PHILOX noise (host draws cannot be resident)");
+    CU(h, cudaSetDevice(h->cfg.device));
+    const Geometry &g = h->g;
+    const int n = opts->n_steps, ns = h->ns, H = g.H;
+    // device histories: true_state[ns] | states | true_states | actions | costs | plan_us | plan_xs | plan_costs
+    const size_t o_true = 0, o_states = o_true + ns, o_tstates = o_states + (size_t)(n + 1) * ns,
+                 o_act = o_tstates + (size_t)(n + 1) * ns, o_cost = o_act + n, o_pus = o_cost + n,
+                 o_pxs = o_pus + (plan_us ? (size_t)n * H : 0), o_pc = o_pxs + (plan_xs ? (size_t)n * (H + 1) * ns : 0),
+                 total = o_pc + (plan_costs ? n : 0);
+    if (total > h->ep_elems) {
+        if (h->d_episode) cudaFree(h->d_episode);
+        h->d_episode = nullptr;
+        h->ep_elems = 0;
+        CU(h, cudaMalloc(&h->d_episode, total * sizeof(double)));
+        h->ep_elems = total;
+    }
+    double *d = h->d_episode;
+    int rc = stage_inputs(h, x0, nullptr, U_in);  // state + zero goal (+ plan) in one copy
+    if (rc) return rc;
+    CU(h, cudaMemcpyAsync(d + o_true, h->d_in + off_x(h), ns * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(d + o_states, h->d_in + off_x(h), ns * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(d + o_tstates, h->d_in + off_x(h), ns * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    EpisodeArgs ea;
+    memset(&ea, 0, sizeof ea);
+    ea.H = H;
+    ea.n_steps = n;
+    ea.shift = opts->shift ? 1 : 0;
+    ea.lo = h->cfg.bounds_low;
+    ea.hi = h->cfg.bounds_high;
+    ea.actuation_std = opts->actuation_std;
+    ea.sensor_std = opts->sensor_std;
+    ea.seed = opts->seed;
+    EpisodeBuffers eb;
+    eb.out = h->d_out;
+    eb.U = h->d_in + off_U(h);
+    eb.x0 = h->d_in + off_x(h);
+    eb.true_state = d + o_true;
+    eb.states = d + o_states;
+    eb.true_states = d + o_tstates;
+    eb.actions = d + o_act;
+    eb.costs = d + o_cost;
+    eb.plan_us = plan_us ? d + o_pus : nullptr;
+    eb.plan_xs = plan_xs ? d + o_pxs : nullptr;
+    eb.plan_costs = plan_costs ? d + o_pc : nullptr;
+    // one solve of either agent, enqueued only
+    auto enqueue_solve = [&](int want_traj) -> int {
+        if (mppi) return mppi_enqueue(h, want_traj);
+        CU(h, launch_cem_reset(cem_args(h, 0, 0), cem_bufs(h), h->stream));
+        h->launches++;
+        for (int it = 0; it < h->cfg.max_iter; ++it) {
+            const int r = cem_enqueue_iter(h, it);
+            if (r) return r;
+        }
+        CU(h, launch_cem_finish(h->cfg.dtype, h->ep, cem_args(h, 0, want_traj), cem_bufs(h), h->stream));
+        h->launches++;
+        h->solves++;
+        return MPC_OK;
+    };
+    for (int w = 0; w < opts->warm_start_iters; ++w) {  // Agent.warm_start (agent.py:42-47)
+        rc = enqueue_solve(0);
+        if (rc) return rc;
+        ea.mode = 1;
+        CU(h, launch_episode_step(h->ep, ea, eb, h->stream));
+        h->launches++;
+    }
+    ea.mode = 0;
+    const int want_traj = (ea.shift || plan_xs || plan_costs) ? 1 : 0;
+    for (int i = 0; i < n; ++i) {
+        rc = enqueue_solve(want_traj);
+        if (rc) return rc;
+        ea.step = i;
+        CU(h, launch_episode_step(h->ep, ea, eb, h->stream));
+        h->launches++;
+    }
+    // one synchronisation: histories back through the pinned staging buffer when they fit, else straight to the caller
+    auto fetch = [&](double *dst, size_t off, size_t cnt) -> int {
+        if (dst) CU(h, cudaMemcpyAsync(dst, d + off, cnt * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        return MPC_OK;
+    };
+    if ((rc = fetch(states, o_states, (size_t)(n + 1) * ns))) return rc;
+    if ((rc = fetch(true_states, o_tstates, (size_t)(n + 1) * ns))) return rc;
+    if ((rc = fetch(actions, o_act, n))) return rc;
+    if ((rc = fetch(costs, o_cost, n))) return rc;
+    if ((rc = fetch(plan_us, o_pus, (size_t)n * H))) return rc;
+    if ((rc = fetch(plan_xs, o_pxs, (size_t)n * (H + 1) * ns))) return rc;
+    if ((rc = fetch(plan_costs, o_pc, n))) return rc;
+    if (U_final)
+        CU(h, cudaMemcpyAsync(U_final, h->d_in + off_U(h), H * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
 int mpc_simulate(mpc_handle *h, const double *x, const double *us, const double *g_z, double *xs_out, double *cost_out) {
     if (!h || !x || !us) return fail(h, MPC_EINVAL, "null argument");
     CU(h, cudaSetDevice(h->cfg.device));

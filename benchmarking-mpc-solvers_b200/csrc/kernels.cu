@@ -340,6 +340,71 @@ __global__ void model_step_kernel(const EnvConst<typename Env::Vec> ec, int n, c
     Env::leave(ec, x, xn + (size_t)i * NS);
 }
 
+// ------------------------------------------------------------------------------------------------ closed loop
+// One control step of Experiment.run (Experiment.py:78-90) around the solve that has just finished on this stream,
+// without the host: what Agent.predict_action does after _calc_action (agent.py:63-76) and Environment.step
+// (env.py:35-50), one block.
+//   out (the solve's outputs): u0, U[H] (updated, unclipped plan), cost and xs of the clipped plan's nominal rollout
+//   plan: planned_us = clip(planned_us); log (planned_xs, planned_us, planned_costs); planned_us = roll(-1), last = 0
+//   plant: u = clip(u0) (+ actuation noise); cost of (x_true, u) with a zero goal; x_true = model.predict(x_true, u);
+//          observation = x_true (+ sensor noise) -> the next solve's x0
+// The plant is always stepped in float64 with the reference's expression tree (this kernel is launched from the
+// float64 translation unit whatever the rollout dtype): the environment is the ground truth of an episode.
+// Noise: Philox streams 2 (actuation) and 3 (sensor), counter = control step.
+template <class Env>
+__global__ void episode_step_kernel(const EnvConst<double> ec, const EpisodeArgs a, const EpisodeBuffers b) {
+    constexpr int NS = Env::NS;
+    const int H = a.H, i = a.step, tid = threadIdx.x, nt = blockDim.x;
+    const double *o = b.out;
+    __shared__ double s_next[8];
+    if (a.mode == 1) {  // Agent.warm_start: planned_us = clip(planned_us)   agent.py:45-47
+        for (int t = tid; t < H; t += nt) b.U[t] = fmin(fmax(o[1 + t], a.lo), a.hi);
+        return;
+    }
+    if (tid == 0) {
+        double u = fmin(fmax(o[0], a.lo), a.hi);  // return np.clip(u0, ...)   agent.py:76
+        float z[4];
+        if (a.actuation_std > 0.0) {  // env.py:36-38
+            philox_normal4(a.seed, 2u, (uint32_t)i, 0u, 0u, z);
+            u += a.actuation_std * (double)z[0];
+        }
+        double x[NS], g[Env::NG], zero[NS + 1];
+#pragma unroll
+        for (int k = 0; k < NS; ++k) x[k] = b.true_state[k];
+#pragma unroll
+        for (int k = 0; k <= NS; ++k) zero[k] = 0.0;
+        Env::prep_goal(ec, zero, g);  // Model.predict(x, u) with goal = None -> zeros   model.py:32-33
+        const double c = Env::step(ec, x, u, g);
+        if (a.sensor_std > 0.0) philox_normal4(a.seed, 3u, (uint32_t)i, 0u, 0u, z);  // env.py:42-44
+#pragma unroll
+        for (int k = 0; k < NS; ++k) {
+            const double obs = x[k] + (a.sensor_std > 0.0 ? a.sensor_std * (double)z[k] : 0.0);
+            b.true_state[k] = x[k];
+            b.true_states[(size_t)(i + 1) * NS + k] = x[k];
+            b.states[(size_t)(i + 1) * NS + k] = obs;
+            s_next[k] = obs;
+        }
+        b.actions[i] = u;
+        b.costs[i] = c;
+        if (b.plan_costs) b.plan_costs[i] = o[1 + H];
+    }
+    // the log rows of this step (agent.py:67-69) and the receding-horizon shift (agent.py:70-71)
+    for (int t = tid; t < H; t += nt) {
+        const double uc = fmin(fmax(o[1 + t], a.lo), a.hi);
+        if (b.plan_us) b.plan_us[(size_t)i * H + t] = uc;
+        if (a.shift) {
+            if (t > 0) b.U[t - 1] = uc;
+            if (t == H - 1) b.U[t] = 0.0;
+        } else {
+            b.U[t] = uc;
+        }
+    }
+    if (b.plan_xs)
+        for (int k = tid; k < (H + 1) * NS; k += nt) b.plan_xs[(size_t)i * (H + 1) * NS + k] = o[2 + H + k];
+    __syncthreads();
+    if (tid < NS) b.x0[tid] = s_next[tid];  // the next predict_action sees env.state (Experiment.py:81-82)
+}
+
 // FMA-pipe peak: 16 independent chains per thread, no memory traffic.
 template <typename R>
 __global__ void __launch_bounds__(256) fma_peak_kernel(float *sink, int iters) {
@@ -574,6 +639,18 @@ cudaError_t FN(launch_model_step)(const EnvParamsHost &ep, int n, const double *
     });
     return cudaGetLastError();
 }
+
+#ifdef MPC_IS_F64
+cudaError_t launch_episode_step(const EnvParamsHost &ep, const EpisodeArgs &a, const EpisodeBuffers &b, cudaStream_t s) {
+    EnvConst<double> ec = make_env<double>(ep);
+    switch (ep.env) {
+    case ENV_PENDULUM: episode_step_kernel<Pendulum<double, false>><<<1, 128, 0, s>>>(ec, a, b); break;
+    case ENV_CARTPOLE: episode_step_kernel<CartPole<double, false>><<<1, 128, 0, s>>>(ec, a, b); break;
+    default: episode_step_kernel<Acrobot<double, false>><<<1, 128, 0, s>>>(ec, a, b); break;
+    }
+    return cudaGetLastError();
+}
+#endif
 
 cudaError_t FN(launch_fma_peak)(float *sink, int blocks, int iters, cudaStream_t s) {
     fma_peak_kernel<R_><<<blocks, 256, 0, s>>>(sink, iters);

@@ -107,6 +107,26 @@ struct CemBuffers {
     double *err_word;      // set when a peer did not deliver in time
 };
 
+// closed-loop control step on the device (episode_step_kernel, kernels.cu)
+struct EpisodeArgs {
+    int H, step, n_steps, shift, mode;  // mode 0 = control step, 1 = warm-start step (clip the plan only)
+    double lo, hi, actuation_std, sensor_std;
+    uint64_t seed;
+};
+struct EpisodeBuffers {
+    const double *out;    // solve outputs (see above)
+    double *U;            // device-resident plan of the agent (MPPI planned_us / CEM mean)
+    double *x0;           // the solver's state input: receives the next observation
+    double *true_state;   // [ns] plant state
+    double *states;       // [n+1][ns] observations   (row 0 written by the host)
+    double *true_states;  // [n+1][ns]
+    double *actions;      // [n] applied controls (after actuation noise: env.py history "action")
+    double *costs;        // [n]
+    double *plan_us;      // [n][H]        nullable
+    double *plan_xs;      // [n][H+1][ns]  nullable
+    double *plan_costs;   // [n]           nullable
+};
+
 // launches (kernels.cu); all return cudaGetLastError()
 // the whole solve (rollout + softmin update + plan update + nominal rollout); world > 1: up to this rank's record
 cudaError_t launch_mppi_solve(int dtype, int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
@@ -133,6 +153,8 @@ cudaError_t launch_model_step(int dtype, const EnvParamsHost &ep, int n, const d
                               const double *g, double *cost, double *xn, cudaStream_t s);
 cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaStream_t s);
 cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s);
+// always the float64 plant (compiled in the float64 translation unit only)
+cudaError_t launch_episode_step(const EnvParamsHost &ep, const EpisodeArgs &a, const EpisodeBuffers &b, cudaStream_t s);
 
 // rows = time steps per ring stage (H, or the STREAM chunk); S = ring stages of the block (STREAM: W * depth)
 size_t mppi_solve_smem(int dtype, int variant, int H, int rows, int S, int W, int cap, int G, int nz);

@@ -570,8 +570,15 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
     }
 
     // ---- tail: every stage is free after this barrier; the arena is reused from offset 0 -------------------------
+    __shared__ unsigned long long s_wexit[MAX_WARPS];  // profiling: when each warp left the tile loop
+    if (a.trace && lane == 0) s_wexit[w] = global_ns();
     __syncthreads();
-    const unsigned long long t_tiles_done = a.trace ? global_ns() : 0ull;
+    unsigned long long t_wmin = ~0ull, t_wmax = 0ull;
+    if (a.trace && tid == 0)
+        for (int i = 0; i < W; ++i) {
+            t_wmin = s_wexit[i] < t_wmin ? s_wexit[i] : t_wmin;
+            t_wmax = s_wexit[i] > t_wmax ? s_wexit[i] : t_wmax;
+        }
     __shared__ double red[32];
     __shared__ int s_last;
     double *arena = reinterpret_cast<double *>(smem_raw);
@@ -595,6 +602,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             for (int i = 0; i < MAX_ROWS; ++i)
                 if (lane + 32 * i < H) rec[PART_HDR + lane + 32 * i] = E[i];
         }
+        const unsigned long long t_a0 = a.trace ? global_ns() : 0ull;
         __syncthreads();
         const unsigned long long t_a = a.trace ? global_ns() : 0ull;
         double bb = INFINITY;
@@ -625,10 +633,13 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
         __syncthreads();
         if (!s_last) return;
         if (a.trace && tid == 0) {
-            a.trace[TR_TILES_DONE] = t_tiles_done;
+            a.trace[TR_TILES_DONE] = t_wmax;  // the last warp's exit from the tile loop
             a.trace[9] = t_a;
             a.trace[10] = t_b;
             a.trace[11] = t_c;
+            a.trace[12] = t_wmin;
+            a.trace[13] = t_wmax;
+            a.trace[14] = t_a0;
         }
         stamp(a.trace, TR_TICKET);
         __threadfence();

@@ -27,6 +27,22 @@ class Model:
         self._stepper = None
         self._device = 0
 
+    # model.py:46-48 (gym.utils.seeding.np_random(seed) of the gym the reference pins returns a RandomState-like
+    # generator; only .uniform is used, by Environment.reset)
+    def seed(self, seed=None):
+        self.np_random = np.random.RandomState(seed)
+        return [seed]
+
+    @property
+    def np_random(self):
+        if getattr(self, "_np_random", None) is None:
+            self._np_random = np.random.RandomState()
+        return self._np_random
+
+    @np_random.setter
+    def np_random(self, rng):
+        self._np_random = rng
+
     # model.py:20-24
     def set_sensor_noise(self, sensor_std):
         self.sensor_noise = True

@@ -152,6 +152,34 @@ int mpc_cem_get_elites(mpc_handle *h, int32_t iter, int32_t *idx_out);
 /* Current std of solve 0 (cem.py:73): out [H]. */
 int mpc_cem_get_std(mpc_handle *h, double *std_out);
 
+/* ---- closed-loop episode, resident on the device ----------------------------------------------------------------
+ * Replaces the control loop of Experiment.run (ExperimentCore/Experiment.py:67-90): env.reset(start), agent.reset(),
+ * agent.warm_start(env.true_state, warm_start_iters, goal = 0) (agents/agent.py:30-48), then n_steps times
+ * action = agent.predict_action(env.state, goal = 0) (agent.py:50-76, logging branch included when `shift`) followed
+ * by env.step(action) (envs/env.py:35-50) with optional actuation / sensor noise.  Every solve, the plan clip / log /
+ * shift and the plant step are kernels enqueued back to back on the handle's stream; the host synchronises ONCE, at
+ * the end, and reads the histories.  The plant is stepped in float64 whatever the rollout dtype.  Goal = zeros (what
+ * every reference script passes); batch = 1, world = 1.  MPPI: resident noise tensor or Philox; CEM: Philox noise.
+ * Environment noise is Philox (streams 2, 3; key `seed`), so noisy episodes are reproducible — the reference's are
+ * not (global numpy RNG shared with forked workers). */
+typedef struct mpc_episode_opts {
+    uint32_t struct_size;      /* sizeof(mpc_episode_opts) */
+    int32_t n_steps;           /* Experiment.experiment_length */
+    int32_t warm_start_iters;  /* 0 = no warm start */
+    int32_t shift;             /* 1 = agent.logging (default of the reference): log rows + receding-horizon shift */
+    double actuation_std;      /* Environment.set_actuation_noise, 0 = off */
+    double sensor_std;         /* Environment.set_sensor_noise, 0 = off */
+    uint64_t seed;
+} mpc_episode_opts;
+/* x0 [ns] start state; U_in [H] initial plan (null = keep the resident one; agent.reset does not clear it).
+ * Outputs (caller-owned): states [n+1][ns] observations (env.history "state", row 0 = x0), true_states [n+1][ns],
+ * actions [n] (env.history "action": after actuation noise), costs [n] (env.history "cost"); nullable: plan_us
+ * [n][H] (planning_action_history), plan_xs [n][H+1][ns] (planning_state_history), plan_costs [n]
+ * (planning_costs_history), U_final [H] (agent.planned_us after the last step). */
+int mpc_episode_run(mpc_handle *h, const double *x0, const double *U_in, const mpc_episode_opts *opts, double *states,
+                    double *true_states, double *actions, double *costs, double *plan_us, double *plan_xs,
+                    double *plan_costs, double *U_final);
+
 /* ---- nominal rollout ------------------------------------------------------------------------------------- */
 /* Agent.simulate_trajectory (agent.py:97-108) for one plan: us [H], g_z [H][nz] -> xs [H+1][ns], cost. */
 int mpc_simulate(mpc_handle *h, const double *x, const double *us, const double *g_z, double *xs_out,
