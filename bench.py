@@ -282,6 +282,67 @@ def latency_extras(capi, dist, reps=200, warm=20):
     return out
 
 
+def config_extras(capi, dist):
+    """The other BASELINE.json configs on one GPU (reported in `extra`, not the headline):
+    configs[4]: batch of 4096 independent CartPole MPPI solves (K = 1024, H = 50) in ONE launch;
+    configs[3]: MPPI Pendulum K = 65536, H = 50 over the temperature grid of scripts/mppi_temperature.py:23;
+    configs[0]-style closed loop: a 200-step Pendulum episode resident on the device (mpc_episode_run) next to the
+    same episode driven from the host one predict_action-sized call per step."""
+    out = {}
+    one = dist  # extras run on world == 1 only
+    # ---- configs[4]
+    B, K, H = 4096, 1024, 50
+    s = make_solver(capi, None, "MPPI", "cartpole", K, H, dict(lam=0.5, sigma=1.0), one, batch=B)
+    s.set_profiling(True)
+    rng = np.random.RandomState(0)
+    xs = np.array(START["cartpole"]) + rng.normal(0, 0.2, (B, 4))  # cartpole_swingup_model.py:50-51
+    s.upload_inputs(xs, None, np.zeros((B, H)))
+    ms, _, _, _ = time_device(s, 10, 3, one, flush=True)
+    out["batch4096_cartpole_k1024_h50_f32_steps_per_s"] = B * K * H * 10 / (ms * 1e-3)
+    out["batch4096_cartpole_k1024_h50_f32_ms_per_batch"] = ms / 10
+    t = time.perf_counter()
+    for _ in range(5):
+        s.mppi_solve(xs, None, np.zeros((B, H)), want_traj=True)
+    out["batch4096_cartpole_k1024_h50_f32_e2e_steps_per_s"] = B * K * H * 5 / (time.perf_counter() - t)
+    s.close()
+    # ---- configs[3]
+    for lam in (0.001, 0.01, 0.1, 0.5, 1.0, 10.0):
+        s = make_solver(capi, None, "MPPI", "pendulum", 65536, 50, dict(lam=lam, sigma=1.0), one)
+        x, U = np.array(START["pendulum"]), np.zeros(50)
+        for _ in range(10):
+            s.mppi_solve(x, None, U)
+        lat = []
+        for _ in range(100):
+            t = time.perf_counter()
+            s.mppi_solve(x, None, U)
+            lat.append(time.perf_counter() - t)
+        out["mppi_pendulum_k65536_h50_lam%g_p50_ms" % lam] = round(1e3 * statistics.median(lat), 4)
+        s.close()
+    # ---- closed loop
+    n = 200
+    s = make_solver(capi, None, "MPPI", "pendulum", 4096, 50, dict(lam=0.5, sigma=1.0), one)
+    x0 = np.array(START["pendulum"])
+    s.episode_run(x0, 20, U_in=np.zeros(50))
+    t = time.perf_counter()
+    ep = s.episode_run(x0, n, U_in=np.zeros(50), actuation_std=0.1, sensor_std=0.1, seed=1)
+    dt_dev = time.perf_counter() - t
+    out["episode_pendulum_k4096_h50_device_us_per_control_step"] = round(1e6 * dt_dev / n, 2)
+    out["episode_pendulum_k4096_h50_device_steps_per_s"] = 4096 * 50 * n / dt_dev
+    out["episode_pendulum_k4096_h50_final_cost"] = float(ep["costs"][-1])
+    U = np.zeros(50)
+    x = x0.copy()
+    t = time.perf_counter()
+    for _ in range(n):  # the host loop: solve (H2D + launch + D2H) then one plant step through mpc_model_step
+        u0, Un, xs_, c_ = s.mppi_solve(x, None, U, want_traj=True)
+        Uc = np.clip(Un[0], -2.0, 2.0)
+        U = np.append(Uc[1:], 0.0)
+        _, xn = s.model_step(x[None, :], np.clip(u0, -2.0, 2.0))
+        x = xn[0]
+    out["episode_pendulum_k4096_h50_hostloop_us_per_control_step"] = round(1e6 * (time.perf_counter() - t) / n, 2)
+    s.close()
+    return out
+
+
 def cpu_baseline_sample(env, K_full, H, prm, budget_s=12.0):
     """The oracle port (oracle/mpc_oracle.c, pthreads over samples) timed on this host: a bounded sample of the same
     workload (same env, H, lam, std; fewer samples)."""
@@ -431,6 +492,7 @@ def run_ours(args, dist):
                 extra = {}
                 try:
                     extra.update(latency_extras(capi, dist))
+                    extra.update(config_extras(capi, dist))
                     one = dist
                     for wl in ("mppi_pendulum_h50_k1m", "mppi_cartpole_h50_k1m"):
                         a2, e2, K2, H2, p2 = WORKLOADS[wl]
