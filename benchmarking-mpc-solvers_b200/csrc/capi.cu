@@ -101,6 +101,9 @@ struct mpc_handle {
     int cem_z_stride = 0;         // row stride of the standard-normal tensor
     // host (pinned)
     double *h_in = nullptr, *h_out = nullptr;
+    unsigned long long *h_flag = nullptr;  // pinned completion word the solve kernel raises (host-flag path)
+    unsigned long long host_epoch = 0;
+    bool host_flag_on = true;              // MPC_B200_HOSTFLAG=0 selects the D2H copy + stream synchronise instead
     size_t in_elems = 0, out_elems = 0, out_stride = 0;
     float *d_flush = nullptr;
     double *d_episode = nullptr;  // histories of mpc_episode_run
@@ -374,6 +377,7 @@ int mpc_destroy(mpc_handle *h) {
     cudaFree(h->d_episode);
     if (h->h_in) cudaFreeHost(h->h_in);
     if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->h_flag) cudaFreeHost(h->h_flag);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->evr0) cudaEventDestroy(h->evr0);
@@ -568,6 +572,9 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     CUC(cudaMemsetAsync(h->d_out, 0, h->out_elems * sizeof(double), h->stream));
     CUC(cudaMallocHost(&h->h_in, h->in_elems * sizeof(double)));
     CUC(cudaMallocHost(&h->h_out, h->out_elems * sizeof(double)));
+    CUC(cudaMallocHost(&h->h_flag, 64));
+    *h->h_flag = 0ull;
+    if (const char *e = getenv("MPC_B200_HOSTFLAG")) h->host_flag_on = atoi(e) != 0;
     memset(h->h_in, 0, h->in_elems * sizeof(double));
     h->g_zero_on_device = true;
     // CEM over several GPUs: elites are global, so the standard normals of an iteration (TENSOR noise) are resident in
@@ -737,14 +744,52 @@ static int fetch_outputs(mpc_handle *h, int want_traj, double *u0, double *U_out
     return MPC_OK;
 }
 
+// Host-flag completion of a batch-1 solve: poll the pinned word the finalising block raises.  The stream is queried
+// now and then so that a faulted launch turns into an error instead of an endless spin.
+static int await_host_flag(mpc_handle *h, int want_traj, double *u0, double *U_out, double *xs_out, double *cost_out) {
+    volatile unsigned long long *flag = h->h_flag;
+    const unsigned long long want = h->host_epoch;
+    unsigned spins = 0;
+    while (*flag != want) {
+        if ((++spins & 0x3fffu) == 0) {
+            cudaError_t q = cudaStreamQuery(h->stream);
+            if (q == cudaSuccess) {
+                if (*flag == want) break;
+                return fail(h, MPC_ECUDA, "solve kernel finished without raising its completion flag");
+            }
+            if (q != cudaErrorNotReady) return fail(h, MPC_ECUDA, "solve kernel: %s", cudaGetErrorString(q));
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+    }
+    __atomic_thread_fence(__ATOMIC_ACQUIRE);
+    const Geometry &g = h->g;
+    const double *o = h->h_out;
+    if (h->p2p_ready && o[h->out_stride] != 0.0)
+        return fail(h, MPC_ENCCL, "peer exchange timed out: a rank did not deliver its record within 4 s");
+    if (u0) u0[0] = o[0];
+    if (U_out) memcpy(U_out, o + 1, g.H * sizeof(double));
+    if (want_traj) {
+        if (cost_out) cost_out[0] = o[1 + g.H];
+        if (xs_out) memcpy(xs_out, o + 2 + g.H, (size_t)(g.H + 1) * h->ns * sizeof(double));
+    }
+    return MPC_OK;
+}
+
 // ---------------------------------------------------------------------------------------------- MPPI
-static int mppi_enqueue(mpc_handle *h, int want_traj) {
+static int mppi_enqueue(mpc_handle *h, int want_traj, bool host_flag = false) {
     if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "not an MPPI handle");
     if (!h->noise_ready) return fail(h, MPC_ESTATE, "noise tensor not set: call mpc_set_noise or mpc_fill_noise first");
     if (h->cfg.world > 1 && !h->comm && !h->p2p_ready)
         return fail(h, MPC_ESTATE, "world > 1 but neither mpc_p2p_import/mpc_p2p_link nor mpc_comm_init was called");
     if (h->p2p_ready) h->epoch++;
-    const MppiArgs a = mppi_args(h, want_traj);
+    MppiArgs a = mppi_args(h, want_traj);
+    if (host_flag) {
+        a.host_out = h->h_out;  // pinned host memory is device-addressable at the same address (UVA)
+        a.host_flag = h->h_flag;
+        a.host_epoch = ++h->host_epoch;
+    }
     const MppiBuffers b = mppi_bufs(h);
     if (h->profiling) CU(h, cudaEventRecord(h->evr0, h->stream));
     CU(h, launch_mppi_solve(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
@@ -769,9 +814,13 @@ int mpc_mppi_solve(mpc_handle *h, const double *x, const double *g_z, const doub
     const int want_traj = (xs_out || cost_out) ? 1 : 0;
     int rc = stage_inputs(h, x, g_z, U_in);
     if (rc) return rc;
-    rc = mppi_enqueue(h, want_traj);
+    // host-flag completion: batch = 1 and the tail that applies the update runs inside the solve kernel (one GPU,
+    // or the in-kernel peer exchange) — the kernel writes the outputs into pinned host memory and raises a flag
+    const bool use_flag = h->host_flag_on && h->g.B == 1 && (h->cfg.world == 1 || h->p2p_ready);
+    rc = mppi_enqueue(h, want_traj, use_flag);
     if (rc) return rc;
-    return fetch_outputs(h, want_traj, u0, U_out, xs_out, cost_out);
+    if (!use_flag) return fetch_outputs(h, want_traj, u0, U_out, xs_out, cost_out);
+    return await_host_flag(h, want_traj, u0, U_out, xs_out, cost_out);
 }
 
 int mpc_mppi_rollout_partial(mpc_handle *h, const double *x, const double *g_z, const double *U_in, double *rec_out) {

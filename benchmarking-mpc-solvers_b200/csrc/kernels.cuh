@@ -61,6 +61,12 @@ struct MppiArgs {
     unsigned long long *trace; // null, or 16 words for the finalising block's phase stamps (mpc_get_trace)
     int world;            // ranks whose records the final merge combines
     int rank;
+    // host-flag completion (batch = 1, host-buffer solve call): the finalising block also writes the solve's outputs
+    // into mapped pinned host memory and then raises host_flag to host_epoch — the host polls the flag instead of
+    // submitting a D2H copy and a stream synchronise
+    double *host_out;                 // null = off; same layout as `out`
+    unsigned long long *host_flag;
+    unsigned long long host_epoch;
 };
 
 struct CemArgs {

@@ -670,6 +670,18 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
         } else {
             block_apply<Env>(a, ec, b, false, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG);
         }
+        if (a.host_out && !(a.record_only)) {
+            // outputs straight into the caller-visible pinned buffer, then the completion flag (system-scope release)
+            __syncthreads();
+            const size_t stride = (size_t)(2 + H + (H + 1) * NS);
+            const double *o = out + (size_t)b * stride;
+            const int n_copy = a.want_traj ? (int)stride : 1 + H;
+            for (int i = tid; i < n_copy; i += nt) a.host_out[i] = o[i];
+            if (tid < 2) a.host_out[stride + tid] = out[(size_t)a.g.B * stride + tid];  // peer-wait error words
+            __threadfence_system();
+            __syncthreads();
+            if (tid == 0) st_release_sys(a.host_flag, a.host_epoch);
+        }
         stamp(a.trace, TR_END);
     } else {
         // mode B: this block owns whole solves; its warps' records are in global memory (slot = warp).  One warp
