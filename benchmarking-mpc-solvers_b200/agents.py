@@ -103,7 +103,10 @@ class _GpuAgent(Agent):
             bounds=(float(np.ravel(self.bounds_low)[0]), float(np.ravel(self.bounds_high)[0])),
             device=params.get("device", 0), rank=params.get("rank", 0), world=params.get("world", 1),
             seed=params.get("seed", 0), resample=params.get("resample", False),
-            fast_math=params.get("fast_math", False), lanes=params.get("lanes", 0), **kw)
+            fast_math=params.get("fast_math", False), lanes=params.get("lanes", 0),
+            # a model with sensor noise adds it in every predict of the rollouts (model.py:42-43, noise_tests.py:44)
+            model_noise_std=float(getattr(self.model, "sensor_std", 0.0)) if getattr(self.model, "sensor_noise", False) else 0.0,
+            **kw)
         if params.get("world", 1) > 1:
             if "comm_id" in params:   # NCCL all-gather + merge kernel (MPPI)
                 self._solver.comm_init(params["comm_id"])

@@ -29,7 +29,7 @@ SYMBOLS = [
     "mpc_cem_solve", "mpc_cem_get_rewards", "mpc_cem_get_elites", "mpc_cem_get_std", "mpc_simulate", "mpc_model_step",
     "mpc_comm_create_id", "mpc_comm_init", "mpc_mppi_rollout_partial", "mpc_mppi_apply_partials", "mpc_upload_inputs", "mpc_solve_enqueue", "mpc_download_outputs",
     "mpc_timer_start", "mpc_timer_stop", "mpc_sync", "mpc_set_profiling", "mpc_get_rollout_ms", "mpc_launch_count", "mpc_get_geometry", "mpc_measure_fma_peak",
-    "mpc_flush_l2", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace", "mpc_episode_run",
+    "mpc_flush_l2", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace", "mpc_episode_run", "mpc_philox_model_noise",
 ]
 
 
@@ -41,7 +41,7 @@ class MpcConfig(C.Structure):
         ("resample", C.c_int32), ("fast_math", C.c_int32), ("lanes", C.c_int32),
         ("lam", C.c_double), ("sigma", C.c_double), ("epsilon", C.c_double), ("alpha", C.c_double),
         ("bounds_low", C.c_double), ("bounds_high", C.c_double), ("seed", C.c_uint64),
-        ("env_params", C.c_double * MAX_ENV_PARAMS),
+        ("env_params", C.c_double * MAX_ENV_PARAMS), ("model_noise_std", C.c_double),
     ]
 
 
@@ -95,6 +95,7 @@ def load():
     L.mpc_p2p_import.argtypes = [hp, C.c_void_p]
     L.mpc_p2p_link.argtypes = [C.POINTER(hp), C.c_int32]
     L.mpc_get_trace.argtypes = [hp, C.POINTER(C.c_uint64)]
+    L.mpc_philox_model_noise.argtypes = [hp, C.c_uint64, _dp]
     L.mpc_episode_run.argtypes = [hp, _dp, _dp, C.POINTER(MpcEpisodeOpts)] + [_dp] * 8
     L.mpc_mppi_rollout_partial.argtypes = [hp, _dp, _dp, _dp, _dp]
     L.mpc_mppi_apply_partials.argtypes = [hp, _dp, _dp, _dp, _dp, _dp]
@@ -135,7 +136,7 @@ class Solver:
 
     def __init__(self, agent, env, env_params, K, H, *, dtype="f64", noise="tensor", lam=1.0, sigma=1.0,
                  max_iter=1, n_elite=1, epsilon=0.0, alpha=0.0, bounds=(-1.0, 1.0), batch=1, device=0, rank=0,
-                 world=1, seed=0, resample=False, fast_math=False, lanes=0):
+                 world=1, seed=0, resample=False, fast_math=False, lanes=0, model_noise_std=0.0):
         self._h = None
         L = load()
         cfg = MpcConfig()
@@ -148,6 +149,7 @@ class Solver:
         cfg.rank, cfg.world = int(rank), int(world)
         cfg.max_iter, cfg.n_elite, cfg.resample = int(max_iter), int(n_elite), int(bool(resample))
         cfg.fast_math, cfg.lanes = int(bool(fast_math)), int(lanes)
+        cfg.model_noise_std = float(model_noise_std)
         cfg.lam, cfg.sigma, cfg.epsilon, cfg.alpha = float(lam), float(sigma), float(epsilon), float(alpha)
         cfg.bounds_low, cfg.bounds_high = float(bounds[0]), float(bounds[1])
         cfg.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
@@ -303,6 +305,11 @@ class Solver:
     def cem_std(self):
         out, p = _out((self.H,))
         self._ck(self.L.mpc_cem_get_std(self._h, p))
+        return out
+
+    def philox_model_noise(self, solve_index):
+        out, p = _out((self.K_local, self.H, 4))
+        self._ck(self.L.mpc_philox_model_noise(self._h, int(solve_index), p))
         return out
 
     # -- nominal rollout / single steps

@@ -257,6 +257,8 @@ static MppiArgs mppi_args(const mpc_handle *h, int want_traj) {
     a.trace = h->profiling ? h->d_trace : nullptr;
     a.world = h->cfg.world;
     a.rank = h->cfg.rank;
+    a.model_noise = h->cfg.model_noise_std > 0 ? h->cfg.model_noise_std : 0.0;
+    a.noise_draw = (uint32_t)(h->solves & 0xffffffffu);
     return a;
 }
 
@@ -295,6 +297,8 @@ static CemArgs cem_args(const mpc_handle *h, int iter, int want_traj) {
     a.z_stride = h->cem_z_stride;
     a.z_off = h->cfg.world > 1 ? h->g.k_begin : 0;
     a.epoch = h->epoch;
+    a.model_noise = h->cfg.model_noise_std > 0 ? h->cfg.model_noise_std : 0.0;
+    a.noise_draw = (uint32_t)((h->solves * (uint64_t)h->cfg.max_iter + (uint64_t)iter) & 0xffffffffu);
     return a;
 }
 
@@ -405,6 +409,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         return fail(nullptr, MPC_EINVAL, "bad rank/world %d/%d", cfg->rank, cfg->world);
     if (cfg->K < cfg->world) return fail(nullptr, MPC_EINVAL, "K = %d smaller than world = %d", cfg->K, cfg->world);
     if (!(cfg->sigma > 0)) return fail(nullptr, MPC_EINVAL, "std must be > 0");
+    if (!(cfg->model_noise_std >= 0)) return fail(nullptr, MPC_EINVAL, "model_noise_std must be >= 0");
     if (cfg->agent == MPC_AGENT_MPPI && !(cfg->lam > 0)) return fail(nullptr, MPC_EINVAL, "lam must be > 0");
     if (cfg->agent == MPC_AGENT_CEM) {
         if (cfg->batch != 1) return fail(nullptr, MPC_EINVAL, "CEM supports batch = 1");
@@ -460,7 +465,8 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     g.H = cfg->H;
     g.B = cfg->batch;
     // rollout flavour: float32 rolls out two samples per thread (packed f32x2) unless asked otherwise
-    const int lanes = (cfg->dtype == MPC_F32 && cfg->agent == MPC_AGENT_MPPI) ? (cfg->lanes ? cfg->lanes : 2) : 1;
+    const int lanes = (cfg->dtype == MPC_F32 && cfg->agent == MPC_AGENT_MPPI && !(cfg->model_noise_std > 0))
+                          ? (cfg->lanes ? cfg->lanes : 2) : 1;  // the noisy-model flavour rolls out one sample per thread
     g.variant = (cfg->dtype == MPC_F32 && cfg->fast_math ? 1 : 0) | (lanes == 2 ? 2 : 0);
     g.wt = 32 * lanes;
     g.tiles_per_solve = g.Kpad / g.wt;
@@ -503,8 +509,9 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         // the rollout is pipe bound).  MPC_B200_STREAM=0|1 overrides (profiling).
         g.stream_rows = g.stream_depth = 0;
         if (cfg->noise == MPC_NOISE_TENSOR) {
-            bool stream = s_cap < 8;  // measured (tools/stream_probe.py): at 8+ whole-tile warps the two flavours tie
+            bool stream = s_cap < 8 && !(cfg->model_noise_std > 0);  // measured (tools/stream_probe.py): at 8+ whole-tile warps the two flavours tie
             if (const char *e = getenv("MPC_B200_STREAM")) stream = atoi(e) != 0;
+            if (cfg->model_noise_std > 0) stream = false;  // the noisy-model flavour exists for whole tiles only
             if (stream) {
                 g.stream_rows = 8;
                 g.stream_depth = 4;
@@ -676,6 +683,22 @@ int mpc_philox_noise(mpc_handle *h, uint64_t draw, double *out) {
     if (h->cfg.agent == MPC_AGENT_CEM && h->cfg.resample) seed += 0x9E3779B97F4A7C15ull * (h->solves ? h->solves - 1 : 0);
     CU(h, launch_philox_materialize(h->d_scratch, g.K_local, g.k_begin, g.H, seed,
                                     ((uint32_t)draw & 0x7fffffffu) | stream_bit, h->stream));
+    h->launches++;
+    CU(h, cudaMemcpyAsync(out, h->d_scratch, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return MPC_OK;
+}
+
+int mpc_philox_model_noise(mpc_handle *h, uint64_t solve_index, double *out) {
+    if (!h || !out) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "not an MPPI handle");
+    CU(h, cudaSetDevice(h->cfg.device));
+    const Geometry &g = h->g;
+    const size_t n = (size_t)g.K_local * g.H * 4;
+    int rc = ensure_scratch(h, n);
+    if (rc) return rc;
+    CU(h, launch_philox_blocks(h->d_scratch, g.K_local, g.k_begin, g.H, h->cfg.seed, (uint32_t)(solve_index & 0xffffffffu),
+                               4u /* PHILOX_MODEL_MPPI */, h->stream));
     h->launches++;
     CU(h, cudaMemcpyAsync(out, h->d_scratch, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));

@@ -215,6 +215,12 @@ cudaError_t launch_philox_materialize(double *dst, int K_local, int k_begin, int
     philox_materialize_kernel<<<(K_local + 127) / 128, 128, 0, s>>>(dst, K_local, k_begin, H, seed, d, stream);
     return cudaGetLastError();
 }
+cudaError_t launch_philox_blocks(double *dst, int K_local, int k_begin, int n_blocks, uint64_t seed, uint32_t draw,
+                                 uint32_t stream, cudaStream_t s) {
+    // dst [K_local][n_blocks][4]: the four normals of Philox block (sample, block index, draw, stream)
+    philox_materialize_kernel<<<(K_local + 127) / 128, 128, 0, s>>>(dst, K_local, k_begin, 4 * n_blocks, seed, draw, stream);
+    return cudaGetLastError();
+}
 cudaError_t launch_cem_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const CemArgs &a,
                                const CemBuffers &b, cudaStream_t s) {
     return BY_DTYPE(launch_cem_rollout, noise, variant, ep, a, b, s);

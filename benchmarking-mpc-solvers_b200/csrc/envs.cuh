@@ -402,4 +402,20 @@ struct Acrobot<double, FAST> {
     }
 };
 
+// ------------------------------------------------------------------------------------------------ model noise
+// Model.predict of a model with sensor noise adds N(0, std) to every component of the new state (model.py:42-43),
+// after clipping and wrapping.  unit(i) converts the reference's units to the ones step() keeps component i in.
+template <class Env>
+struct NoiseUnit {
+    static __device__ __forceinline__ typename Env::S unit(int) { return (typename Env::S)1; }
+};
+template <bool FAST>
+struct NoiseUnit<Acrobot<float, FAST>> {  // angles in half-turns
+    static __device__ __forceinline__ float unit(int i) { return i < 2 ? 0.318309886f : 1.0f; }
+};
+// One sample per thread (float or double lanes).  Philox counter = (sample, step, draw, stream).
+template <class Env>
+__device__ __forceinline__ void add_model_noise(typename Env::S (&x)[Env::NS], double sigma, uint64_t seed,
+                                                uint32_t stream, uint32_t draw, uint32_t k, uint32_t t);
+
 }  // namespace mpc

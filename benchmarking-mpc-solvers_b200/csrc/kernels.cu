@@ -95,13 +95,28 @@ static EnvConst<V> make_env(const EnvParamsHost &ep) {
     return ec;
 }
 
+template <class Env>
+__device__ __forceinline__ void add_model_noise(typename Env::S (&x)[Env::NS], double sigma, uint64_t seed,
+                                                uint32_t stream, uint32_t draw, uint32_t k, uint32_t t) {
+    typedef typename Env::S R;
+    static_assert(Env::NS <= 4, "one Philox block of four normals per state");
+    float z[4];
+    philox_normal4(seed, stream, draw, k, t, z);
+#pragma unroll
+    for (int i = 0; i < Env::NS; ++i) x[i] += (R)sigma * NoiseUnit<Env>::unit(i) * (R)z[i];
+}
+
+// Philox streams of the model noise: sample rollouts of MPPI / CEM, nominal rollouts
+enum { PHILOX_MODEL_MPPI = 4, PHILOX_MODEL_NOMINAL = 5, PHILOX_MODEL_CEM = 6 };
+
 // Nominal rollout of one plan by a single thread: Agent.simulate_trajectory (agent.py:97-108).
 // us: plan (already clipped by the caller if required); goal row of step t at g_z + t * g_stride (g_stride = 0: one
 // row for every step); xs [H+1][ns] (nullable); returns the cost.  Callers keep us / g_z in shared memory: the loop is
 // a serial dependency chain and must not wait on global loads.
 template <class Env>
 __device__ double nominal_rollout(const EnvConst<typename Env::Vec> &ec, int H, const double *x0, const double *us,
-                                  const double *g_z, int g_stride, double *xs) {
+                                  const double *g_z, int g_stride, double *xs, double model_noise = 0.0,
+                                  uint64_t seed = 0, uint32_t draw = 0, uint32_t which = 0) {
     constexpr int NS = Env::NS;
     typedef typename Env::S R;
     R x[NS];
@@ -117,6 +132,7 @@ __device__ double nominal_rollout(const EnvConst<typename Env::Vec> &ec, int H, 
     for (int t = 0; t < H; ++t) {
         if (g_stride != 0) Env::prep_goal(ec, g_z + t * g_stride, gs);
         const R c = Env::step(ec, x, (R)us[t], gs);
+        if (model_noise > 0.0) add_model_noise<Env>(x, model_noise, seed, PHILOX_MODEL_NOMINAL, draw, which, (uint32_t)t);
         reward += -(double)c;
         if (xs) Env::leave(ec, x, xs + (t + 1) * NS);
     }
@@ -211,6 +227,8 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
             const R z = zt[(size_t)t * a.z_stride + a.z_off + k];
             const R u = vclip(vfma(ssd[t], z, smu[t]), lo, hi);
             reward += -(double)Env::step(ec, x, u, gs);
+            if (a.model_noise > 0.0)
+                add_model_noise<Env>(x, a.model_noise, a.seed, PHILOX_MODEL_CEM, a.noise_draw, (uint32_t)(a.g.k_begin + k), (uint32_t)t);
         }
     } else {
         const uint32_t kglob = (uint32_t)(a.g.k_begin + k);
@@ -223,6 +241,8 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
                 if (t < H) {
                     const R u = vclip(vfma(ssd[t], (R)z[i], smu[t]), lo, hi);
                     reward += -(double)Env::step(ec, x, u, gs);
+                    if (a.model_noise > 0.0)
+                        add_model_noise<Env>(x, a.model_noise, a.seed, PHILOX_MODEL_CEM, a.noise_draw, kglob, (uint32_t)t);
                 }
             }
         }
@@ -302,7 +322,7 @@ __global__ void cem_finish_kernel(const CemArgs a, const EnvConst<typename Env::
         out[0] = mu[0];
         out[2 + H + (H + 1) * NS] = (double)sel[SEL_ITERS];
         if (a.want_traj) {
-            out[1 + H] = nominal_rollout<Env>(ec, H, x0g, sUc, sG, NS + 1, out + 2 + H);
+            out[1 + H] = nominal_rollout<Env>(ec, H, x0g, sUc, sG, NS + 1, out + 2 + H, a.model_noise, a.seed, a.noise_draw, 0u);
         }
     }
 }
@@ -486,10 +506,10 @@ static void with_scalar_env(int env, bool fast, F &&f) {
     }
 }
 
-template <class Env, int NOISE>
+template <class Env, int NOISE, bool NOISY = false>
 static cudaError_t mppi_solve_go(const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b, cudaStream_t s) {
     typedef typename Env::Vec V;
-    auto kern = mppi_solve_kernel<Env, NOISE>;
+    auto kern = mppi_solve_kernel<Env, NOISE, NOISY>;
     const size_t smem = a.g.smem_rollout;
     // per instantiation AND per device (the attribute is a per-device function property): raise the dynamic
     // shared memory limit only when it grows
@@ -541,6 +561,14 @@ size_t FN(mppi_stage_bytes)(int variant, int rows) {
 cudaError_t FN(launch_mppi_solve)(int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
                                   const MppiBuffers &b, cudaStream_t s) {
     cudaError_t e = cudaSuccess;
+    if (a.model_noise > 0.0) {  // noisy model: one sample per thread (capi.cu forces lanes = 1, whole tiles)
+        with_scalar_env(ep.env, (variant & VAR_FAST) != 0, [&](auto env) {
+            typedef decltype(env) E;
+            e = (noise == NOISE_PHILOX) ? mppi_solve_go<E, NOISE_PHILOX, true>(a, ep, b, s)
+                                        : mppi_solve_go<E, NOISE_TENSOR, true>(a, ep, b, s);
+        });
+        return e;
+    }
     with_rollout_env(ep.env, variant, [&](auto env) {
         typedef decltype(env) E;
         if (noise == NOISE_PHILOX)

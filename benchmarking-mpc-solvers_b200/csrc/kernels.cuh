@@ -64,6 +64,8 @@ struct MppiArgs {
     // host-flag completion (batch = 1, host-buffer solve call): the finalising block also writes the solve's outputs
     // into mapped pinned host memory and then raises host_flag to host_epoch — the host polls the flag instead of
     // submitting a D2H copy and a stream synchronise
+    double model_noise;   // std of the noise Model.predict adds to every new state (model.py:42-43); 0 = off
+    uint32_t noise_draw;  // Philox draw of the model noise: the solve counter (fresh per solve)
     double *host_out;                 // null = off; same layout as `out`
     unsigned long long *host_flag;
     unsigned long long host_epoch;
@@ -82,6 +84,8 @@ struct CemArgs {
     int z_stride;         // row stride of the standard-normal tensor (TENSOR noise): Kpad, or the padded FULL K
     int z_off;            // column of this rank's first sample in it: 0, or k_begin
     unsigned long long epoch;  // flag value of this iteration's candidate exchange
+    double model_noise;   // as MppiArgs
+    uint32_t noise_draw;  // solve counter * max_iter + iteration
 };
 
 struct MppiBuffers {
@@ -146,6 +150,8 @@ cudaError_t launch_philox_fill(int dtype, void *dst_HK, int K_local, int k_begin
                                uint64_t seed, uint32_t draw, cudaStream_t s);
 cudaError_t launch_philox_materialize(double *dst_KH, int K_local, int k_begin, int H, uint64_t seed, uint32_t draw,
                                       cudaStream_t s);
+cudaError_t launch_philox_blocks(double *dst_K_n_4, int K_local, int k_begin, int n_blocks, uint64_t seed, uint32_t draw,
+                                 uint32_t stream, cudaStream_t s);
 cudaError_t launch_cem_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b,
                                cudaStream_t s);
 cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s);

@@ -228,13 +228,14 @@ __device__ __forceinline__ void block_apply(const MppiArgs &a, const EnvConst<ty
     stamp(a.trace, TR_APPLIED);
     if (tid == 0 && a.want_traj)
         o[1 + H] = nominal_rollout<typename Env::Scalar>(scalar_consts(ec), H, x0g + (size_t)b * NS, sUc, sG,
-                                                         a.goal_zero ? 0 : NZ, o + 2 + H);
+                                                         a.goal_zero ? 0 : NZ, o + 2 + H, a.model_noise, a.seed,
+                                                         a.noise_draw, (uint32_t)b);
 }
 
 // ================================================================================================ the solve kernel
 // Geometry (capi.cu): tiles are WARP tiles.  mode A (solves_per_block == 0): blocks_per_solve blocks share one solve,
 // block blk works on solve blk / blocks_per_solve.  mode B: a block owns solves_per_block whole solves.
-template <class Env, int NOISE>
+template <class Env, int NOISE, bool NOISY = false>  // NOISY: the model has sensor noise (one sample per thread only)
 __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
     mppi_solve_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec,
                       const __grid_constant__ CUtensorMap noise_map, const typename Env::S *__restrict__ noise_g,
@@ -394,6 +395,11 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
         auto one = [&](int t, const V &e, V &acc) {
             const V u = V(sU[t]) + e;
             const V c = Env::step(ec, x, u, gs);
+            if constexpr (NOISY) {  // newstate += N(0, sensor_std)   model.py:42-43
+                static_assert(PACK == 1, "the noisy-model flavour rolls out one sample per thread");
+                add_model_noise<Env>(x, a.model_noise, a.seed, PHILOX_MODEL_MPPI, a.noise_draw,
+                                     (uint32_t)(a.g.k_begin + kl), (uint32_t)t);
+            }
             acc = acc + vfma(u * e, pert, c);
         };
         auto fold = [&](const V &acc) {
@@ -765,7 +771,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                 double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
                 o[1 + H] = nominal_rollout<typename Env::Scalar>(scalar_consts(ec), H, x0g + (size_t)b * NS, sUc + (size_t)tid * H,
                                                 a.goal_zero ? sG : sG + (size_t)tid * H * NZ, a.goal_zero ? 0 : NZ,
-                                                o + 2 + H);
+                                                o + 2 + H, a.model_noise, a.seed, a.noise_draw, (uint32_t)b);
             }
             __syncthreads();
         }

@@ -127,9 +127,6 @@ class Experiment:
         noise is drawn on the device (Philox, key `seed`): reproducible, unlike the reference's global numpy RNG."""
         from .models import env_spec
         env, model, agent = self._make()
-        if self.model_is_noised:
-            raise NotImplementedError("model_noise (sensor noise inside the rollouts, model.py:42-43) is not part of "
-                                      "the CUDA rollout; use Experiment.run with a host-side noisy model")
         if env_spec(env.model) != env_spec(model):
             raise ValueError("the environment's plant and the agent's model differ; run_device steps the plant with "
                              "the handle's own model parameters")
@@ -266,8 +263,9 @@ def temperature_sweep(env, model, agent, base_config, start_state, lams=(0.001, 
 
 def noise_sweep(env, model, agent, base_config, start_state, stds=(0.1, 0.5, 1.0), kinds=("actuation_noise", "sensor_noise"),
                 experiment_length=100, sink=None, device=True, warmstart=None, repeats=1):
-    """scripts/noise_tests.py:24-49: actuation / sensor noise grid (model_noise is host-loop only, see run_device)."""
-    cfgs = [{"env": env, "model": model, "agent": agent, "agent_config": dict(base_config),
-             "experiment_length": experiment_length, "start_state": start_state, kind: std}
+    """scripts/noise_tests.py:24-49: actuation noise grid, and sensor noise grid with the noisy model (:44)."""
+    cfgs = [dict({"env": env, "model": model, "agent": agent, "agent_config": dict(base_config),
+                  "experiment_length": experiment_length, "start_state": start_state, kind: std},
+                 **({"model_noise": True} if kind == "sensor_noise" else {}))
             for kind in kinds for std in stds]
     return _sweep(cfgs, sink, device, warmstart, repeats)

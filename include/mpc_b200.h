@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define MPC_B200_ABI_VERSION 2
+#define MPC_B200_ABI_VERSION 3
 
 typedef struct mpc_handle mpc_handle;
 
@@ -86,6 +86,10 @@ typedef struct {
     double bounds_high;
     uint64_t seed;        /* PHILOX key */
     double env_params[MPC_MAX_ENV_PARAMS];
+    double model_noise_std; /* Model.set_sensor_noise (model.py:20-24): every Model.predict INSIDE the rollouts (and the
+                             nominal rollout) adds N(0, std) to each component of the new state (model.py:42-43).  0 = off.
+                             The draws are Philox (fresh per solve): statistically the reference's, not its numpy stream
+                             (which is not reproducible there either: forked workers share one RNG state). */
 } mpc_config;
 
 /* ---- lifetime ------------------------------------------------------------------------------------------ */
@@ -109,6 +113,10 @@ int mpc_fill_noise(mpc_handle *h);
  * normals for draw index `draw` (MPPI: solve counter if resample else 0; CEM: iteration counter).  Lets a checker
  * feed the identical noise to a CPU implementation. */
 int mpc_philox_noise(mpc_handle *h, uint64_t draw, double *out_KlocalH);
+/* The standard normals the noisy-model flavour (mpc_config.model_noise_std > 0) adds, times the std, to the new state
+ * of sample k at step t during MPPI solve number `solve_index` (0 = the handle's first solve): out [K_local][H][4],
+ * components 0..ns-1 used (model.py:42-43).  For checkers. */
+int mpc_philox_model_noise(mpc_handle *h, uint64_t solve_index, double *out_KlocalH4);
 
 /* ---- MPPI ---------------------------------------------------------------------------------------------- */
 /* One MPPI._calc_action (mppi.py:54-75) for `batch` independent solves, fused with what Agent.predict_action does

@@ -235,6 +235,7 @@ typedef struct {
     const double *x0, *U, *eps, *goal;
     double lam, pinv;
     double *S;
+    const double *xnoise; /* NULL, or [K][H][ns]: the draws of model.py:42-43 when the model has sensor noise */
 } mppi_ctx;
 
 static void mppi_range(void *vctx, int k0, int k1) {
@@ -249,6 +250,8 @@ static void mppi_range(void *vctx, int k0, int k1) {
             orc_step(c->m, x, test_u, c->goal, &cost, xn);           /* mppi.py:43-44 */
             sample_cost += cost + ((c->lam * test_u) * c->pinv) * e; /* mppi.py:45-46 */
             for (int i = 0; i < ns; ++i) x[i] = xn[i];
+            if (c->xnoise) /* newstate += np.random.normal(0, sensor_std, state_size)   model.py:42-43 */
+                for (int i = 0; i < ns; ++i) x[i] += c->xnoise[((long)k * H + t) * ns + i];
         }
         c->S[k] = sample_cost;
     }
@@ -257,7 +260,16 @@ static void mppi_range(void *vctx, int k0, int k1) {
 /* MPPI.f for all K samples.  eps is the reference layout [K][H] (du = 1); goal = g_z[0]. */
 void orc_mppi_costs(const orc_model *m, int K, int H, const double *x0, const double *U, const double *eps,
                     const double *goal, double lam, double sigma, double *S, int nthreads) {
-    mppi_ctx c = {m, H, x0, U, eps, goal, lam, 1.0 / (sigma * sigma) /* np.linalg.pinv(std**2), 1x1 */, S};
+    mppi_ctx c = {m, H, x0, U, eps, goal, lam, 1.0 / (sigma * sigma) /* np.linalg.pinv(std**2), 1x1 */, S, NULL};
+    orc_parallel_for(mppi_range, &c, K, nthreads);
+}
+
+/* The same with a noisy model (Model.set_sensor_noise, model.py:20-24,42-43): xnoise [K][H][ns] holds the normal draws,
+ * already scaled by sensor_std, that predict adds to each new state.  The reference draws them from numpy's global RNG
+ * inside forked workers (not reproducible); handing them in makes the restatement deterministic. */
+void orc_mppi_costs_noisy(const orc_model *m, int K, int H, const double *x0, const double *U, const double *eps,
+                          const double *goal, double lam, double sigma, const double *xnoise, double *S, int nthreads) {
+    mppi_ctx c = {m, H, x0, U, eps, goal, lam, 1.0 / (sigma * sigma), S, xnoise};
     orc_parallel_for(mppi_range, &c, K, nthreads);
 }
 

@@ -55,6 +55,8 @@ def lib():
         L.orc_step.restype = None
         L.orc_mppi_costs.argtypes = [mp, C.c_int, C.c_int, dp, dp, dp, dp, C.c_double, C.c_double, dp, C.c_int]
         L.orc_mppi_costs.restype = None
+        L.orc_mppi_costs_noisy.argtypes = [mp, C.c_int, C.c_int, dp, dp, dp, dp, C.c_double, C.c_double, dp, dp, C.c_int]
+        L.orc_mppi_costs_noisy.restype = None
         L.orc_mppi_update.argtypes = [C.c_int, C.c_int, dp, dp, C.c_double, dp, dp]
         L.orc_mppi_update.restype = None
         L.orc_simulate.argtypes = [mp, C.c_int, dp, dp, dp, dp, dp]
@@ -111,6 +113,21 @@ def mppi_costs(m, x0, U, eps, lam, sigma, goal=None, nthreads=1):
     S = np.zeros(K)
     lib().orc_mppi_costs(C.byref(m), K, H, xp, Up, ep, gp, float(lam), float(sigma),
                          S.ctypes.data_as(C.POINTER(C.c_double)), int(nthreads))
+    return S
+
+
+def mppi_costs_noisy(m, x0, U, eps, lam, sigma, xnoise, goal=None, nthreads=1):
+    """MPPI.f with a model that has sensor noise (model.py:42-43): xnoise [K,H,ns] = the scaled normal draws."""
+    eps = np.asarray(eps, dtype=np.float64)
+    K, H = eps.shape[0], eps.shape[1]
+    x_, xp = _d(x0)
+    U_, Up = _d(np.asarray(U).reshape(-1))
+    e_, ep = _d(eps.reshape(K, H))
+    n_, np_ = _d(np.asarray(xnoise, dtype=np.float64).reshape(K, H, m.ns))
+    g_, gp = _d(np.zeros(m.ns + 1) if goal is None else goal)
+    S = np.zeros(K)
+    lib().orc_mppi_costs_noisy(C.byref(m), K, H, xp, Up, ep, gp, float(lam), float(sigma), np_,
+                               S.ctypes.data_as(C.POINTER(C.c_double)), int(nthreads))
     return S
 
 
