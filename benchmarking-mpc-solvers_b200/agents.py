@@ -8,6 +8,7 @@ sampling inner loop executed by libmpcb200.so on a B200.
 Extra, optional params keys (defaults reproduce the reference): "dtype" ("f64" | "f32"), "noise" ("tensor": host
 numpy noise exactly as the reference draws it | "philox": generated in-kernel), "fast_math" (f32: MUFU trig),
 "lanes" (f32 MPPI: samples per thread, 1 | 2), "seed", "resample", "device",
+"devices" (list: ONE process drives several GPUs, K sharded over them — no torchrun needed),
 "rank"/"world"/"comm_id" (K-sharding across GPUs, one process per GPU).
 
 What stays on the host is only what the reference's Agent base class does around `_calc_action`
@@ -97,6 +98,21 @@ class _GpuAgent(Agent):
     def _make_solver(self, kind, params, **kw):
         env, env_params = env_spec(self.model)
         self._env_id = env
+        devices = params.get("devices")
+        if devices is not None and len(devices) > 1:
+            # one process, several GPUs: K sharded over `devices`, exchange inside the kernels over NVLink
+            self._solver = capi.SolverGroup(
+                kind, env, env_params, self.K, self.horizon_length, devices,
+                dtype=params.get("dtype", "f64"), noise=params.get("noise", "tensor"),
+                bounds=(float(np.ravel(self.bounds_low)[0]), float(np.ravel(self.bounds_high)[0])),
+                seed=params.get("seed", 0), resample=params.get("resample", False),
+                fast_math=params.get("fast_math", False), lanes=params.get("lanes", 0),
+                model_noise_std=float(getattr(self.model, "sensor_std", 0.0)) if getattr(self.model, "sensor_noise", False) else 0.0,
+                **kw)
+            self._traj = None
+            return
+        if devices is not None and len(devices) == 1:
+            params = dict(params, device=int(devices[0]))
         self._solver = capi.Solver(
             kind, env, env_params, K=self.K, H=self.horizon_length,
             dtype=params.get("dtype", "f64"), noise=params.get("noise", "tensor"),

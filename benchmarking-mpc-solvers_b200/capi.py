@@ -29,7 +29,7 @@ SYMBOLS = [
     "mpc_cem_solve", "mpc_cem_get_rewards", "mpc_cem_get_elites", "mpc_cem_get_std", "mpc_simulate", "mpc_model_step",
     "mpc_comm_create_id", "mpc_comm_init", "mpc_mppi_rollout_partial", "mpc_mppi_apply_partials", "mpc_upload_inputs", "mpc_solve_enqueue", "mpc_download_outputs",
     "mpc_timer_start", "mpc_timer_stop", "mpc_sync", "mpc_set_profiling", "mpc_get_rollout_ms", "mpc_launch_count", "mpc_get_geometry", "mpc_measure_fma_peak",
-    "mpc_flush_l2", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace", "mpc_episode_run", "mpc_philox_model_noise",
+    "mpc_flush_l2", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace", "mpc_episode_run", "mpc_philox_model_noise", "mpc_cem_get_iterations",
 ]
 
 
@@ -95,6 +95,7 @@ def load():
     L.mpc_p2p_import.argtypes = [hp, C.c_void_p]
     L.mpc_p2p_link.argtypes = [C.POINTER(hp), C.c_int32]
     L.mpc_get_trace.argtypes = [hp, C.POINTER(C.c_uint64)]
+    L.mpc_cem_get_iterations.argtypes = [hp, C.POINTER(C.c_int32)]
     L.mpc_philox_model_noise.argtypes = [hp, C.c_uint64, _dp]
     L.mpc_episode_run.argtypes = [hp, _dp, _dp, C.POINTER(MpcEpisodeOpts)] + [_dp] * 8
     L.mpc_mppi_rollout_partial.argtypes = [hp, _dp, _dp, _dp, _dp]
@@ -292,6 +293,11 @@ class Solver:
             return arrs["u0"].copy(), arrs["Uo"][0].copy(), arrs["xs"][0].copy(), arrs["cost"].copy(), iters.value
         return arrs["u0"].copy(), arrs["Uo"][0].copy(), None, None, iters.value
 
+    def cem_iterations(self):
+        n = C.c_int32(0)
+        self._ck(self.L.mpc_cem_get_iterations(self._h, C.byref(n)))
+        return n.value
+
     def cem_rewards(self, it):
         out, p = _out((self.K_local,))
         self._ck(self.L.mpc_cem_get_rewards(self._h, int(it), p))
@@ -475,3 +481,85 @@ def measure_fma_peak(device=0, dtype="f32"):
     if rc != MPC_OK:
         raise MpcError(rc, (load().mpc_last_error(None) or b"").decode())
     return out.value
+
+
+class SolverGroup:
+    """One process driving several GPUs ("no torchrun needed for a drop-in class"): one handle per
+    device, K sharded across them, exchange buffers wired with mpc_p2p_link so that the all-gather of the rank records
+    (MPPI) / elite candidates (CEM) happens inside the kernels over NVLink.  Presents the part of Solver's surface the
+    agents use; every rank ends with the identical plan, rank 0's copy is returned."""
+
+    def __init__(self, agent, env, env_params, K, H, devices, **kw):
+        kw.pop("device", None), kw.pop("rank", None), kw.pop("world", None)
+        if kw.get("batch", 1) != 1:
+            raise ValueError("a device group shards ONE solve; use one handle per device for batches")
+        self.ranks = []
+        try:
+            for r, d in enumerate(devices):
+                self.ranks.append(Solver(agent, env, env_params, K, H, device=int(d), rank=r, world=len(devices), **kw))
+            Solver.p2p_link(self.ranks)
+        except Exception:
+            self.close()
+            raise
+        s0 = self.ranks[0]
+        self.is_mppi, self.tensor_noise = s0.is_mppi, s0.tensor_noise
+        self.K, self.H, self.B, self.ns, self.nz = s0.K, s0.H, s0.B, s0.ns, s0.nz
+        self.fast_math, self.lanes, self.geometry = s0.fast_math, s0.lanes, s0.geometry
+
+    def close(self):
+        for s in self.ranks:
+            s.close()
+        self.ranks = []
+
+    # noise: every handle takes its own shard of the GLOBAL tensor
+    def set_noise(self, delta_u):
+        for s in self.ranks:
+            s.set_noise(delta_u)
+
+    def fill_noise(self):
+        for s in self.ranks:
+            s.fill_noise()
+
+    def _solve_all(self, x, g_z, U_in):
+        for s in self.ranks:
+            s.upload_inputs(x, g_z, U_in)
+        for s in self.ranks:  # enqueue everywhere before waiting anywhere: the kernels wait for each other's records
+            s.solve_enqueue()
+        outs = [s.download_outputs() for s in self.ranks]
+        return outs[0]
+
+    def mppi_solve(self, x, g_z=None, U_in=None, want_traj=True):
+        u0, U, xs, cost = self._solve_all(x, g_z, U_in)
+        return (u0, U, xs, cost) if want_traj else (u0, U, None, None)
+
+    def mppi_costs(self):
+        return np.concatenate([s.mppi_costs() for s in self.ranks], axis=1)
+
+    def cem_solve(self, x, g_z=None, U_in=None, want_traj=True):
+        u0, U, xs, cost = self._solve_all(x, g_z, U_in)
+        return u0, U[0], (xs[0] if want_traj else None), (cost if want_traj else None), self.ranks[0].cem_iterations()
+
+    def cem_begin(self, x, g_z=None, U_in=None):
+        for s in self.ranks:
+            s.cem_begin(x, g_z, U_in)
+
+    def cem_iterate(self, z=None):
+        for s in self.ranks[:-1]:
+            s.cem_iterate(z, wait=False)
+        return self.ranks[-1].cem_iterate(z, wait=True)  # every rank reaches the same verdict
+
+    def cem_end(self, want_traj=True):
+        outs = [s.cem_end(want_traj) for s in self.ranks]
+        return outs[0]
+
+    def cem_elites(self, it):
+        return self.ranks[0].cem_elites(it)
+
+    def simulate(self, x, us, g_z=None):
+        return self.ranks[0].simulate(x, us, g_z)
+
+    def model_step(self, x, u, g=None):
+        return self.ranks[0].model_step(x, u, g)
+
+    def episode_run(self, *a, **k):
+        raise MpcError(MPC_ESTATE, "device-resident episodes run on one GPU (world = 1); use Experiment.run with a device group")

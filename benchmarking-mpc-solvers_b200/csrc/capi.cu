@@ -1016,6 +1016,17 @@ int mpc_cem_get_elites(mpc_handle *h, int32_t iter, int32_t *idx_out) {
     return MPC_OK;
 }
 
+int mpc_cem_get_iterations(mpc_handle *h, int32_t *iters_out) {
+    if (!h || !iters_out) return fail(h, MPC_EINVAL, "null argument");
+    if (h->cfg.agent != MPC_AGENT_CEM) return fail(h, MPC_ESTATE, "not a CEM handle");
+    CU(h, cudaSetDevice(h->cfg.device));
+    double it = 0.0;  // cem_finish_kernel leaves the executed iteration count behind the solve's outputs
+    CU(h, cudaMemcpyAsync(&it, h->d_out + h->out_stride, sizeof it, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    *iters_out = h->last_iters = (int)it;
+    return MPC_OK;
+}
+
 int mpc_cem_get_std(mpc_handle *h, double *std_out) {
     if (!h || !std_out) return fail(h, MPC_EINVAL, "null argument");
     if (h->cfg.agent != MPC_AGENT_CEM) return fail(h, MPC_ESTATE, "not a CEM handle");

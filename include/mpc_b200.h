@@ -157,6 +157,8 @@ int mpc_cem_solve(mpc_handle *h, const double *x, const double *g_z, const doubl
  * ascending.  (cem.py:64,67) */
 int mpc_cem_get_rewards(mpc_handle *h, int32_t iter, double *R_out);
 int mpc_cem_get_elites(mpc_handle *h, int32_t iter, int32_t *idx_out);
+/* Iterations the last solve executed before all(std < epsilon) stopped it (cem.py:76-77), at most max_iter. */
+int mpc_cem_get_iterations(mpc_handle *h, int32_t *iters_out);
 /* Current std of solve 0 (cem.py:73): out [H]. */
 int mpc_cem_get_std(mpc_handle *h, double *std_out);
 

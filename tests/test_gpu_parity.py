@@ -366,6 +366,30 @@ def test_cem_sharded_two_gpus(noise):
         s.close()
 
 
+@pytest.mark.skipif(_device_count() < 2, reason="needs two GPUs (run under gpurun --gpus 2)")
+@pytest.mark.parametrize("agent_name", ["MPPI", "CEM"])
+def test_drop_in_agents_over_a_device_group(agent_name):
+    """params["devices"] = [0, 1]: ONE process, K sharded over both GPUs, same constructor / predict_action as the
+    reference — the actions and plans equal the single-GPU agent's (same numpy RNG stream on both sides)."""
+    cfg = ({"K": 1000, "T": 25, "std": 1.0, "lam": 0.5} if agent_name == "MPPI" else
+           {"K": 600, "T": 15, "max_iter": 4, "n_elite": 60, "epsilon": 1e-5, "alpha": 0.2, "std": 1.0})
+    cls = getattr(mpc_b200, agent_name)
+    x = np.array([0.1, 0.0, np.pi, -0.2])
+    goal = np.zeros(5)
+    runs = []
+    for extra in ({}, {"devices": [0, 1]}):
+        np.random.seed(4)
+        agent = cls(mpc_b200.CartPoleSwingUpModel(), dict(cfg, **extra))
+        acts = [agent.predict_action(x + 0.01 * i, goal_state=goal) for i in range(4)]
+        runs.append((np.array(acts), agent.planned_us.copy(), agent.planned_xs.copy()))
+        if agent_name == "MPPI":
+            assert agent.last_sample_costs().shape == (cfg["K"],)
+        agent.close()
+    np.testing.assert_allclose(runs[1][0], runs[0][0], rtol=1e-10, atol=1e-12)
+    np.testing.assert_allclose(runs[1][1], runs[0][1], rtol=1e-10, atol=1e-12)
+    np.testing.assert_allclose(runs[1][2], runs[0][2], rtol=1e-9, atol=1e-9)
+
+
 def test_mppi_full_size_properties():
     """BASELINE full size (K = 2^20, H = 50, float32, Philox): size-independent properties.
        (1) sample k's cost depends only on (seed, k): the first 4096 costs equal a K = 4096 solve's costs bit for bit;
