@@ -144,47 +144,93 @@ __device__ __forceinline__ void peer_signal_and_wait(const PeerTable &pt, const 
 // ------------------------------------------------------------------------------------------------ record merging
 // Block-wide merge of `count` records (beta_j, eta_j, E_j[H]) at src + j * stride: beta = min beta_j,
 // eta = sum s_j eta_j, Eout[t] = sum s_j E_j[t] with s_j = exp(-(beta_j - beta)/lam).  The records were written by
-// other blocks (or ranks): they are read through L2 (__ldcg).  Warp w owns records j = w, w + nw, ... (eight loads in
-// flight per thread), lanes own time steps; the per-warp sums meet in shared memory in a fixed order, so repeated
-// solves are bit-identical.  Scratch: sscale[count], sEw[nw][H], red[32].  All threads return beta / eta.
+// other blocks (or ranks): they are read through L2 (__ldcg).  The merge is latency bound (a few KB per thread
+// block, on the critical path of every solve), so ALL loads of the common case are issued before the first
+// reduction: the headers (beta_j, eta_j) by thread j, and the first MERGE_BATCH records of every column by the
+// thread that owns (column t, record group g) — the scales are applied to registers once they are known.  Threads
+// are laid out as G groups x TT columns (TT = power of two >= H); group g owns records g, g + G, ...; the group sums
+// meet in shared memory in a fixed order, so repeated solves are bit-identical.
+// Scratch: sscale[count], sEw[>= G][H] (callers size it [warps][H]; G <= warps), red[32].  All threads return beta / eta.
+constexpr int MERGE_BATCH = 20;
 __device__ __forceinline__ void block_merge(const double neg_inv_lam, const int H, const double *src, const int count,
                                             const size_t stride, double *sscale, double *sEw, double *red,
                                             double *Eout, double *beta_out, double *eta_out) {
-    const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, w = tid >> 5, nw = nt >> 5;
-    double m = INFINITY;
-    for (int j = tid; j < count; j += nt) m = fmin(m, __ldcg(src + j * stride));
-    const double beta = block_reduce<true>(m, red);
-    double es = 0.0;
-    for (int j = tid; j < count; j += nt) {
-        const double sc = rec_scale(neg_inv_lam, __ldcg(src + j * stride), beta);
-        sscale[j] = sc;
-        es += sc * __ldcg(src + j * stride + 1);
+    const int tid = threadIdx.x, nt = blockDim.x;
+    int TT = 32;
+    while (TT < H && TT < nt) TT <<= 1;
+    const bool by_column = TT >= H;  // every column has its own thread in each group (else: blocks narrower than H)
+    const int G = nt / TT, t = tid & (TT - 1), g = tid / TT;
+    const bool single = count <= nt;  // one header per thread
+    // ---- every load of the common case, issued back to back
+    double b0 = INFINITY, e0 = 0.0, m = INFINITY;
+    if (single) {
+        if (tid < count) {
+            b0 = __ldcg(src + (size_t)tid * stride);
+            e0 = __ldcg(src + (size_t)tid * stride + 1);
+        }
+        m = b0;
+    } else {
+        for (int j = tid; j < count; j += nt) m = fmin(m, __ldcg(src + (size_t)j * stride));
     }
-    const double eta = block_reduce<false>(es, red);  // its barriers publish sscale
-    for (int t0 = 0; t0 < H; t0 += 32) {
-        const int t = t0 + lane;
-        double e[8];
+    double ereg[MERGE_BATCH];
+    const double *col = src + PART_HDR + t;
+    if (by_column && t < H) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) e[i] = 0.0;
-        if (t < H) {
-            const double *col = src + PART_HDR + t;
-            int j = w;
-            for (; j + 7 * nw < count; j += 8 * nw) {
-                double v[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = __ldcg(col + (size_t)(j + i * nw) * stride);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) e[i] += sscale[j + i * nw] * v[i];
-            }
-            for (; j < count; j += nw) e[0] += sscale[j] * __ldcg(col + (size_t)j * stride);
-            sEw[w * H + t] = ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
+        for (int i = 0; i < MERGE_BATCH; ++i) {
+            const int j = g + i * G;
+            ereg[i] = (j < count) ? __ldcg(col + (size_t)j * stride) : 0.0;
         }
     }
-    __syncthreads();
-    for (int t = tid; t < H; t += nt) {
-        double E = 0.0;
-        for (int i = 0; i < nw; ++i) E += sEw[i * H + t];
-        Eout[t] = E;
+    // ---- beta, scales, eta
+    const double beta = block_reduce<true>(m, red);
+    double es = 0.0;
+    if (single) {
+        if (tid < count) {
+            const double sc = rec_scale(neg_inv_lam, b0, beta);
+            sscale[tid] = sc;
+            es = sc * e0;
+        }
+    } else {
+        for (int j = tid; j < count; j += nt) {
+            const double sc = rec_scale(neg_inv_lam, __ldcg(src + (size_t)j * stride), beta);
+            sscale[j] = sc;
+            es += sc * __ldcg(src + (size_t)j * stride + 1);
+        }
+    }
+    const double eta = block_reduce<false>(es, red);  // its barriers publish sscale
+    // ---- E
+    if (by_column) {
+        if (t < H) {
+            double acc = 0.0;
+#pragma unroll
+            for (int i = 0; i < MERGE_BATCH; ++i) {
+                const int j = g + i * G;
+                if (j < count) acc += sscale[j] * ereg[i];
+            }
+            int j = g + MERGE_BATCH * G;
+            for (; j + 7 * G < count; j += 8 * G) {  // records beyond the preloaded batch: eight loads in flight
+                double v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = __ldcg(col + (size_t)(j + i * G) * stride);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) acc += sscale[j + i * G] * v[i];
+            }
+            for (; j < count; j += G) acc += sscale[j] * __ldcg(col + (size_t)j * stride);
+            sEw[g * H + t] = acc;
+        }
+        __syncthreads();
+        for (int tt = tid; tt < H; tt += nt) {
+            double E = 0.0;
+            for (int i = 0; i < G; ++i) E += sEw[i * H + tt];
+            Eout[tt] = E;
+        }
+    } else {
+        // narrow blocks (fewer threads than H rounded up): every thread walks its columns, all records
+        for (int tt = tid; tt < H; tt += nt) {
+            double E = 0.0;
+            for (int j = 0; j < count; ++j) E += sscale[j] * __ldcg(src + (size_t)j * stride + PART_HDR + tt);
+            Eout[tt] = E;
+        }
     }
     __syncthreads();
     *beta_out = beta;
