@@ -49,55 +49,128 @@ __device__ __forceinline__ int block_scan_excl(int v, int *swarp, int *total) {
 }
 
 // Radix select of the `want` largest of n keys by one block of 1024 threads (np.argsort(-rewards)[:n_elite],
-// cem.py:67): 8 passes of 8 bits from the top find the want-th largest key T; then an ordered compaction emits, in
+// cem.py:67): passes of 8 bits from the top find the want-th largest key T; then an ordered compaction emits, in
 // ascending position, every key > T plus the lowest-position keys equal to T needed to reach `want`.
-// key(i) reads key i; emit(pos, i) receives output slot pos for input position i.  Returns the number emitted.
+// key(i) reads key i; emit(pos, i) receives output slot pos for input position i.
+// Up to SEL_KPT keys per thread (n <= 8192) live in REGISTERS, positions tid * SEL_KPT + i (blocked: one pair of block
+// scans orders the whole output); the 256-bin scan of a pass is done by warp 0 alone, the histogram is double
+// buffered (two barriers per pass), and the passes stop as soon as the bin that holds the want-th key is wanted
+// entirely (then every key with that prefix is selected; with distinct float64 rewards that is after the 2-3 digits
+// that differ).  Larger n fall back to re-reading the keys through key_at().
+constexpr int SEL_KPT = 8;
 template <class KeyFn, class EmitFn>
 __device__ __forceinline__ void radix_select_block(const int n, const int want_total, KeyFn key_at, EmitFn emit, int *hist,
                                                    int *swarp, unsigned long long *s_prefix, int *s_want) {
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const bool in_regs = n <= SEL_KPT * (int)blockDim.x;
+    unsigned long long kr[SEL_KPT];
+    if (in_regs) {
+#pragma unroll
+        for (int i = 0; i < SEL_KPT; ++i) {
+            const int p = tid * SEL_KPT + i;
+            kr[i] = (p < n) ? key_at(p) : 0ull;
+        }
+    }
     __syncthreads();
     if (tid == 0) {
         *s_prefix = 0ull;
         *s_want = want_total;
+        hist[512] = 0;  // "stop" flag
     }
+    if (tid < 256) hist[tid] = 0;
+    __syncthreads();
     unsigned long long mask = 0ull;
+    int buf = 0;
     for (int shift = 56; shift >= 0; shift -= 8) {
-        if (tid < 256) hist[tid] = 0;
-        __syncthreads();
+        int *hb = hist + buf * 256;
         const unsigned long long prefix = *s_prefix;
         const int want = *s_want;
-        for (int k = tid; k < n; k += blockDim.x) {
-            const unsigned long long key = key_at(k);
-            if ((key & mask) == prefix) atomicAdd(&hist[(int)((key >> shift) & 0xffull)], 1);
+        if (in_regs) {
+#pragma unroll
+            for (int i = 0; i < SEL_KPT; ++i)
+                if (tid * SEL_KPT + i < n && (kr[i] & mask) == prefix) atomicAdd(&hb[(int)((kr[i] >> shift) & 0xffull)], 1);
+        } else {
+            for (int k = tid; k < n; k += blockDim.x) {
+                const unsigned long long key = key_at(k);
+                if ((key & mask) == prefix) atomicAdd(&hb[(int)((key >> shift) & 0xffull)], 1);
+            }
         }
+        if (tid < 256) hist[(buf ^ 1) * 256 + tid] = 0;  // the other buffer, for the next pass
         __syncthreads();
-        // descending inclusive scan over the 256 bins: thread i looks at bin 255 - i
-        const int v = (tid < 256) ? hist[255 - tid] : 0;
-        int total;
-        const int excl = block_scan_excl(v, swarp, &total);
-        if (tid < 256 && excl < want && excl + v >= want) {
-            *s_prefix = prefix | ((unsigned long long)(255 - tid) << shift);
-            *s_want = want - excl;
+        if (w == 0) {
+            // descending scan over the 256 bins: lane l owns bins 255 - 8 l ... 248 - 8 l
+            int c[8], sum = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                c[i] = hb[255 - 8 * lane - i];
+                sum += c[i];
+            }
+            int inc = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += v;
+            }
+            int excl = inc - sum;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (excl < want && excl + c[i] >= want) {
+                    *s_prefix = prefix | ((unsigned long long)(255 - 8 * lane - i) << shift);
+                    *s_want = want - excl;
+                    if (c[i] == want - excl) hist[512] = 1;  // the whole bin is wanted: nothing left to decide
+                }
+                excl += c[i];
+            }
         }
         mask |= 0xffull << shift;
+        buf ^= 1;
         __syncthreads();
+        if (hist[512]) break;
     }
-    const unsigned long long T = *s_prefix;
-    const int want_ties = *s_want;  // how many keys == T belong to the selection
-    int tie_base = 0, sel_base = 0;
-    for (int k0 = 0; k0 < n; k0 += blockDim.x) {
-        const int k = k0 + tid;
-        const unsigned long long key = (k < n) ? key_at(k) : 0ull;
-        const int is_tie = (k < n && key == T) ? 1 : 0;
-        const int is_gt = (k < n && key > T) ? 1 : 0;
-        int tot_tie, tot_sel;
-        const int tie_rank = tie_base + block_scan_excl(is_tie, swarp, &tot_tie);
-        const int chosen = is_gt | (is_tie && tie_rank < want_ties);
-        const int pos = sel_base + block_scan_excl(chosen, swarp, &tot_sel);
-        if (chosen && pos < want_total) emit(pos, k);
-        tie_base += tot_tie;
-        sel_base += tot_sel;
+    const unsigned long long T = *s_prefix;  // with `mask`: keys whose masked bits exceed T are in, equal ones tie
+    const int want_ties = *s_want;           // how many of the tying keys belong to the selection (lowest positions)
+    if (in_regs) {
+        int n_tie = 0;
+#pragma unroll
+        for (int i = 0; i < SEL_KPT; ++i) n_tie += (tid * SEL_KPT + i < n && (kr[i] & mask) == T) ? 1 : 0;
+        int tot;
+        int tie_rank = block_scan_excl(n_tie, swarp, &tot);
+        int n_sel = 0;
+        unsigned chosen = 0u;
+#pragma unroll
+        for (int i = 0; i < SEL_KPT; ++i) {
+            const bool valid = tid * SEL_KPT + i < n;
+            const unsigned long long km = kr[i] & mask;
+            const bool tie = valid && km == T;
+            if ((valid && km > T) || (tie && tie_rank < want_ties)) {
+                chosen |= 1u << i;
+                ++n_sel;
+            }
+            tie_rank += tie ? 1 : 0;
+        }
+        __syncthreads();  // swarp is reused by the second scan
+        int pos = block_scan_excl(n_sel, swarp, &tot);
+#pragma unroll
+        for (int i = 0; i < SEL_KPT; ++i)
+            if (chosen & (1u << i)) {
+                if (pos < want_total) emit(pos, tid * SEL_KPT + i);
+                ++pos;
+            }
+    } else {
+        int tie_base = 0, sel_base = 0;
+        for (int k0 = 0; k0 < n; k0 += blockDim.x) {
+            const int k = k0 + tid;
+            const unsigned long long km = (k < n) ? (key_at(k) & mask) : 0ull;
+            const int is_tie = (k < n && km == T) ? 1 : 0;
+            const int is_gt = (k < n && km > T) ? 1 : 0;
+            int tot_tie, tot_sel;
+            const int tie_rank = tie_base + block_scan_excl(is_tie, swarp, &tot_tie);
+            const int chosen = is_gt | (is_tie && tie_rank < want_ties);
+            const int pos = sel_base + block_scan_excl(chosen, swarp, &tot_sel);
+            if (chosen && pos < want_total) emit(pos, k);
+            tie_base += tot_tie;
+            sel_base += tot_sel;
+        }
     }
     __syncthreads();
 }
@@ -113,7 +186,7 @@ __global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const
                                                          int *__restrict__ elite_hist, int *__restrict__ sel,
                                                          const PeerTable pt, double *__restrict__ err_word) {
     if (sel[SEL_DONE]) return;
-    __shared__ int hist[256];
+    __shared__ int hist[2 * 256 + 1];  // double-buffered digit histogram + stop flag
     __shared__ int swarp[64];
     __shared__ unsigned long long s_prefix;
     __shared__ int s_want;
