@@ -226,7 +226,7 @@ class Solver:
         if hb is None:
             B, H, ns = self.B, self.H, self.ns
             arrs = dict(x=np.empty((B, ns)), U=np.empty((B, H)), g=np.empty((B, H, self.nz)), u0=np.empty(B),
-                        Uo=np.empty((B, H)), xs=np.empty((B, H + 1, ns)), cost=np.empty(B))
+                        Uo=np.empty((B, H)), xs=np.empty((B if B == 1 else 0, H + 1, ns)), cost=np.empty(B))
             hb = self._hb = (arrs, {k: v.ctypes.data for k, v in arrs.items()})
         return hb
 
@@ -246,6 +246,13 @@ class Solver:
 
     def mppi_solve(self, x, g_z=None, U_in=None, want_traj=True):
         arrs, ptr, gp, up = self._stage_hot(x, g_z, U_in)
+        if self.B > 1:  # batches: outputs are megabytes, let the library write the caller's arrays directly
+            u0, U = np.empty(self.B), np.empty((self.B, self.H))
+            xs = np.empty((self.B, self.H + 1, self.ns)) if want_traj else None
+            cost = np.empty(self.B) if want_traj else None
+            self._ck(self.L.mpc_mppi_solve(self._h, ptr["x"], gp, up, u0.ctypes.data, U.ctypes.data,
+                                           xs.ctypes.data if want_traj else None, cost.ctypes.data if want_traj else None))
+            return u0, U, xs, cost
         if want_traj:
             self._ck(self.L.mpc_mppi_solve(self._h, ptr["x"], gp, up, ptr["u0"], ptr["Uo"], ptr["xs"], ptr["cost"]))
             return arrs["u0"].copy(), arrs["Uo"].copy(), arrs["xs"].copy(), arrs["cost"].copy()
