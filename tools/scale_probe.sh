@@ -1,5 +1,5 @@
 # N-GPU bench lines (run under gpurun --gpus 8): the driver's own launch line, per workload
-for n in 8 4; do
+for n in ${SCALE_NS:-8 4}; do
 for wl in mppi_pendulum_h50_k1m mppi_cartpole_h50_k1m mppi_acrobot_h100_k1m; do
   CUDA_VISIBLE_DEVICES=$(seq -s, 0 $((n-1))) python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n --steps 20 --warmup 5 --no-extra --workload $wl 2>gpurun_out/scale_n${n}_$wl.err | tail -1 > gpurun_out/scale_n${n}_$wl.json
   python - <<PY
