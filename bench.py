@@ -439,6 +439,13 @@ def run_ours(args, dist):
     steps_total = float(K) * H * args.steps
     value = steps_total / (total_ms * 1e-3)
 
+    # phase stamps of the last timed solve's finalising block on rank 0 (us since its kernel start): where a solve's
+    # time goes when the shard is small (tiles_done = rollouts finished; peers_in = every rank's record has arrived)
+    try:
+        tr = s.trace()
+        trace_us = {k: round(v / 1e3, 1) for k, v in tr.items() if v is not None and k != "start"}
+    except Exception:
+        trace_us = None
     e2e_total, lat = time_e2e(s, x, U, args.steps, args.warmup, dist)
     e2e_value = steps_total / e2e_total
     h2d = (s.ns + H) * 8
@@ -481,7 +488,7 @@ def run_ours(args, dist):
         "clocks": clk, "gpu_launches": launches,
         "e2e": {"value": e2e_value, "unit": "rollout-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "p50_solve_ms": round(1e3 * statistics.median(lat), 4)},
-        "roofline": roofline, "roofline_hbm": roofline_hbm, "wall_s_timed_loop": wall,
+        "roofline": roofline, "roofline_hbm": roofline_hbm, "wall_s_timed_loop": wall, "solve_phases_us": trace_us,
     }
     s.close()
     if dist.rank == 0:

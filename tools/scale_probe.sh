@@ -5,7 +5,7 @@ for wl in mppi_pendulum_h50_k1m mppi_cartpole_h50_k1m mppi_acrobot_h100_k1m; do
   python - <<PY
 import json
 try:
-    d=json.load(open("gpurun_out/scale_n${n}_$wl.json")); print("$wl", d["n_gpus"], "%.3e"%d["value"], "ms %.4f"%d["ms_per_step"], "e2e %.3e"%d["e2e"]["value"], d["e2e"]["p50_solve_ms"])
+    d=json.load(open("gpurun_out/scale_n${n}_$wl.json")); print("$wl", d["n_gpus"], "%.3e"%d["value"], "ms %.4f"%d["ms_per_step"], "e2e %.3e"%d["e2e"]["value"], d["e2e"]["p50_solve_ms"], d.get("solve_phases_us"))
 except Exception as e:
     print("$wl n=$n failed", e)
 PY
