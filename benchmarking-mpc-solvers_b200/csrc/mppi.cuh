@@ -709,7 +709,8 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                     dst[1] = eta;
                 }
             }
-            __threadfence_system();
+            // no system fence by every thread here: the block barrier orders all the record stores before the flag
+            // stores below, and those are st.release.sys (cumulative) — one fence per flag writer, not two in a row
             __syncthreads();
             stamp(a.trace, TR_PUBLISHED);
             if (tid < a.world) peer_signal_and_wait(pt, a, b, tid, rec_len, out + (size_t)a.g.B * (2 + H + (H + 1) * NS));
