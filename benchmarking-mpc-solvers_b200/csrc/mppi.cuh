@@ -152,10 +152,50 @@ __device__ __forceinline__ void peer_signal_and_wait(const PeerTable &pt, const 
 // meet in shared memory in a fixed order, so repeated solves are bit-identical.
 // Scratch: sscale[count], sEw[>= G][H] (callers size it [warps][H]; G <= warps), red[32].  All threads return beta / eta.
 constexpr int MERGE_BATCH = 20;
+constexpr int MERGE_SMALL = 16;  // up to this many records are merged warp-locally (no block reductions)
 __device__ __forceinline__ void block_merge(const double neg_inv_lam, const int H, const double *src, const int count,
                                             const size_t stride, double *sscale, double *sEw, double *red,
                                             double *Eout, double *beta_out, double *eta_out) {
     const int tid = threadIdx.x, nt = blockDim.x;
+    if (count <= MERGE_SMALL) {
+        // Few records (the rank records of a multi-GPU solve, the block records of a small solve): no block
+        // reductions at all.  Every warp reads the headers (lane j = record j) and derives beta, the scales and eta
+        // with shuffles — redundantly, identically; thread t owns column t and has its `count` loads in flight
+        // before the scales exist.  One L2 round trip, one barrier.
+        const int lane = tid & 31;
+        const double bj = (lane < count) ? __ldcg(src + (size_t)lane * stride) : INFINITY;
+        const double ej = (lane < count) ? __ldcg(src + (size_t)lane * stride + 1) : 0.0;
+        double e[MERGE_SMALL];
+        const bool own = tid < H;
+        if (own) {
+#pragma unroll
+            for (int j = 0; j < MERGE_SMALL; ++j)
+                e[j] = (j < count) ? __ldcg(src + (size_t)j * stride + PART_HDR + tid) : 0.0;
+        }
+        const double beta = warp_min(bj);
+        const double sc = rec_scale(neg_inv_lam, bj, beta);  // 0 for lanes >= count (bj = inf)
+        const double eta = warp_sum(sc * ej);
+        double acc = 0.0;
+#pragma unroll
+        for (int j = 0; j < MERGE_SMALL; ++j) {
+            const double sj = __shfl_sync(0xffffffffu, sc, j);
+            if (own) acc += sj * e[j];
+        }
+        if (own) Eout[tid] = acc;
+        for (int t0 = nt; t0 < H; t0 += nt) {  // blocks narrower than H: the remaining columns, loads not hoisted
+            const int t = t0 + tid;            // (the shuffles stay warp-uniform: the bound is t0, not t)
+            double a2 = 0.0;
+            for (int j = 0; j < count; ++j) {
+                const double sj = __shfl_sync(0xffffffffu, sc, j);
+                if (t < H) a2 += sj * __ldcg(src + (size_t)j * stride + PART_HDR + t);
+            }
+            if (t < H) Eout[t] = a2;
+        }
+        __syncthreads();
+        *beta_out = beta;
+        *eta_out = eta;
+        return;
+    }
     int TT = 32;
     while (TT < H && TT < nt) TT <<= 1;
     const bool by_column = TT >= H;  // every column has its own thread in each group (else: blocks narrower than H)
