@@ -523,6 +523,15 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
                 s_cap = MPPI_MAX_WARPS;
             }
         }
+        // latency regime: when the solve is at most one tile per warp in one wave of blocks, fewer warps per block
+        // spread it over more SMs, so each warp's dependent chain shares an issue port with fewer others — the
+        // smallest multiple of 4 warps (one per SM sub-partition) that still fits one wave.  Measured
+        // (profiles/r1j_warps_latency.txt): K=4096 p50 45 -> 39 µs (Pendulum), 53 -> 42 (CartPole); K=65536 48 -> 44.
+        if (g.B < h->num_sms) {
+            const int wave = h->num_sms / g.B;
+            for (int w = 4; w < W; w += 4)
+                if ((g.tiles_per_solve + w - 1) / w <= wave) { W = w; break; }
+        }
         // tuning knobs (profiling only): MPC_B200_WARPS, MPC_B200_STAGES
         if (const char *e = getenv("MPC_B200_WARPS")) { int v = atoi(e); if (v >= 1 && v <= MPPI_MAX_WARPS && v <= s_cap) W = v; }
         if (const char *e = getenv("MPC_B200_STAGES")) { int v = atoi(e); if (v >= W && v <= s_cap) S = v; }
