@@ -184,7 +184,8 @@ __device__ __forceinline__ void radix_select_block(const int n, const int want_t
 // Exchange buffer of a rank: pairs [world][n_cand] of (u64 key, u64 global index), then u64 flags [world].
 __global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const unsigned long long *__restrict__ keys,
                                                          int *__restrict__ elite_hist, int *__restrict__ sel,
-                                                         const PeerTable pt, double *__restrict__ err_word) {
+                                                         const __grid_constant__ PeerTable pt,
+                                                         double *__restrict__ err_word) {
     if (sel[SEL_DONE]) return;
     __shared__ int hist[2 * 256 + 1];  // double-buffered digit histogram + stop flag
     __shared__ int swarp[64];
