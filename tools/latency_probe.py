@@ -15,7 +15,7 @@ import tune_probe as tp  # noqa: E402
 
 for env in ("pendulum", "cartpole", "acrobot"):
     H = 100 if env == "acrobot" else 50
-    for K in (64, 4096, 65536):
+    for K in [int(v) for v in os.environ.get("PROBE_KS", "64,4096,65536").split(",")]:
         s = tp.solver(env, K, H, dtype="f32", noise="tensor")
         s.fill_noise()
         x = tp.START[env] + 0.01
