@@ -204,6 +204,34 @@ def test_mppi_stream_flavour_equals_whole_tile_flavour(env, dtype, monkeypatch):
 
 
 @pytest.mark.parametrize("env", ENVS)
+@pytest.mark.parametrize("K", [4096, 20000 + 13])
+def test_mppi_latency_regime_block_shape_does_not_change_the_solve(env, K, monkeypatch):
+    """Small solves run fewer warps per block over more SMs (capi.cu: smallest multiple of 4 warps that keeps one tile
+    per warp in one wave).  The shape decides which block and warp owns a sample, never its arithmetic: per-sample
+    costs bit-identical to the 16-warp shape, plan equal up to the merge's summation order, both on the oracle."""
+    H, lam = 50, 0.5
+    x, U, eps = _rand_case(env, K, H, seed=11)
+    S_ref, U_ref, _ = orc.mppi_solve(orc.model(env), x, U, eps, lam, 1.0, nthreads=0)
+    res, geo = {}, {}
+    for warps in (None, "16"):
+        if warps:
+            monkeypatch.setenv("MPC_B200_WARPS", warps)
+        s = _solver("MPPI", env, K, H, dtype="f32", lam=lam, sigma=1.0)
+        geo[warps] = (s.geometry["grid"], s.geometry["block"])
+        s.set_noise(eps)
+        u0, Unew, xs, cost = s.mppi_solve(x, None, U)
+        res[warps] = (s.mppi_costs()[0].copy(), Unew[0].copy())
+        s.close()
+    monkeypatch.delenv("MPC_B200_WARPS")
+    assert geo[None][1] < geo["16"][1] and geo[None][1] % 128 == 0, geo  # fewer warps, whole sub-partition groups
+    assert geo[None][0] > geo["16"][0] and geo[None][0] <= 148, geo      # over more SMs, still one wave
+    np.testing.assert_array_equal(res[None][0], res["16"][0])
+    np.testing.assert_allclose(res[None][1], res["16"][1], atol=1e-6, rtol=0)
+    tol = 6e-8 * float(np.max(np.abs(S_ref))) / lam * 4 + 1e-5
+    np.testing.assert_allclose(res[None][1], U_ref, atol=tol, rtol=tol)
+
+
+@pytest.mark.parametrize("env", ENVS)
 @pytest.mark.parametrize("dtype", ["f64", "f32"])
 def test_mppi_vs_oracle_philox_noise(env, dtype):
     """In-kernel Philox noise: materialise the same stream and hand it to the oracle."""
