@@ -1,7 +1,9 @@
 """Builds libmpcb200.so (hand-written sm_100a CUDA + the C ABI) in-tree with nvcc.  No torch involved.
 
-kernels.cu is compiled twice: float32 instantiation with FMA contraction, float64 instantiation with -fmad=false so
-that the float64 (parity) path keeps the reference's rounding sequence operation by operation."""
+kernels.cu is compiled once per (dtype, env): float32 instantiations with FMA contraction, float64 instantiations with
+-fmad=false so that the float64 (parity) path keeps the reference's rounding sequence operation by operation; the
+Acrobot float32 unit is split once more (per-stage trig splits).  The units build in parallel."""
+import glob
 import os
 import shutil
 import subprocess
@@ -11,16 +13,17 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmpcb200.so")
-HEADERS = ["kernels.cuh", "envs.cuh", "philox.cuh", "vec.cuh", "mppi.cuh", os.path.join("..", "..", "include", "mpc_b200.h")]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
 # (object name, source, extra flags)
-UNITS = [
-    ("kernels_f32.o", "kernels.cu", ["-DMPC_REAL=float", "-DMPC_SUFFIX=_f32"]),
-    ("kernels_f64.o", "kernels.cu", ["-DMPC_REAL=double", "-DMPC_SUFFIX=_f64", "-DMPC_IS_F64", "-fmad=false"]),
-    ("dispatch.o", "dispatch.cu", []),
-    ("capi.o", "capi.cu", []),
-]
+F64 = ["-DMPC_REAL=double", "-DMPC_IS_F64", "-fmad=false"]
+UNITS = [("kernels_f32_e%d.o" % e, "kernels.cu", ["-DMPC_REAL=float", "-DMPC_ENV_ONLY=%d" % e, "-DMPC_SUFFIX=_f32_e%d" % e])
+         for e in (2, 1, 0)]
+UNITS += [("kernels_f32_e2s.o", "kernels.cu", ["-DMPC_REAL=float", "-DMPC_ENV_ONLY=2", "-DMPC_TRIG_GROUP=1",
+                                               "-DMPC_SUFFIX=_f32_e2s"])]
+UNITS += [("kernels_f64_e%d.o" % e, "kernels.cu", F64 + ["-DMPC_ENV_ONLY=%d" % e, "-DMPC_SUFFIX=_f64_e%d" % e])
+          for e in (2, 1, 0)]
+UNITS += [("dispatch.o", "dispatch.cu", []), ("capi.o", "capi.cu", [])]
 
 
 def _nvcc():
@@ -34,7 +37,9 @@ def needs_build():
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, s) for s in {u[1] for u in UNITS} | set(HEADERS)] + [os.path.abspath(__file__)]
+    # every source and header of the library (globbed: a new .cuh can never be forgotten here)
+    deps = glob.glob(os.path.join(CSRC, "*.cu")) + glob.glob(os.path.join(CSRC, "*.cuh")) + \
+        glob.glob(os.path.join(HERE, "..", "include", "*.h")) + [os.path.abspath(__file__)]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -49,12 +54,15 @@ def build(force=False, verbose=False):
         obj, src, flags = u
         cmd = [nvcc] + COMMON + flags + extra + ["-c", os.path.join(CSRC, src), "-o", os.path.join(OBJ, obj)]
         r = subprocess.run(cmd, capture_output=True, text=True)
+        if verbose:
+            with open(os.path.join(OBJ, obj + ".log"), "w") as f:
+                f.write(r.stdout + r.stderr)
         return obj, r.returncode, r.stdout + r.stderr
 
-    with ThreadPoolExecutor(len(UNITS)) as ex:
+    with ThreadPoolExecutor(min(len(UNITS), os.cpu_count() or 4)) as ex:
         results = list(ex.map(compile_unit, UNITS))
     for obj, rc, out in results:
-        if verbose or rc != 0:
+        if rc != 0:
             print("==", obj, "\n" + out)
         if rc != 0:
             raise RuntimeError("nvcc failed on %s" % obj)

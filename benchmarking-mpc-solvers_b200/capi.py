@@ -27,7 +27,7 @@ SYMBOLS = [
     "mpc_create", "mpc_destroy", "mpc_last_error", "mpc_abi_version", "mpc_set_noise", "mpc_fill_noise",
     "mpc_philox_noise", "mpc_mppi_solve", "mpc_mppi_get_costs", "mpc_cem_begin", "mpc_cem_iterate", "mpc_cem_end",
     "mpc_cem_solve", "mpc_cem_get_rewards", "mpc_cem_get_elites", "mpc_cem_get_std", "mpc_simulate", "mpc_model_step",
-    "mpc_comm_create_id", "mpc_comm_init", "mpc_mppi_rollout_partial", "mpc_mppi_apply_partials", "mpc_upload_inputs", "mpc_solve_enqueue", "mpc_download_outputs",
+    "mpc_comm_create_id", "mpc_comm_init", "mpc_mppi_rollout_partial", "mpc_mppi_apply_partials", "mpc_upload_inputs", "mpc_solve_enqueue", "mpc_solve_enqueue_ex", "mpc_time_solves", "mpc_download_outputs",
     "mpc_timer_start", "mpc_timer_stop", "mpc_sync", "mpc_set_profiling", "mpc_get_rollout_ms", "mpc_launch_count", "mpc_get_geometry", "mpc_measure_fma_peak",
     "mpc_flush_l2", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace", "mpc_episode_run", "mpc_philox_model_noise", "mpc_cem_get_iterations",
 ]
@@ -102,6 +102,8 @@ def load():
     L.mpc_mppi_apply_partials.argtypes = [hp, _dp, _dp, _dp, _dp, _dp]
     L.mpc_upload_inputs.argtypes = [hp, _dp, _dp, _dp]
     L.mpc_solve_enqueue.argtypes = [hp]
+    L.mpc_solve_enqueue_ex.argtypes = [hp, C.c_int32]
+    L.mpc_time_solves.argtypes = [hp, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_float)]
     L.mpc_download_outputs.argtypes = [hp, _dp, _dp, _dp, _dp]
     L.mpc_timer_start.argtypes = [hp]
     L.mpc_timer_stop.argtypes = [hp, C.POINTER(C.c_float)]
@@ -149,7 +151,7 @@ class Solver:
         cfg.device, cfg.K, cfg.H, cfg.batch = int(device), int(K), int(H), int(batch)
         cfg.rank, cfg.world = int(rank), int(world)
         cfg.max_iter, cfg.n_elite, cfg.resample = int(max_iter), int(n_elite), int(bool(resample))
-        cfg.fast_math, cfg.lanes = int(bool(fast_math)), int(lanes)
+        cfg.fast_math, cfg.lanes = int(fast_math), int(lanes)  # fast_math: 0 / 1, Acrobot also 2, 4, 5 (mpc_b200.h)
         cfg.model_noise_std = float(model_noise_std)
         cfg.lam, cfg.sigma, cfg.epsilon, cfg.alpha = float(lam), float(sigma), float(epsilon), float(alpha)
         cfg.bounds_low, cfg.bounds_high = float(bounds[0]), float(bounds[1])
@@ -166,7 +168,7 @@ class Solver:
         self.nz = self.ns + 1
         self.is_mppi = cfg.agent == AGENT_MPPI
         self.tensor_noise = cfg.noise == NOISE_TENSOR
-        self.fast_math = bool(cfg.fast_math)
+        self.fast_math = int(cfg.fast_math)
         self.lanes = int(lanes) if lanes else (2 if (dtype == "f32" and self.is_mppi) else 1)
         h = C.c_void_p()
         rc = L.mpc_create(C.byref(cfg), C.byref(h))
@@ -435,8 +437,14 @@ class Solver:
         ua, up = _in(U_in, (self.B, self.H))
         self._ck(self.L.mpc_upload_inputs(self._h, xp, gp, up))
 
-    def solve_enqueue(self):
-        self._ck(self.L.mpc_solve_enqueue(self._h))
+    def solve_enqueue(self, want_traj=True):
+        self._ck(self.L.mpc_solve_enqueue_ex(self._h, int(bool(want_traj))))
+
+    def time_solves(self, n, want_traj=True, flush_l2=False):
+        """Device time (ms) of each of n back-to-back device-resident solves (own event pair each, one sync at the end)."""
+        ms = (C.c_float * int(n))()
+        self._ck(self.L.mpc_time_solves(self._h, int(n), int(bool(want_traj)), int(bool(flush_l2)), ms))
+        return [float(v) for v in ms]
 
     def download_outputs(self):
         u0, u0p = _out((self.B,))
@@ -454,8 +462,8 @@ class Solver:
         self._ck(self.L.mpc_timer_stop(self._h, C.byref(ms)))
         return ms.value
 
-    def set_profiling(self, on=True):
-        self._ck(self.L.mpc_set_profiling(self._h, int(bool(on))))
+    def set_profiling(self, on=True, store_costs=True):
+        self._ck(self.L.mpc_set_profiling(self._h, int(bool(on)) | (0 if store_costs else 2)))
 
     def rollout_ms(self):
         ms = C.c_float()

@@ -13,6 +13,7 @@
 #include <string.h>
 
 #include <string>
+#include <vector>
 
 using namespace mpc;
 
@@ -72,6 +73,8 @@ struct mpc_handle {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evr0 = nullptr, evr1 = nullptr;
     bool profiling = false;
+    bool store_costs = true;      // mpc_set_profiling(h, 2) turns the per-sample cost store off (tools/trace_probe.py)
+    bool prefer_stream = false;   // STREAM flavour whenever it gives more resident warps than whole tiles (see mpc_create)
     // device
     void *d_noise = nullptr;      // R [Bn][H][Kpad]          (MPPI tensor / CEM z of the current iteration)
     CUtensorMap noise_map;        // TMA descriptor over d_noise: box [H][wt] per warp tile (MPPI, TENSOR mode)
@@ -82,7 +85,7 @@ struct mpc_handle {
     double *d_rank_part = nullptr;  // [world][B][2+H]
     int *d_done = nullptr;        // [B] block arrival tickets of the solve kernel
     // peer exchange (multi-GPU, in-kernel all-gather): this rank's buffer and every rank's mapped buffer
-    double *d_xchg = nullptr;     // [world][B][2+H] doubles | u64 flags [world][B]
+    double *d_xchg = nullptr;     // [2][world][B][2+H] doubles | u64 flags [2][world][B] (double-buffered by epoch parity)
     double *peer_recs[16] = {nullptr};
     bool peer_opened[16] = {false};  // mapped through cudaIpcOpenMemHandle (to be closed)
     bool p2p_ready = false;
@@ -116,6 +119,7 @@ struct mpc_handle {
     int64_t launches = 0;
     int last_iters = 0;
     ncclComm_t comm = nullptr;
+    std::vector<cudaEvent_t> ev_pool;  // mpc_time_solves: one pair per timed solve
     std::string err;
 };
 
@@ -229,8 +233,6 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
     return 0;
 }
 
-namespace mpc {
-}
 
 static size_t off_x(const mpc_handle *) { return 0; }
 static size_t off_gz(const mpc_handle *h) { return (size_t)h->g.B * h->ns; }
@@ -250,7 +252,7 @@ static MppiArgs mppi_args(const mpc_handle *h, int want_traj) {
     a.noise_batched = 0;
     a.want_traj = want_traj;
     a.goal_zero = h->g_zero_on_device ? 1 : 0;
-    a.store_costs = getenv("MPC_B200_NOCOSTS") ? 0 : 1;  // experiment knob (tools/trace_probe.py)
+    a.store_costs = h->store_costs ? 1 : 0;
     a.p2p = (h->cfg.world > 1 && h->p2p_ready) ? 1 : 0;
     a.record_only = (h->cfg.world > 1 && !a.p2p) ? 1 : 0;
     a.epoch = h->epoch;
@@ -289,7 +291,9 @@ static CemArgs cem_args(const mpc_handle *h, int iter, int want_traj) {
     a.epsilon = h->cfg.epsilon;
     a.n_elite = h->cfg.n_elite;
     a.iter = iter;
-    a.seed = h->cfg.seed + 0x9E3779B97F4A7C15ull * (h->cfg.resample ? h->solves : 0);
+    // fresh standard normals every solve, as np.random.normal draws them (cem.py:58-59): the solve counter is folded
+    // into the Philox key unconditionally (`resample` only concerns MPPI, whose reference noise IS fixed, mppi.py:20-21)
+    a.seed = h->cfg.seed + 0x9E3779B97F4A7C15ull * h->solves;
     a.want_traj = want_traj;
     a.world = h->cfg.world;
     a.rank = h->cfg.rank;
@@ -386,6 +390,7 @@ int mpc_destroy(mpc_handle *h) {
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->evr0) cudaEventDestroy(h->evr0);
     if (h->evr1) cudaEventDestroy(h->evr1);
+    for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return MPC_OK;
@@ -467,7 +472,11 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     // rollout flavour: float32 rolls out two samples per thread (packed f32x2) unless asked otherwise
     const int lanes = (cfg->dtype == MPC_F32 && cfg->agent == MPC_AGENT_MPPI && !(cfg->model_noise_std > 0))
                           ? (cfg->lanes ? cfg->lanes : 2) : 1;  // the noisy-model flavour rolls out one sample per thread
-    g.variant = (cfg->dtype == MPC_F32 && cfg->fast_math ? 1 : 0) | (lanes == 2 ? 2 : 0);
+    // fast_math: 0 polynomial trig, 1 MUFU; Acrobot also 2, 4, 5 = per-stage splits (envs.cuh, STREAM flavour only)
+    int trig = cfg->dtype == MPC_F32 ? cfg->fast_math : 0;
+    if (trig < 0 || trig > 5 || trig == 3) trig = trig ? 1 : 0;
+    if (cfg->env != MPC_ENV_ACROBOT && trig > 1) trig = 1;
+    g.variant = trig | (lanes == 2 ? 8 : 0);
     g.wt = 32 * lanes;
     g.tiles_per_solve = g.Kpad / g.wt;
     g.total_tiles = g.B * g.tiles_per_solve;
@@ -482,45 +491,62 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         }
         int max_smem = 0;
         CUC(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
-        const size_t esz_r = cfg->dtype == MPC_F32 ? 4 : 8;
-        const size_t stage = mppi_stage_bytes(cfg->dtype, g.variant, cfg->H);
-        const long long fixed = 1024 + (long long)MPPI_MAX_WARPS * (cfg->H + g.wt) * esz_r + MPPI_MAX_WARPS * 8 * 2;
-        int s_cap = (int)(((long long)max_smem - fixed) / (long long)stage);
-        if (s_cap > 32) s_cap = 32;
+        const int nblk_cap = h->num_sms > 32 ? h->num_sms : 32;  // records the last block may have to merge
+        // does a block of W warps with a ring of S stages of `rows` time steps fit in shared memory?
+        auto fits = [&](int W, int S, int rows) {
+            return mppi_solve_smem(cfg->dtype, g.variant, cfg->H, rows, S, W, W > nblk_cap ? W : nblk_cap, 1, h->nz) <=
+                   (size_t)max_smem;
+        };
+        // whole [H][wt] tiles: the most stages that fit next to 16 warps' worth of records (more stages than warps
+        // = tiles prefetched ahead)
+        int s_cap = 0;
+        while (s_cap < 40 && fits(s_cap + 1 < 16 ? s_cap + 1 : 16, s_cap + 1, cfg->H)) ++s_cap;
         if (s_cap < 1) {
-            int rc = fail(nullptr, MPC_EINVAL, "H = %d needs %zu B of shared memory per warp tile (limit %d)", cfg->H, stage,
-                          max_smem);
+            int rc = fail(nullptr, MPC_EINVAL, "H = %d needs %zu B of shared memory per warp tile (limit %d)", cfg->H,
+                          mppi_stage_bytes(cfg->dtype, g.variant, cfg->H), max_smem);
             mpc_destroy(h);
             return rc;
         }
-        int W, S;
+        int W, S, maxW = 16;
         if (cfg->noise == MPC_NOISE_PHILOX) {
-            W = S = s_cap < MPPI_MAX_WARPS ? s_cap : MPPI_MAX_WARPS;  // one private buffer per warp, nothing to prefetch
+            W = S = s_cap < maxW ? s_cap : maxW;  // one private buffer per warp, nothing to prefetch
         } else {
+            // WIDE (MPC_B200_WIDE=1, one sample per thread only): the 32-warp whole-tile flavour at 64 registers
+            if (const char *e = getenv("MPC_B200_WIDE"))
+                if (atoi(e) != 0 && lanes == 1 && cfg->dtype == MPC_F32 && !(cfg->model_noise_std > 0)) g.variant |= 16;
+            maxW = mppi_max_warps(cfg->dtype, NOISE_TENSOR, g.variant);
+            if (maxW > 16) {  // recount the stages next to 32 warps' records
+                s_cap = 0;
+                while (s_cap < 40 && fits(s_cap + 1 < maxW ? s_cap + 1 : maxW, s_cap + 1, cfg->H)) ++s_cap;
+            }
             // measured (tools/tune_probe.py, profiles/): more resident warps beat deeper prefetch, and warp counts that
             // fill the four SM sub-partitions evenly (multiples of 4) beat the ones in between
             S = s_cap;
-            W = S < MPPI_MAX_WARPS ? S : MPPI_MAX_WARPS;
+            W = S < maxW ? S : maxW;
             if (W >= 8) W -= W % 4;
         }
-        // STREAM (mppi.cuh): when whole [H][wt] tiles leave room for fewer than 8 warps (long horizons, H > ~100), the
-        // rollout reads the noise through small per-warp chunk rings instead and the weighted sum re-reads the rows
-        // from L2: 16 resident warps for any H, at the price of touching the tensor twice (HBM has the headroom:
-        // the rollout is pipe bound).  MPC_B200_STREAM=0|1 overrides (profiling).
+        // STREAM (mppi.cuh): the rollout reads the noise through small per-warp chunk rings and the weighted sum
+        // re-reads the rows from L2, so the resident warps are bounded by registers (24 packed / 32 scalar), not by
+        // H * wt * 4 bytes per warp.  Default: whenever whole tiles leave room for fewer than 8 warps (long horizons);
+        // for Acrobot (a long dependent chain per step: the XU and FMA pipes only fill up with 6-8 warps per scheduler,
+        // profiles/r2*) whenever it gives more warps than whole tiles do.  MPC_B200_STREAM=0|1 overrides (profiling).
         g.stream_rows = g.stream_depth = 0;
         if (cfg->noise == MPC_NOISE_TENSOR) {
-            bool stream = s_cap < 8 && !(cfg->model_noise_std > 0);  // measured (tools/stream_probe.py): at 8+ whole-tile warps the two flavours tie
+            const int stream_maxW = mppi_max_warps(cfg->dtype, NOISE_STREAM, g.variant);
+            bool stream = s_cap < 8 || (h->prefer_stream && stream_maxW > W);
             if (const char *e = getenv("MPC_B200_STREAM")) stream = atoi(e) != 0;
             if (cfg->model_noise_std > 0) stream = false;  // the noisy-model flavour exists for whole tiles only
             if (stream) {
+                g.variant &= ~16;
                 g.stream_rows = 8;
                 g.stream_depth = 4;
                 if (const char *e = getenv("MPC_B200_STREAM_ROWS")) { int v = atoi(e); if (v >= 4 && v <= 64 && v % 4 == 0) g.stream_rows = v; }
                 if (const char *e = getenv("MPC_B200_STREAM_DEPTH")) { int v = atoi(e); if (v >= 2 && v <= 16) g.stream_depth = v; }
-                const size_t cstage = mppi_stage_bytes(cfg->dtype, g.variant, g.stream_rows);
-                W = MPPI_MAX_WARPS;
-                while (W > 1 && fixed + (long long)W * g.stream_depth * (long long)cstage > max_smem) --W;
-                s_cap = MPPI_MAX_WARPS;
+                maxW = stream_maxW;
+                W = maxW;
+                while (W > 1 && !fits(W, W * g.stream_depth, g.stream_rows)) --W;
+                if (W >= 8) W -= W % 4;
+                s_cap = maxW;
             }
         }
         // latency regime: when the solve is at most one tile per warp in one wave of blocks, fewer warps per block
@@ -533,7 +559,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
                 if ((g.tiles_per_solve + w - 1) / w <= wave) { W = w; break; }
         }
         // tuning knobs (profiling only): MPC_B200_WARPS, MPC_B200_STAGES
-        if (const char *e = getenv("MPC_B200_WARPS")) { int v = atoi(e); if (v >= 1 && v <= MPPI_MAX_WARPS && v <= s_cap) W = v; }
+        if (const char *e = getenv("MPC_B200_WARPS")) { int v = atoi(e); if (v >= 1 && v <= maxW && v <= s_cap) W = v; }
         if (const char *e = getenv("MPC_B200_STAGES")) { int v = atoi(e); if (v >= W && v <= s_cap) S = v; }
         if (cfg->noise == MPC_NOISE_PHILOX || S < W) S = W;
         const int tps = g.tiles_per_solve;
@@ -689,7 +715,7 @@ int mpc_philox_noise(mpc_handle *h, uint64_t draw, double *out) {
     if (rc) return rc;
     const uint32_t stream_bit = (h->cfg.agent == MPC_AGENT_CEM) ? 0x80000000u : 0u;
     uint64_t seed = h->cfg.seed;
-    if (h->cfg.agent == MPC_AGENT_CEM && h->cfg.resample) seed += 0x9E3779B97F4A7C15ull * (h->solves ? h->solves - 1 : 0);
+    if (h->cfg.agent == MPC_AGENT_CEM) seed += 0x9E3779B97F4A7C15ull * (h->solves ? h->solves - 1 : 0);  // the last solve's
     CU(h, launch_philox_materialize(h->d_scratch, g.K_local, g.k_begin, g.H, seed,
                                     ((uint32_t)draw & 0x7fffffffu) | stream_bit, h->stream));
     h->launches++;
@@ -745,6 +771,17 @@ static int stage_inputs(mpc_handle *h, const double *x, const double *g_z, const
     return MPC_OK;
 }
 
+// A peer never delivered within the bounded wait: report MPC_ENCCL once and clear the device-side error words, so that
+// the handle is usable again after the caller has dealt with it.  The resident plan U was updated from a partial
+// merge by the timed-out kernel: the caller must pass U_in on its next solve (every reference-style caller does).
+static int peer_timeout(mpc_handle *h, const char *what) {
+    cudaMemsetAsync(h->d_out + (size_t)h->g.B * h->out_stride, 0, 2 * sizeof(double), h->stream);
+    cudaStreamSynchronize(h->stream);
+    h->cem_open = false;
+    return fail(h, MPC_ENCCL, "peer exchange timed out: a rank did not deliver its %s within 4 s; the resident plan is "
+                "undefined until the next call passes U_in", what);
+}
+
 static int fetch_outputs(mpc_handle *h, int want_traj, double *u0, double *U_out, double *xs_out, double *cost_out) {
     const Geometry &g = h->g;
     const size_t per = want_traj ? h->out_stride : (size_t)(1 + g.H);
@@ -762,8 +799,7 @@ static int fetch_outputs(mpc_handle *h, int want_traj, double *u0, double *U_out
     if (h->p2p_ready)
         CU(h, cudaMemcpyAsync(h->h_out + err_at, h->d_out + err_at, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
-    if (h->p2p_ready && h->h_out[err_at] != 0.0)
-        return fail(h, MPC_ENCCL, "peer exchange timed out: a rank did not deliver its record within 4 s");
+    if (h->p2p_ready && h->h_out[err_at] != 0.0) return peer_timeout(h, "record");
     for (int b = 0; b < g.B; ++b) {
         const double *o = h->h_out + (size_t)b * h->out_stride;
         if (u0) u0[b] = o[0];
@@ -798,8 +834,7 @@ static int await_host_flag(mpc_handle *h, int want_traj, double *u0, double *U_o
     __atomic_thread_fence(__ATOMIC_ACQUIRE);
     const Geometry &g = h->g;
     const double *o = h->h_out;
-    if (h->p2p_ready && o[h->out_stride] != 0.0)
-        return fail(h, MPC_ENCCL, "peer exchange timed out: a rank did not deliver its record within 4 s");
+    if (h->p2p_ready && o[h->out_stride] != 0.0) return peer_timeout(h, "record");
     if (u0) u0[0] = o[0];
     if (U_out) memcpy(U_out, o + 1, g.H * sizeof(double));
     if (want_traj) {
@@ -891,6 +926,7 @@ int mpc_mppi_apply_partials(mpc_handle *h, const double *recs, double *u0, doubl
 int mpc_mppi_get_costs(mpc_handle *h, double *S_out) {
     if (!h || !S_out) return fail(h, MPC_EINVAL, "null argument");
     if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "not an MPPI handle");
+    if (!h->store_costs) return fail(h, MPC_ESTATE, "the per-sample cost store is switched off (mpc_set_profiling bit 1)");
     CU(h, cudaSetDevice(h->cfg.device));
     const Geometry &g = h->g;
     CU(h, cudaMemcpy2DAsync(S_out, (size_t)g.K_local * sizeof(double), h->d_S, (size_t)g.Kpad * sizeof(double),
@@ -973,8 +1009,7 @@ static int cem_finish(mpc_handle *h, int want_traj, double *u0, double *U_out, d
     }
     h->last_iters = (int)o[h->out_stride];
     if (iters_out) *iters_out = h->last_iters;
-    if (o[h->out_stride + 1] != 0.0)
-        return fail(h, MPC_ENCCL, "peer exchange timed out: a rank did not deliver its elite candidates within 4 s");
+    if (o[h->out_stride + 1] != 0.0) return peer_timeout(h, "elite candidates");
     h->cem_open = false;
     h->solves++;
     return MPC_OK;
@@ -1232,10 +1267,11 @@ static int xchg_alloc(mpc_handle *h) {
     if (h->d_xchg) return MPC_OK;
     if (h->cfg.world > 16) return fail(h, MPC_EINVAL, "peer exchange supports up to 16 ranks");
     if (h->cfg.agent == MPC_AGENT_CEM) {
-        // candidate pairs [world][n_cand] of (u64 key, u64 global index), then u64 flags [world]
+        // double-buffered by epoch parity: candidate pairs [2][world][n_cand] of (u64 key, u64 global index), then u64
+        // flags [2][world]
         CU(h, cudaSetDevice(h->cfg.device));
         const size_t n = (size_t)h->cfg.world * (h->cem_n_cand > 0 ? h->cem_n_cand : 1);
-        const size_t bytes = n * 16 + (size_t)h->cfg.world * 8;
+        const size_t bytes = 2 * (n * 16 + (size_t)h->cfg.world * 8);
         CU(h, cudaMalloc(&h->d_xchg, bytes));
         CU(h, cudaMemset(h->d_xchg, 0, bytes));
         return MPC_OK;
@@ -1245,7 +1281,7 @@ static int xchg_alloc(mpc_handle *h) {
         return fail(h, MPC_ESTATE, "peer exchange needs the whole grid resident (batch %d too large for K %d); use NCCL",
                     h->g.B, h->cfg.K);
     CU(h, cudaSetDevice(h->cfg.device));
-    const size_t slots = (size_t)h->cfg.world * h->g.B;
+    const size_t slots = 2 * (size_t)h->cfg.world * h->g.B;  // double-buffered by epoch parity (mppi.cuh)
     const size_t bytes = slots * (PART_HDR + h->g.H) * sizeof(double) + slots * sizeof(unsigned long long);
     CU(h, cudaMalloc(&h->d_xchg, bytes));
     CU(h, cudaMemset(h->d_xchg, 0, bytes));
@@ -1325,10 +1361,9 @@ int mpc_upload_inputs(mpc_handle *h, const double *x, const double *g_z, const d
     return MPC_OK;
 }
 
-int mpc_solve_enqueue(mpc_handle *h) {
-    if (!h) return MPC_EINVAL;
-    CU(h, cudaSetDevice(h->cfg.device));
-    if (h->cfg.agent == MPC_AGENT_MPPI) return mppi_enqueue(h, 1);
+extern "C" int mpc_flush_l2(mpc_handle *h);
+static int solve_enqueue(mpc_handle *h, int want_traj) {
+    if (h->cfg.agent == MPC_AGENT_MPPI) return mppi_enqueue(h, want_traj);
     if (h->cfg.noise != MPC_NOISE_PHILOX) return fail(h, MPC_ESTATE, "device-resident CEM solve needs PHILOX noise");
     CU(h, launch_cem_reset(cem_args(h, 0, 0), cem_bufs(h), h->stream));
     h->launches++;
@@ -1336,9 +1371,47 @@ int mpc_solve_enqueue(mpc_handle *h) {
         int rc = cem_enqueue_iter(h, it);
         if (rc) return rc;
     }
-    CU(h, launch_cem_finish(h->cfg.dtype, h->ep, cem_args(h, 0, 1), cem_bufs(h), h->stream));
+    CU(h, launch_cem_finish(h->cfg.dtype, h->ep, cem_args(h, 0, want_traj), cem_bufs(h), h->stream));
     h->launches++;
     h->solves++;
+    return MPC_OK;
+}
+
+int mpc_solve_enqueue(mpc_handle *h) {
+    if (!h) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    return solve_enqueue(h, 1);
+}
+
+int mpc_solve_enqueue_ex(mpc_handle *h, int32_t want_traj) {
+    if (!h) return MPC_EINVAL;
+    CU(h, cudaSetDevice(h->cfg.device));
+    return solve_enqueue(h, want_traj ? 1 : 0);
+}
+
+int mpc_time_solves(mpc_handle *h, int32_t n, int32_t want_traj, int32_t flush_l2, float *ms_each) {
+    if (!h || !ms_each || n < 1) return fail(h, MPC_EINVAL, "bad argument");
+    CU(h, cudaSetDevice(h->cfg.device));
+    while ((int)h->ev_pool.size() < 2 * n) {
+        cudaEvent_t e;
+        CU(h, cudaEventCreate(&e));
+        h->ev_pool.push_back(e);
+    }
+    // every solve between its own pair of events, nothing but the (untimed) L2 flush between two pairs, and no host
+    // synchronisation until all n are enqueued: the device queue never runs dry, so an event pair brackets the solve's
+    // own launches and not the host's launch latency
+    for (int i = 0; i < n; ++i) {
+        CU(h, cudaEventRecord(h->ev_pool[2 * i], h->stream));
+        int rc = solve_enqueue(h, want_traj ? 1 : 0);
+        if (rc) return rc;
+        CU(h, cudaEventRecord(h->ev_pool[2 * i + 1], h->stream));
+        if (flush_l2) {
+            rc = mpc_flush_l2(h);
+            if (rc) return rc;
+        }
+    }
+    CU(h, cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < n; ++i) CU(h, cudaEventElapsedTime(&ms_each[i], h->ev_pool[2 * i], h->ev_pool[2 * i + 1]));
     return MPC_OK;
 }
 
@@ -1366,7 +1439,8 @@ int mpc_timer_stop(mpc_handle *h, float *ms_out) {
 
 int mpc_set_profiling(mpc_handle *h, int32_t on) {
     if (!h) return MPC_EINVAL;
-    h->profiling = on != 0;
+    h->profiling = (on & 1) != 0;
+    h->store_costs = (on & 2) == 0;
     return MPC_OK;
 }
 

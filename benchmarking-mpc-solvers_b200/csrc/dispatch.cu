@@ -181,7 +181,9 @@ __device__ __forceinline__ void radix_select_block(const int n, const int want_t
 // store into every rank's exchange buffer, flag, bounded wait), (3) every rank selects the same global n_elite from
 // the world * n_cand candidates.  Candidate lists are ascending in global index and ranks own ascending shards, so
 // "ties by lowest position" is "ties by lowest global index" in both cases.
-// Exchange buffer of a rank: pairs [world][n_cand] of (u64 key, u64 global index), then u64 flags [world].
+// Exchange buffer of a rank, double-buffered by epoch parity (mppi.cuh: a fast rank may publish iteration e + 1 while a
+// slow one still re-reads its iteration-e slots): pairs [2][world][n_cand] of (u64 key, u64 global index), then u64
+// flags [2][world].
 __global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const unsigned long long *__restrict__ keys,
                                                          int *__restrict__ elite_hist, int *__restrict__ sel,
                                                          const __grid_constant__ PeerTable pt,
@@ -199,7 +201,10 @@ __global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const
         return;
     }
     const int n_cand = a.n_cand;
-    unsigned long long *mine = reinterpret_cast<unsigned long long *>(pt.recs[a.rank]);
+    const size_t par = (size_t)(a.epoch & 1ull);
+    const size_t half = (size_t)a.world * n_cand * 2;  // u64 words of one parity's candidate lists
+    unsigned long long *mine = reinterpret_cast<unsigned long long *>(pt.recs[a.rank]) + par * half;
+    unsigned long long *my_flags = reinterpret_cast<unsigned long long *>(pt.recs[a.rank]) + 2 * half + par * a.world;
     unsigned long long *my_slot = mine + (size_t)a.rank * n_cand * 2;
     const int n_local = min(a.n_elite, a.g.K_local);
     for (int i = n_local + tid; i < n_cand; i += blockDim.x) {  // padding: sorts below everything
@@ -215,15 +220,15 @@ __global__ void __launch_bounds__(1024) cem_select_kernel(const CemArgs a, const
     // all-gather: copy my candidate list into every peer's slot [rank]
     for (int q = 0; q < a.world; ++q) {
         if (q == a.rank) continue;
-        unsigned long long *dst = reinterpret_cast<unsigned long long *>(pt.recs[q]) + (size_t)a.rank * n_cand * 2;
+        unsigned long long *dst = reinterpret_cast<unsigned long long *>(pt.recs[q]) + par * half + (size_t)a.rank * n_cand * 2;
         for (int i = tid; i < 2 * n_cand; i += blockDim.x) dst[i] = my_slot[i];
     }
     __threadfence_system();
     __syncthreads();
     if (tid < a.world) {
         unsigned long long *theirs =
-            reinterpret_cast<unsigned long long *>(pt.recs[tid]) + (size_t)a.world * n_cand * 2 + a.rank;
-        peer_flag_exchange(theirs, mine + (size_t)a.world * n_cand * 2 + tid, a.epoch, err_word);
+            reinterpret_cast<unsigned long long *>(pt.recs[tid]) + 2 * half + par * a.world + a.rank;
+        peer_flag_exchange(theirs, my_flags + tid, a.epoch, err_word);
     }
     __syncthreads();
     const int n_all = a.world * n_cand;
@@ -244,35 +249,56 @@ __global__ void fill_kernel(float *p, size_t n, float v) {
 }
 
 
-#define DECL2(ret, name, ...) ret name##_f32(__VA_ARGS__); ret name##_f64(__VA_ARGS__);
-DECL2(size_t, mppi_solve_smem, int, int, int, int, int, int, int, int)
-DECL2(size_t, mppi_stage_bytes, int, int)
-DECL2(cudaError_t, launch_mppi_solve, int, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
-DECL2(cudaError_t, launch_mppi_rank_merge, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
-DECL2(cudaError_t, launch_transpose_noise, const double *, void *, int, int, int, cudaStream_t)
-DECL2(cudaError_t, launch_philox_fill, void *, int, int, int, int, double, uint64_t, uint32_t, cudaStream_t)
-DECL2(cudaError_t, launch_cem_rollout, int, int, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
-DECL2(cudaError_t, launch_cem_refit, int, const CemArgs &, const CemBuffers &, cudaStream_t)
-DECL2(cudaError_t, launch_cem_finish, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
-DECL2(cudaError_t, launch_simulate, const EnvParamsHost &, int, double, double, int, const double *, const double *,
-      const double *, double *, double *, cudaStream_t)
-DECL2(cudaError_t, launch_model_step, const EnvParamsHost &, int, const double *, const double *, const double *,
-      double *, double *, cudaStream_t)
-DECL2(cudaError_t, launch_fma_peak, float *, int, int, cudaStream_t)
-#undef DECL2
-#define BY_DTYPE(name, ...) ((dtype) == DT_F32 ? name##_f32(__VA_ARGS__) : name##_f64(__VA_ARGS__))
+// ---- the (dtype, env) switch over the compilations of kernels.cu (build.py: suffixes _f32_e0 ... _f64_e2, and
+// _f32_e2s for the Acrobot per-stage trig splits)
+#define DECL_E(ret, name, ...)                                                                        \
+    ret name##_f32_e0(__VA_ARGS__); ret name##_f32_e1(__VA_ARGS__); ret name##_f32_e2(__VA_ARGS__);   \
+    ret name##_f64_e0(__VA_ARGS__); ret name##_f64_e1(__VA_ARGS__); ret name##_f64_e2(__VA_ARGS__);
+#define DECL_0(ret, name, ...) ret name##_f32_e0(__VA_ARGS__); ret name##_f64_e0(__VA_ARGS__);
+DECL_0(size_t, mppi_solve_smem, int, int, int, int, int, int, int, int)
+DECL_0(size_t, mppi_stage_bytes, int, int)
+DECL_0(int, mppi_max_warps, int, int)
+DECL_E(cudaError_t, launch_mppi_solve, int, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
+cudaError_t launch_mppi_solve_f32_e2s(int, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t);
+DECL_E(cudaError_t, launch_mppi_rank_merge, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
+DECL_0(cudaError_t, launch_transpose_noise, const double *, void *, int, int, int, cudaStream_t)
+DECL_0(cudaError_t, launch_philox_fill, void *, int, int, int, int, double, uint64_t, uint32_t, cudaStream_t)
+DECL_E(cudaError_t, launch_cem_rollout, int, int, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
+DECL_0(cudaError_t, launch_cem_refit, int, const CemArgs &, const CemBuffers &, cudaStream_t)
+DECL_E(cudaError_t, launch_cem_finish, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
+DECL_E(cudaError_t, launch_simulate, const EnvParamsHost &, int, double, double, int, const double *, const double *,
+       const double *, double *, double *, cudaStream_t)
+DECL_E(cudaError_t, launch_model_step, const EnvParamsHost &, int, const double *, const double *, const double *,
+       double *, double *, cudaStream_t)
+DECL_0(cudaError_t, launch_fma_peak, float *, int, int, cudaStream_t)
+cudaError_t launch_episode_step_f64_e0(const EnvParamsHost &, const EpisodeArgs &, const EpisodeBuffers &, cudaStream_t);
+cudaError_t launch_episode_step_f64_e1(const EnvParamsHost &, const EpisodeArgs &, const EpisodeBuffers &, cudaStream_t);
+cudaError_t launch_episode_step_f64_e2(const EnvParamsHost &, const EpisodeArgs &, const EpisodeBuffers &, cudaStream_t);
+#undef DECL_E
+#undef DECL_0
+#define BY_DTYPE(name, ...) ((dtype) == DT_F32 ? name##_f32_e0(__VA_ARGS__) : name##_f64_e0(__VA_ARGS__))
+#define BY_ENV_(name, sfx, env, ...) \
+    ((env) == 0 ? name##sfx##_e0(__VA_ARGS__) : (env) == 1 ? name##sfx##_e1(__VA_ARGS__) : name##sfx##_e2(__VA_ARGS__))
+#define BY_DTYPE_ENV(name, env, ...) \
+    ((dtype) == DT_F32 ? BY_ENV_(name, _f32, env, __VA_ARGS__) : BY_ENV_(name, _f64, env, __VA_ARGS__))
 
 size_t mppi_solve_smem(int dtype, int variant, int H, int rows, int S, int W, int cap, int G, int nz) {
     return BY_DTYPE(mppi_solve_smem, variant, H, rows, S, W, cap, G, nz);
 }
 size_t mppi_stage_bytes(int dtype, int variant, int rows) { return BY_DTYPE(mppi_stage_bytes, variant, rows); }
+int mppi_max_warps(int dtype, int noise_kind, int variant) { return BY_DTYPE(mppi_max_warps, noise_kind, variant); }
 cudaError_t launch_mppi_solve(int dtype, int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
                               const MppiBuffers &b, cudaStream_t s) {
-    return BY_DTYPE(launch_mppi_solve, noise, variant, ep, a, b, s);
+    // Acrobot's per-stage trig splits (variant bits 0-2 in 2..5) exist for the STREAM flavour only, in their own unit
+    const int trig = variant & 7;
+    if (dtype == DT_F32 && ep.env == 2 && trig >= 2 && trig <= 5 && noise != NOISE_PHILOX && a.g.stream_rows > 0 &&
+        !(a.model_noise > 0.0))
+        return launch_mppi_solve_f32_e2s(noise, variant, ep, a, b, s);
+    return BY_DTYPE_ENV(launch_mppi_solve, ep.env, noise, variant, ep, a, b, s);
 }
 cudaError_t launch_mppi_rank_merge(int dtype, const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
                                    cudaStream_t s) {
-    return BY_DTYPE(launch_mppi_rank_merge, ep, a, b, s);
+    return BY_DTYPE_ENV(launch_mppi_rank_merge, ep.env, ep, a, b, s);
 }
 cudaError_t launch_transpose_noise(int dtype, const double *src, void *dst, int K_local, int Kpad, int H,
                                    cudaStream_t s) {
@@ -297,7 +323,7 @@ cudaError_t launch_philox_blocks(double *dst, int K_local, int k_begin, int n_bl
 }
 cudaError_t launch_cem_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const CemArgs &a,
                                const CemBuffers &b, cudaStream_t s) {
-    return BY_DTYPE(launch_cem_rollout, noise, variant, ep, a, b, s);
+    return BY_DTYPE_ENV(launch_cem_rollout, ep.env, noise, variant, ep, a, b, s);
 }
 cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
     PeerTable pt;
@@ -309,7 +335,7 @@ cudaError_t launch_cem_refit(int dtype, int noise, const CemArgs &a, const CemBu
     return BY_DTYPE(launch_cem_refit, noise, a, b, s);
 }
 cudaError_t launch_cem_finish(int dtype, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
-    return BY_DTYPE(launch_cem_finish, ep, a, b, s);
+    return BY_DTYPE_ENV(launch_cem_finish, ep.env, ep, a, b, s);
 }
 cudaError_t launch_cem_reset(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
     cem_reset_kernel<<<1, 128, 0, s>>>(a, b.sd, b.sel);
@@ -318,11 +344,14 @@ cudaError_t launch_cem_reset(const CemArgs &a, const CemBuffers &b, cudaStream_t
 cudaError_t launch_simulate(int dtype, const EnvParamsHost &ep, int H, double lo, double hi, int do_clip,
                             const double *x0, const double *us, const double *g_z, double *xs, double *cost,
                             cudaStream_t s) {
-    return BY_DTYPE(launch_simulate, ep, H, lo, hi, do_clip, x0, us, g_z, xs, cost, s);
+    return BY_DTYPE_ENV(launch_simulate, ep.env, ep, H, lo, hi, do_clip, x0, us, g_z, xs, cost, s);
 }
 cudaError_t launch_model_step(int dtype, const EnvParamsHost &ep, int n, const double *x, const double *u,
                               const double *g, double *cost, double *xn, cudaStream_t s) {
-    return BY_DTYPE(launch_model_step, ep, n, x, u, g, cost, xn, s);
+    return BY_DTYPE_ENV(launch_model_step, ep.env, ep, n, x, u, g, cost, xn, s);
+}
+cudaError_t launch_episode_step(const EnvParamsHost &ep, const EpisodeArgs &a, const EpisodeBuffers &b, cudaStream_t s) {
+    return BY_ENV_(launch_episode_step, _f64, ep.env, ep, a, b, s);
 }
 cudaError_t launch_fma_peak(int dtype, float *sink, int blocks, int iters, cudaStream_t s) {
     return BY_DTYPE(launch_fma_peak, sink, blocks, iters, s);

@@ -11,7 +11,7 @@
 //    cost as a sum of squares of sqrt(W_i)-scaled residuals (one FMA per residual, one per square), trig shared
 //    (cos(a - pi/2) = sin a, angle addition for theta1 + theta2), x^10 by squaring, all quotients of one `_dsdt` /
 //    one CartPole step through ONE reciprocal, angle wraps by round-to-nearest instead of loops, no slow paths.
-//    FAST selects MUFU.SIN/COS instead of the polynomial sincos.
+//    TRIG selects MUFU.SIN/COS instead of the polynomial sincos (0 = polynomial, 1 = MUFU; Acrobot: per-stage splits).
 //  * V = double (parity mode, compiled with -fmad=false): the DYNAMICS follow the reference's numpy expression tree
 //    operation by operation (same association, true divisions, cos(th1+th2-pi/2) evaluated as written, fmod-based
 //    floored remainder, repeated 2*pi wrap), because these systems are chaotic: an ulp of difference per step is
@@ -59,13 +59,13 @@ constexpr double D_PI = 3.14159265358979323846;
 // ------------------------------------------------------------------------------------------------ Pendulum
 // float layout f: 0 A = -c_sin*dt  1 B = c_u*dt  2 dt  3 max_speed  4 max_torque  5..7 sqrt(W0..W2)
 //   with c_sin = -3g/(2l), c_u = 3/(m l^2)
-template <typename V, bool FAST>
+template <typename V, int TRIG>
 struct Pendulum {
     static constexpr int NS = 2, NG = 3, CHUNK = 4;
     static constexpr int ENV = ENV_PENDULUM;
     typedef typename VT<V>::S S;
     typedef V Vec;
-    typedef Pendulum<S, false> Scalar;  // one sample per thread, accurate trig: nominal rollouts
+    typedef Pendulum<S, 0> Scalar;  // one sample per thread, accurate trig: nominal rollouts
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<V> &, S *) {}
     static __device__ __forceinline__ void leave(const EnvConst<V> &, const S *x, double *out) {
@@ -87,7 +87,7 @@ struct Pendulum {
         const V cost = vfma(d0, d0, vfma(d1, d1, d2 * d2));   // u NOT clipped in the cost   pendulum_model.py:40-50
         // dynamics: sin(th + pi) = -sin(th) = -sin(thn)                                      pendulum_model.py:28-38
         const V uc = vclip(u, -k.c[4], k.c[4]);
-        const V s = vsin_wrapped<FAST>(thn);
+        const V s = vsin_wrapped<(TRIG != 0)>(thn);
         const V om2 = vfma(k.c[0], s, vfma(k.c[1], uc, om));
         x[0] = vfma(om2, k.c[2], th);  // integrates with the UNclipped new speed
         x[1] = vclip(om2, -k.c[3], k.c[3]);
@@ -96,13 +96,13 @@ struct Pendulum {
 };
 
 // parity layout c: 0 c_sin=-3g/(2l)  1 c_u=3/(m l^2)  2 dt  3 max_speed  4 max_torque  5..7 W0..W2
-template <bool FAST>
-struct Pendulum<double, FAST> {
+template <int TRIG>
+struct Pendulum<double, TRIG> {
     static constexpr int NS = 2, NG = 3, CHUNK = 1;
     static constexpr int ENV = ENV_PENDULUM;
     typedef double S;
     typedef double Vec;
-    typedef Pendulum<double, FAST> Scalar;
+    typedef Pendulum<double, TRIG> Scalar;
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<double> &, double *) {}
     static __device__ __forceinline__ void leave(const EnvConst<double> &, const double *x, double *out) {
@@ -139,13 +139,13 @@ struct Pendulum<double, FAST> {
 //    4 A1=-2 m_p l  5 A2=3 m_p g  6 A4=4 b  7 D1=4 M  8 D2=3 m_p
 //    9 B1/l=-3 m_p  10 B2/l=6 M g/l  11 6 b/l  12 u clip (1)   13..17 sqrt(-W_i)
 //   (theta_acc's denominator 4 l M - 3 m_p l c^2 is l times x_acc's, so one reciprocal serves both)
-template <typename V, bool FAST>
+template <typename V, int TRIG>
 struct CartPole {
     static constexpr int NS = 4, NG = 5, CHUNK = 4;
     static constexpr int ENV = ENV_CARTPOLE;
     typedef typename VT<V>::S S;
     typedef V Vec;
-    typedef CartPole<S, false> Scalar;  // one sample per thread, accurate trig: nominal rollouts
+    typedef CartPole<S, 0> Scalar;  // one sample per thread, accurate trig: nominal rollouts
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<V> &, S *) {}
     static __device__ __forceinline__ void leave(const EnvConst<V> &, const S *x, double *out) {
@@ -163,7 +163,7 @@ struct CartPole {
     static __device__ __forceinline__ V step(const EnvConst<V> &k, V (&x)[NS], const V &u, const S *gs) {
         const V p = x[0], pd = x[1], th = x[2], thd = x[3];
         V s, c;
-        vsincos<FAST>(th, &s, &c);
+        vsincos<(TRIG != 0)>(th, &s, &c);
         // _transform: xc = q^2 + q^10, tc = 1 - cos(th)                      cartpole_swingup_model.py:87-93
         const V q = p * k.c[0];
         const V q2 = q * q, q4 = q2 * q2, q8 = q4 * q4;
@@ -193,13 +193,13 @@ struct CartPole {
 //    4 A1=-2 m_p l  5 A2=3 m_p g  6 A4=4 b  7 D1=4 M  8 D2=3 m_p
 //    9 B1=-3 m_p l 10 B2=6 M g   11 E1=4 l M 12 E2=3 m_p l
 //   13..17 Wc_i = -W_i  (cost = -(zd W zd), W negative diagonal)   18 x_threshold
-template <bool FAST>
-struct CartPole<double, FAST> {
+template <int TRIG>
+struct CartPole<double, TRIG> {
     static constexpr int NS = 4, NG = 5, CHUNK = 1;
     static constexpr int ENV = ENV_CARTPOLE;
     typedef double S;
     typedef double Vec;
-    typedef CartPole<double, FAST> Scalar;
+    typedef CartPole<double, TRIG> Scalar;
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<double> &, double *) {}
     static __device__ __forceinline__ void leave(const EnvConst<double> &, const double *x, double *out) {
@@ -241,13 +241,13 @@ struct CartPole<double, FAST> {
 //    3 C = m2 lc2^2 + I2   4 D = m2 l1 lc2                                                    (d2 = C + D cos th2)
 //    5 P1 = (m1 lc1 + m2 l1) g   6 P2 = m2 lc2 g   7 max_vel1  8 max_vel2   9 h/2  10 h/6  11 sqrt(W0)  12 sqrt(W4)
 //    13..15 W1..W3 (their residuals are constants of the solve)   16 h/(2 pi)  17 h/pi  18 h/(6 pi)
-template <typename V, bool FAST>
+template <typename V, int TRIG>
 struct Acrobot {
     static constexpr int NS = 4, NG = 3, CHUNK = 2;
     static constexpr int ENV = ENV_ACROBOT;
     typedef typename VT<V>::S S;
     typedef V Vec;
-    typedef Acrobot<S, false> Scalar;  // one sample per thread, accurate trig: nominal rollouts
+    typedef Acrobot<S, 0> Scalar;  // one sample per thread, accurate trig: nominal rollouts
     // step() keeps the two angles in HALF-TURNS (theta / pi): range reductions become exact additions (vec.cuh)
     static __device__ __forceinline__ void enter(const EnvConst<V> &, S *x) {
         x[0] *= 0.318309886f;
@@ -264,6 +264,24 @@ struct Acrobot {
         gs[0] = k0(k, 11) * (S)(2.0 + g[0]);  // residual_0 = -(sW0 (c1 + c12) + gs0)
         gs[1] = -k0(k, 12) * (S)g[4];
         gs[2] = k0(k, 13) * (S)(g[1] * g[1]) + k0(k, 14) * (S)(g[2] * g[2]) + k0(k, 15) * (S)(g[3] * g[3]);
+    }
+
+    // sin/cos of RK4 stage STAGE's angle (half-turns).  TRIG picks, per stage, the polynomial sincospi (FMA pipe, 1.5e-7
+    // abs) or MUFU.SIN/COS (XU pipe, ~4e-7 abs plus the rounding of the radian argument):
+    //   0 polynomial everywhere        1 MUFU everywhere (argument unreduced)
+    //   2 stage 1 polynomial, stages 2-4 MUFU       3 stages 2 and 3 (weight 2/6 each in the RK4 sum) polynomial, 1 and 4 MUFU
+    //   4 MUFU everywhere, the unwrapped stage 2-4 angles first reduced modulo one turn (exact in half-turns), which
+    //     halves the rounding of the radian argument        5 = 2 with the reduction of 4
+    template <int STAGE>
+    static __device__ __forceinline__ void stage_sincos(const V &p, V *s, V *c) {
+        constexpr bool poly = TRIG == 0 || ((TRIG == 2 || TRIG == 5) && STAGE == 1) || (TRIG == 3 && (STAGE == 2 || STAGE == 3));
+        constexpr bool reduce = (TRIG == 4 || TRIG == 5) && STAGE != 1;
+        if constexpr (poly)
+            vsincospi<false>(p, s, c);
+        else if constexpr (reduce)
+            vsincospi<true>(vwrap_halfturns(p), s, c);
+        else
+            vsincospi<true>(p, s, c);
     }
 
     // "book" _dsdt (acrobot_model.py:99-132) given sin/cos of both angles; returns the angular accelerations.
@@ -290,8 +308,8 @@ struct Acrobot {
         const V p1 = x[0], p2 = x[1], w1 = x[2], w2 = x[3];  // p = theta / pi
         const V h = k.c[0], h2 = k.c[9], h6 = k.c[10], hp = k.c[17], h2p = k.c[16], h6p = k.c[18];
         V s1, c1, s2, c2;
-        vsincospi<FAST>(p1, &s1, &c1);
-        vsincospi<FAST>(p2, &s2, &c2);
+        stage_sincos<1>(p1, &s1, &c1);
+        stage_sincos<1>(p2, &s2, &c2);
         const V c12 = vfma(c1, c2, -(s1 * s2));
         const V d0 = vfma(k.c[11], c1 + c12, V(gs[0])), d4 = vfma(k.c[12], u, V(gs[1]));
         const V cost = vfma(d0, d0, vfma(d4, d4, V(gs[2])));
@@ -299,16 +317,16 @@ struct Acrobot {
         V k1a, k1b, k2a, k2b, k3a, k3b, k4a, k4b;
         accel(k, s1, c1, s2, c2, w1, w2, u, &k1a, &k1b);
         const V k2w1 = vfma(h2, k1a, w1), k2w2 = vfma(h2, k1b, w2);
-        vsincospi<FAST>(vfma(h2p, w1, p1), &s1, &c1);
-        vsincospi<FAST>(vfma(h2p, w2, p2), &s2, &c2);
+        stage_sincos<2>(vfma(h2p, w1, p1), &s1, &c1);
+        stage_sincos<2>(vfma(h2p, w2, p2), &s2, &c2);
         accel(k, s1, c1, s2, c2, k2w1, k2w2, u, &k2a, &k2b);
         const V k3w1 = vfma(h2, k2a, w1), k3w2 = vfma(h2, k2b, w2);
-        vsincospi<FAST>(vfma(h2p, k2w1, p1), &s1, &c1);
-        vsincospi<FAST>(vfma(h2p, k2w2, p2), &s2, &c2);
+        stage_sincos<3>(vfma(h2p, k2w1, p1), &s1, &c1);
+        stage_sincos<3>(vfma(h2p, k2w2, p2), &s2, &c2);
         accel(k, s1, c1, s2, c2, k3w1, k3w2, u, &k3a, &k3b);
         const V k4w1 = vfma(h, k3a, w1), k4w2 = vfma(h, k3b, w2);
-        vsincospi<FAST>(vfma(hp, k3w1, p1), &s1, &c1);
-        vsincospi<FAST>(vfma(hp, k3w2, p2), &s2, &c2);
+        stage_sincos<4>(vfma(hp, k3w1, p1), &s1, &c1);
+        stage_sincos<4>(vfma(hp, k3w2, p2), &s2, &c2);
         accel(k, s1, c1, s2, c2, k4w1, k4w2, u, &k4a, &k4b);
         // y' = y + h/6 (k1 + 2 k2 + 2 k3 + k4): the velocity rows with the shared sum k2 + k3
         const V m1 = k2w1 + k3w1, m2 = k2w2 + k3w2, ma = k2a + k3a, mb = k2b + k3b;
@@ -326,13 +344,13 @@ struct Acrobot {
 
 // parity layout c: 0 dt  1 A  2 B  3 C  4 D  5 P1  6 P2  7 max_vel1  8 max_vel2   9..13 W0..W4
 //   14 m1 lc1^2  15 l1^2 + lc2^2  16 2 l1 lc2  17 m2  18 I1  19 I2  20 lc2^2  21 l1 lc2
-template <bool FAST>
-struct Acrobot<double, FAST> {
+template <int TRIG>
+struct Acrobot<double, TRIG> {
     static constexpr int NS = 4, NG = 5, CHUNK = 1;
     static constexpr int ENV = ENV_ACROBOT;
     typedef double S;
     typedef double Vec;
-    typedef Acrobot<double, FAST> Scalar;
+    typedef Acrobot<double, TRIG> Scalar;
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<double> &, double *) {}
     static __device__ __forceinline__ void leave(const EnvConst<double> &, const double *x, double *out) {
@@ -409,8 +427,8 @@ template <class Env>
 struct NoiseUnit {
     static __device__ __forceinline__ typename Env::S unit(int) { return (typename Env::S)1; }
 };
-template <bool FAST>
-struct NoiseUnit<Acrobot<float, FAST>> {  // angles in half-turns
+template <int TRIG>
+struct NoiseUnit<Acrobot<float, TRIG>> {  // angles in half-turns
     static __device__ __forceinline__ float unit(int i) { return i < 2 ? 0.318309886f : 1.0f; }
 };
 // One sample per thread (float or double lanes).  Philox counter = (sample, step, draw, stream).

@@ -139,6 +139,11 @@ __device__ double nominal_rollout(const EnvConst<typename Env::Vec> &ec, int H, 
     return -reward;
 }
 
+// mu + sd * z as numpy forms it (cem.py:58: np.random.normal(loc, scale) = loc + scale * z, two roundings): the float64
+// unit is compiled with -fmad=false, so the product and the sum below stay separate there; float32 contracts to one FMA
+__device__ __forceinline__ double sample_value(double sd, double z, double mu) { return mu + sd * z; }
+__device__ __forceinline__ float sample_value(float sd, float z, float mu) { return fmaf(sd, z, mu); }
+
 __device__ __forceinline__ float load_lanes(const float *p, float *) { return *p; }
 __device__ __forceinline__ double load_lanes(const double *p, double *) { return *p; }
 __device__ __forceinline__ f2 load_lanes(const float *p, f2 *) { return f2(*reinterpret_cast<const float2 *>(p)); }
@@ -225,7 +230,7 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
     if (NOISE == NOISE_TENSOR) {
         for (int t = 0; t < H; ++t) {
             const R z = zt[(size_t)t * a.z_stride + a.z_off + k];
-            const R u = vclip(vfma(ssd[t], z, smu[t]), lo, hi);
+            const R u = vclip(sample_value(ssd[t], z, smu[t]), lo, hi);
             reward += -(double)Env::step(ec, x, u, gs);
             if (a.model_noise > 0.0)
                 add_model_noise<Env>(x, a.model_noise, a.seed, PHILOX_MODEL_CEM, a.noise_draw, (uint32_t)(a.g.k_begin + k), (uint32_t)t);
@@ -239,7 +244,7 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
             for (int i = 0; i < 4; ++i) {
                 const int t = t4 + i;
                 if (t < H) {
-                    const R u = vclip(vfma(ssd[t], (R)z[i], smu[t]), lo, hi);
+                    const R u = vclip(sample_value(ssd[t], (R)z[i], smu[t]), lo, hi);
                     reward += -(double)Env::step(ec, x, u, gs);
                     if (a.model_noise > 0.0)
                         add_model_noise<Env>(x, a.model_noise, a.seed, PHILOX_MODEL_CEM, a.noise_draw, kglob, (uint32_t)t);
@@ -271,7 +276,7 @@ __global__ void __launch_bounds__(128) cem_refit_kernel(const CemArgs a, const R
             philox_normal4(a.seed, 1u, (uint32_t)a.iter, (uint32_t)(a.world > 1 ? k : a.g.k_begin + k), (uint32_t)(t >> 2), z4);
             z = (R)z4[t & 3];
         }
-        return (double)vclip(vfma(s0, z, m0), lo, hi);  // identical expression to the rollout's
+        return (double)vclip(sample_value(s0, z, m0), lo, hi);  // identical expression to the rollout's
     };
     double s = 0.0;
     for (int e = tid; e < n; e += blockDim.x) s += sample(e);
@@ -442,75 +447,91 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float *sink, int iters) {
     if (s == (R)123456789) sink[0] = (float)s;
 }
 
-// ================================================================================================ per-dtype launchers
-// This file is compiled twice (build.py): -DMPC_REAL=float -DMPC_SUFFIX=_f32 with FMA contraction on, and
-// -DMPC_REAL=double -DMPC_SUFFIX=_f64 with -fmad=false so the float64 path keeps the reference's rounding sequence.
-#ifndef MPC_REAL
-#error "compile with -DMPC_REAL=float|double -DMPC_SUFFIX=_f32|_f64"
+// ================================================================================================ per-(dtype, env) launchers
+// This file is compiled once per (dtype, env) pair (build.py) so that the big solve-kernel instantiations build in
+// parallel: -DMPC_REAL=float|double, -DMPC_ENV_ONLY=0|1|2 (Pendulum, CartPole, Acrobot), -DMPC_SUFFIX=_f32_e0 ...;
+// the float64 units are built with -fmad=false so that the parity path keeps the reference's rounding sequence.
+// The Acrobot float32 unit is split once more by trig flavour: -DMPC_TRIG_GROUP=0 (polynomial / MUFU) and 1 (the
+// per-stage splits, suffix _f32_e2s).  Env-independent launchers live in the env-0 unit of each dtype.
+#if !defined(MPC_REAL) || !defined(MPC_ENV_ONLY)
+#error "compile with -DMPC_REAL=float|double -DMPC_ENV_ONLY=0|1|2 -DMPC_SUFFIX=_f32_e0|..."
+#endif
+#ifndef MPC_TRIG_GROUP
+#define MPC_TRIG_GROUP 0
 #endif
 #define MPC_CAT_(a, b) a##b
 #define MPC_CAT(a, b) MPC_CAT_(a, b)
 #define FN(name) MPC_CAT(name, MPC_SUFFIX)
 typedef MPC_REAL R_;
 
-// variant: bit 0 = fast_math (MUFU trig), bit 1 = two samples per thread (packed f32x2).  float64 has one flavour.
-enum { VAR_FAST = 1, VAR_PACK2 = 2 };
+#if MPC_ENV_ONLY == 0
+template <typename V, int TRIG>
+using TheEnv = Pendulum<V, TRIG>;
+#elif MPC_ENV_ONLY == 1
+template <typename V, int TRIG>
+using TheEnv = CartPole<V, TRIG>;
+#else
+template <typename V, int TRIG>
+using TheEnv = Acrobot<V, TRIG>;
+#endif
+constexpr bool IS_ACROBOT = MPC_ENV_ONLY == 2;
 
-// Calls f(Env{}) with the rollout flavour selected by (env, variant): V = float / f2 x accurate / fast, or double.
+// variant: bits 0-2 = trig flavour (0 polynomial, 1 MUFU; Acrobot 2..5: per-stage splits, envs.cuh), bit 3 = two samples
+// per thread (packed f32x2), bit 4 = WIDE (32-warp whole-tile blocks, one sample per thread).  float64 has one flavour.
+enum { VAR_TRIG_MASK = 7, VAR_PACK2 = 8, VAR_WIDE = 16 };
+
+// trig flavours this unit instantiates; everything else collapses to 0 / 1
+static int unit_trig(int variant) {
+    const int t = variant & VAR_TRIG_MASK;
+    if (!IS_ACROBOT) return t ? 1 : 0;
+    return t > 5 ? 1 : t;
+}
+
+// Calls f(Env{}) with this unit's env in the rollout flavour selected by `variant` (V = float / f2 x trig), or double.
+// `splits` = the caller has kernels for the Acrobot split flavours (STREAM / TENSOR); otherwise 2..5 fall back to MUFU.
 template <class F>
-static void with_rollout_env(int env, int variant, F &&f) {
+static void with_rollout_env(int variant, bool splits, F &&f) {
     if constexpr (std::is_same<R_, double>::value) {
-        switch (env) {
-        case ENV_PENDULUM: f(Pendulum<double, false>{}); break;
-        case ENV_CARTPOLE: f(CartPole<double, false>{}); break;
-        default: f(Acrobot<double, false>{}); break;
-        }
+        f(TheEnv<double, 0>{});
     } else {
-#define MPC_ENV_CASES(E)                                      \
-    switch (variant & 3) {                                    \
-    case 0: f(E<float, false>{}); break;                      \
-    case VAR_FAST: f(E<float, true>{}); break;                \
-    case VAR_PACK2: f(E<f2, false>{}); break;                 \
-    default: f(E<f2, true>{}); break;                         \
-    }
-        switch (env) {
-        case ENV_PENDULUM: MPC_ENV_CASES(Pendulum) break;
-        case ENV_CARTPOLE: MPC_ENV_CASES(CartPole) break;
-        default: MPC_ENV_CASES(Acrobot) break;
+        int trig = unit_trig(variant);
+        if (trig > 1 && !splits) trig = 1;
+        const bool pack = (variant & VAR_PACK2) != 0;
+#if MPC_TRIG_GROUP == 0
+        if (trig == 0) {
+            if (pack) f(TheEnv<f2, 0>{}); else f(TheEnv<float, 0>{});
+        } else {
+            if (pack) f(TheEnv<f2, 1>{}); else f(TheEnv<float, 1>{});
         }
-#undef MPC_ENV_CASES
+#else
+        switch (trig) {
+        case 2: if (pack) f(TheEnv<f2, 2>{}); else f(TheEnv<float, 2>{}); break;
+        case 4: if (pack) f(TheEnv<f2, 4>{}); else f(TheEnv<float, 4>{}); break;
+        default: if (pack) f(TheEnv<f2, 5>{}); else f(TheEnv<float, 5>{}); break;
+        }
+#endif
     }
 }
 
 // One sample per thread: CEM rollouts (accurate or fast trig), nominal rollouts and single steps (always accurate).
 template <class F>
-static void with_scalar_env(int env, bool fast, F &&f) {
+static void with_scalar_env(bool fast, F &&f) {
     if constexpr (std::is_same<R_, double>::value) {
-        switch (env) {
-        case ENV_PENDULUM: f(Pendulum<double, false>{}); break;
-        case ENV_CARTPOLE: f(CartPole<double, false>{}); break;
-        default: f(Acrobot<double, false>{}); break;
-        }
+        f(TheEnv<double, 0>{});
     } else {
-#define MPC_ENV_CASES(E)            \
-    if (fast)                       \
-        f(E<float, true>{});        \
-    else                            \
-        f(E<float, false>{});
-        switch (env) {
-        case ENV_PENDULUM: MPC_ENV_CASES(Pendulum) break;
-        case ENV_CARTPOLE: MPC_ENV_CASES(CartPole) break;
-        default: MPC_ENV_CASES(Acrobot) break;
-        }
-#undef MPC_ENV_CASES
+        if (fast)
+            f(TheEnv<float, 1>{});
+        else
+            f(TheEnv<float, 0>{});
     }
 }
 
-template <class Env, int NOISE, bool NOISY = false>
+template <class Env, int NOISE, bool NOISY = false, bool WIDE = false>
 static cudaError_t mppi_solve_go(const MppiArgs &a, const EnvParamsHost &ep, const MppiBuffers &b, cudaStream_t s) {
     typedef typename Env::Vec V;
-    auto kern = mppi_solve_kernel<Env, NOISE, NOISY>;
+    auto kern = mppi_solve_kernel<Env, NOISE, NOISY, WIDE>;
     const size_t smem = a.g.smem_rollout;
+    if (a.g.warps > SolveShape<V, NOISE, WIDE>::MAXW) return cudaErrorInvalidConfiguration;
     // per instantiation AND per device (the attribute is a per-device function property): raise the dynamic
     // shared memory limit only when it grows
     static size_t smem_set[64] = {0};
@@ -535,14 +556,17 @@ static cudaError_t mppi_solve_go(const MppiArgs &a, const EnvParamsHost &ep, con
     return cudaGetLastError();
 }
 
-// shared-memory bytes of the solve kernel: ring (S stages of `rows` time steps, W warps) or the tail arena, whichever
-// is larger
+#if MPC_TRIG_GROUP == 0
+// shared-memory bytes of the solve kernel: records + ring (S stages of `rows` time steps, W warps) or records + the tail
+// arena, whichever is larger
 template <typename V>
 static size_t mppi_smem_bytes(int H, int rows, int S, int W, int cap, int G, int nz) {
     const size_t ring = RingSmem<V>::ring_total(H, rows, S, W), tail = RingSmem<V>::tail_total(H, W, cap, G, nz);
     return ring > tail ? ring : tail;
 }
+#endif
 
+#if MPC_ENV_ONLY == 0
 size_t FN(mppi_solve_smem)(int variant, int H, int rows, int S, int W, int cap, int G, int nz) {
     if constexpr (std::is_same<R_, double>::value)
         return mppi_smem_bytes<double>(H, rows, S, W, cap, G, nz);
@@ -558,33 +582,59 @@ size_t FN(mppi_stage_bytes)(int variant, int rows) {
         return (variant & VAR_PACK2) ? RingSmem<f2>::stage_bytes(rows) : RingSmem<float>::stage_bytes(rows);
 }
 
+// warps per block the (noise mode, lanes, wide) flavour is compiled for (SolveShape)
+int FN(mppi_max_warps)(int noise_kind, int variant) {
+    if constexpr (std::is_same<R_, double>::value) return 16;
+    const bool pack = (variant & VAR_PACK2) != 0, wide = (variant & VAR_WIDE) != 0;
+    if (noise_kind == NOISE_STREAM) return pack ? SolveShape<f2, NOISE_STREAM, false>::MAXW : SolveShape<float, NOISE_STREAM, false>::MAXW;
+    if (noise_kind == NOISE_TENSOR && wide && !pack) return SolveShape<float, NOISE_TENSOR, true>::MAXW;
+    return 16;
+}
+#endif
+
 cudaError_t FN(launch_mppi_solve)(int noise, int variant, const EnvParamsHost &ep, const MppiArgs &a,
                                   const MppiBuffers &b, cudaStream_t s) {
-    cudaError_t e = cudaSuccess;
+    cudaError_t e = cudaErrorInvalidValue;
+#if MPC_TRIG_GROUP == 0
     if (a.model_noise > 0.0) {  // noisy model: one sample per thread (capi.cu forces lanes = 1, whole tiles)
-        with_scalar_env(ep.env, (variant & VAR_FAST) != 0, [&](auto env) {
+        with_scalar_env(unit_trig(variant) != 0, [&](auto env) {
             typedef decltype(env) E;
             e = (noise == NOISE_PHILOX) ? mppi_solve_go<E, NOISE_PHILOX, true>(a, ep, b, s)
                                         : mppi_solve_go<E, NOISE_TENSOR, true>(a, ep, b, s);
         });
         return e;
     }
-    with_rollout_env(ep.env, variant, [&](auto env) {
+#endif
+    const bool stream = noise != NOISE_PHILOX && a.g.stream_rows > 0;
+    with_rollout_env(variant, stream, [&](auto env) {
         typedef decltype(env) E;
-        if (noise == NOISE_PHILOX)
+        typedef typename E::Vec V;
+        if (noise == NOISE_PHILOX) {
+#if MPC_TRIG_GROUP == 0
             e = mppi_solve_go<E, NOISE_PHILOX>(a, ep, b, s);
-        else if (a.g.stream_rows > 0)
+#endif
+        } else if (stream) {
             e = mppi_solve_go<E, NOISE_STREAM>(a, ep, b, s);
-        else
+        } else {
+#if MPC_TRIG_GROUP == 0
+            if constexpr (std::is_same<V, float>::value) {
+                if (variant & VAR_WIDE) {
+                    e = mppi_solve_go<E, NOISE_TENSOR, false, true>(a, ep, b, s);
+                    return;
+                }
+            }
             e = mppi_solve_go<E, NOISE_TENSOR>(a, ep, b, s);
+#endif
+        }
     });
     return e;
 }
 
+#if MPC_TRIG_GROUP == 0
 cudaError_t FN(launch_mppi_rank_merge)(const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
                                        cudaStream_t s) {
     cudaError_t e = cudaSuccess;
-    with_scalar_env(ep.env, false, [&](auto env) {
+    with_scalar_env(false, [&](auto env) {
         typedef decltype(env) E;
         auto kern = mppi_rank_merge_kernel<E>;
         const int H = a.g.H, nw = 256 / 32;
@@ -603,6 +653,7 @@ cudaError_t FN(launch_mppi_rank_merge)(const EnvParamsHost &ep, const MppiArgs &
     return e;
 }
 
+#if MPC_ENV_ONLY == 0
 cudaError_t FN(launch_transpose_noise)(const double *src, void *dst, int K_local, int Kpad, int H, cudaStream_t s) {
     dim3 grid((Kpad + 31) / 32, (H + 31) / 32), block(32, 8);
     transpose_noise_kernel<R_><<<grid, block, 0, s>>>(src, (R_ *)dst, K_local, Kpad, H);
@@ -615,11 +666,25 @@ cudaError_t FN(launch_philox_fill)(void *dst, int K_local, int k_begin, int Kpad
     return cudaGetLastError();
 }
 
+cudaError_t FN(launch_cem_refit)(int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
+    if (noise == NOISE_TENSOR)
+        cem_refit_kernel<R_, NOISE_TENSOR><<<a.g.H, 128, 0, s>>>(a, (const R_ *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
+    else
+        cem_refit_kernel<R_, NOISE_PHILOX><<<a.g.H, 128, 0, s>>>(a, (const R_ *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
+    return cudaGetLastError();
+}
+
+cudaError_t FN(launch_fma_peak)(float *sink, int blocks, int iters, cudaStream_t s) {
+    fma_peak_kernel<R_><<<blocks, 256, 0, s>>>(sink, iters);
+    return cudaGetLastError();
+}
+#endif
+
 cudaError_t FN(launch_cem_rollout)(int noise, int variant, const EnvParamsHost &ep, const CemArgs &a,
                                    const CemBuffers &b, cudaStream_t s) {
     const size_t smem = 2 * (size_t)a.g.H * sizeof(double);
     const int grid = a.g.Kpad / TILE;
-    with_scalar_env(ep.env, (variant & VAR_FAST) != 0, [&](auto env) {
+    with_scalar_env(unit_trig(variant) != 0, [&](auto env) {
         typedef decltype(env) E;
         typedef typename E::Vec V;
         if (noise == NOISE_TENSOR)
@@ -632,17 +697,9 @@ cudaError_t FN(launch_cem_rollout)(int noise, int variant, const EnvParamsHost &
     return cudaGetLastError();
 }
 
-cudaError_t FN(launch_cem_refit)(int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
-    if (noise == NOISE_TENSOR)
-        cem_refit_kernel<R_, NOISE_TENSOR><<<a.g.H, 128, 0, s>>>(a, (const R_ *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
-    else
-        cem_refit_kernel<R_, NOISE_PHILOX><<<a.g.H, 128, 0, s>>>(a, (const R_ *)b.z, b.elite_idx, b.mu, b.sd, b.sel);
-    return cudaGetLastError();
-}
-
 cudaError_t FN(launch_cem_finish)(const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
     const size_t smem = (size_t)a.g.H * (2 + a.g.ns) * sizeof(double);
-    with_scalar_env(ep.env, false, [&](auto env) {
+    with_scalar_env(false, [&](auto env) {
         typedef decltype(env) E;
         cem_finish_kernel<E><<<1, 128, smem, s>>>(a, make_env<typename E::Vec>(ep), b.x0, b.g_z, b.mu, b.sel, b.out);
     });
@@ -652,7 +709,7 @@ cudaError_t FN(launch_cem_finish)(const EnvParamsHost &ep, const CemArgs &a, con
 cudaError_t FN(launch_simulate)(const EnvParamsHost &ep, int H, double lo, double hi, int do_clip, const double *x0,
                                 const double *us, const double *g_z, double *xs, double *cost, cudaStream_t s) {
     const size_t smem = (size_t)H * 6 * sizeof(double);
-    with_scalar_env(ep.env, false, [&](auto env) {
+    with_scalar_env(false, [&](auto env) {
         typedef decltype(env) E;
         simulate_kernel<E><<<1, 64, smem, s>>>(make_env<typename E::Vec>(ep), H, lo, hi, do_clip, x0, us, g_z, xs, cost);
     });
@@ -661,7 +718,7 @@ cudaError_t FN(launch_simulate)(const EnvParamsHost &ep, int H, double lo, doubl
 
 cudaError_t FN(launch_model_step)(const EnvParamsHost &ep, int n, const double *x, const double *u, const double *g,
                                   double *cost, double *xn, cudaStream_t s) {
-    with_scalar_env(ep.env, false, [&](auto env) {
+    with_scalar_env(false, [&](auto env) {
         typedef decltype(env) E;
         model_step_kernel<E><<<(n + 127) / 128, 128, 0, s>>>(make_env<typename E::Vec>(ep), n, x, u, g, cost, xn);
     });
@@ -669,20 +726,12 @@ cudaError_t FN(launch_model_step)(const EnvParamsHost &ep, int n, const double *
 }
 
 #ifdef MPC_IS_F64
-cudaError_t launch_episode_step(const EnvParamsHost &ep, const EpisodeArgs &a, const EpisodeBuffers &b, cudaStream_t s) {
-    EnvConst<double> ec = make_env<double>(ep);
-    switch (ep.env) {
-    case ENV_PENDULUM: episode_step_kernel<Pendulum<double, false>><<<1, 128, 0, s>>>(ec, a, b); break;
-    case ENV_CARTPOLE: episode_step_kernel<CartPole<double, false>><<<1, 128, 0, s>>>(ec, a, b); break;
-    default: episode_step_kernel<Acrobot<double, false>><<<1, 128, 0, s>>>(ec, a, b); break;
-    }
+// always the float64 plant, whatever the rollout dtype
+cudaError_t FN(launch_episode_step)(const EnvParamsHost &ep, const EpisodeArgs &a, const EpisodeBuffers &b, cudaStream_t s) {
+    episode_step_kernel<TheEnv<double, 0>><<<1, 128, 0, s>>>(make_env<double>(ep), a, b);
     return cudaGetLastError();
 }
 #endif
-
-cudaError_t FN(launch_fma_peak)(float *sink, int blocks, int iters, cudaStream_t s) {
-    fma_peak_kernel<R_><<<blocks, 256, 0, s>>>(sink, iters);
-    return cudaGetLastError();
-}
+#endif  // MPC_TRIG_GROUP == 0
 
 }  // namespace mpc

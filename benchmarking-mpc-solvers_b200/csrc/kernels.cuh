@@ -38,7 +38,8 @@ struct Geometry {
     int fin_group;        // mode B: solves finalised together (one thread per nominal rollout)
     int stream_rows;      // 0 = whole [H][wt] tiles in the ring; > 0 = STREAM: time steps per chunk of a warp's private ring
     int stream_depth;     // STREAM: chunk stages per warp
-    int variant;          // rollout flavour: bit 0 fast_math (MUFU trig), bit 1 two samples per thread (f32x2)
+    int variant;          // rollout flavour: bits 0-2 trig (0 polynomial, 1 MUFU, Acrobot 2/4/5 per-stage splits), bit 3 two
+                          // samples per thread (f32x2), bit 4 WIDE (32-warp whole-tile blocks, one sample per thread)
     int ns;
     size_t smem_rollout;  // dynamic shared memory of the solve kernel
 };
@@ -171,7 +172,8 @@ cudaError_t launch_episode_step(const EnvParamsHost &ep, const EpisodeArgs &a, c
 // rows = time steps per ring stage (H, or the STREAM chunk); S = ring stages of the block (STREAM: W * depth)
 size_t mppi_solve_smem(int dtype, int variant, int H, int rows, int S, int W, int cap, int G, int nz);
 size_t mppi_stage_bytes(int dtype, int variant, int rows);
-constexpr int MPPI_MAX_WARPS = 16;   // == MAX_WARPS in mppi.cuh
+// warps per block the solve kernel of (dtype, noise kind, variant) is compiled for (SolveShape in mppi.cuh)
+int mppi_max_warps(int dtype, int noise_kind, int variant);
 constexpr int MPPI_MAX_H = 256;      // 32 * MAX_ROWS
 
 }  // namespace mpc

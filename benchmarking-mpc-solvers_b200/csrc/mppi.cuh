@@ -19,8 +19,22 @@
 
 namespace mpc {
 
-constexpr int MAX_WARPS = 16;   // warps per rollout block
+constexpr int MAX_WARPS = 32;   // warps per rollout block (the register budget of a flavour may allow fewer: SolveShape)
 constexpr int MAX_ROWS = 8;     // time-step rows per lane in the weighted sum: H <= 32 * MAX_ROWS
+
+// Warps per block (= per SM: the grid is persistent, one block per SM) a flavour is compiled for.  The bound is the
+// register file: 64 K registers / (32 W) per thread.  Whole-tile flavours are limited by shared memory to
+// 227 KB / (H * WT * sizeof(R)) resident tiles anyway (17 at H = 50, packed lanes), so they keep 16 warps x 128
+// registers; the STREAM flavour's per-warp chunk ring is a few KB, so it runs 24 (packed lanes, 80 registers) or 32
+// (one sample per thread, 64 registers) warps: the rollout is a dependent chain per sample and the XU / FMA pipes only
+// fill up with 6-8 chains per scheduler.  WIDE asks for the 32-warp whole-tile flavour (one sample per thread, short
+// horizons).
+template <typename V, int NOISE, bool WIDE>
+struct SolveShape {
+    static constexpr bool is_f64 = sizeof(typename VT<V>::S) == 8;
+    static constexpr int PACK = VT<V>::N;
+    static constexpr int MAXW = is_f64 ? 16 : (NOISE == NOISE_STREAM ? (PACK == 2 ? 24 : 32) : (WIDE ? 32 : 16));
+};
 
 template <typename V>
 struct WarpTile {
@@ -31,23 +45,26 @@ struct WarpTile {
     static constexpr int NCHUNK = WT / CE;               // chunks per row (power of two)
 };
 
-// Shared-memory layout of the tile loop.  The tail reuses the arena from offset 0 after a block barrier.
+// Shared-memory layout.  Offset 0: the warps' running records [W][2 + H] doubles (beta, eta, E[H]) — they live through
+// the whole kernel (the weighted sum of every tile folds into them).  Then the tile loop's ring | U | weights |
+// mbarriers | gen; the tail reuses everything behind the records after a block barrier.
 template <typename V>
 struct RingSmem {
     typedef typename VT<V>::S R;
     static constexpr int WT = WarpTile<V>::WT;
     static __host__ __device__ size_t a16(size_t b) { return (b + 15) / 16 * 16; }
+    static __host__ __device__ size_t a128(size_t b) { return (b + 127) / 128 * 128; }
+    static __host__ __device__ size_t off_ring(int H, int W) { return a128((size_t)W * (PART_HDR + H) * sizeof(double)); }
     // a stage holds `rows` time steps of one warp tile: rows = H (whole tiles), or the STREAM chunk
     static __host__ __device__ size_t stage_bytes(int rows) { return (size_t)rows * WT * sizeof(R); }
-    static __host__ __device__ size_t off_sU(int rows, int S) { return S * stage_bytes(rows); }
-    static __host__ __device__ size_t off_sw(int H, int rows, int S, int W) { return off_sU(rows, S) + a16((size_t)W * H * sizeof(R)); }
+    static __host__ __device__ size_t off_sU(int H, int rows, int S, int W) { return off_ring(H, W) + S * stage_bytes(rows); }
+    static __host__ __device__ size_t off_sw(int H, int rows, int S, int W) { return off_sU(H, rows, S, W) + a16((size_t)W * H * sizeof(R)); }
     static __host__ __device__ size_t off_bar(int H, int rows, int S, int W) { return off_sw(H, rows, S, W) + (size_t)W * WT * sizeof(R); }
     static __host__ __device__ size_t off_gen(int H, int rows, int S, int W) { return off_bar(H, rows, S, W) + (size_t)S * 8; }
     static __host__ __device__ size_t ring_total(int H, int rows, int S, int W) { return off_gen(H, rows, S, W) + (size_t)S * 4 + 16; }
-    // tail arena (doubles): warp records [W][2+H] | scale[cap] | clipped plans [G][H] | goals [G][H*NZ] | warp sums
-    // [W][H] ; G = solves finalised together
+    // tail arena behind the records (doubles): scale[cap] | clipped plans [G][H] | goals [G][H*NZ] | group sums [W][H] | E
     static __host__ __device__ size_t tail_total(int H, int W, int cap, int G, int nz) {
-        return ((size_t)W * (PART_HDR + H) + cap + (size_t)G * H + (size_t)G * H * nz + (size_t)W * H + H + 64) * sizeof(double);
+        return off_ring(H, W) + ((size_t)cap + (size_t)G * H + (size_t)G * H * nz + (size_t)W * H + H + 64) * sizeof(double);
     }
 };
 
@@ -122,9 +139,16 @@ __device__ __forceinline__ double rec_scale(double neg_inv_lam, double bj, doubl
 // Multi-GPU (peer.cuh): every rank's solve kernel writes its (beta, eta, E[H]) record straight into the exchange
 // buffer of EVERY rank over NVLink, raises that rank's flag for (writer, solve) to the solve's epoch and waits for the
 // flags of all writers in its own buffer: an all-gather inside the kernel, no NCCL launch and no second kernel.
-// Buffer layout: records [world][B][2+H] doubles, then u64 flags [world][B].
-__device__ __forceinline__ unsigned long long *peer_flags(double *recs, int world, int B, int rec_len) {
-    return reinterpret_cast<unsigned long long *>(recs + (size_t)world * B * rec_len);
+// The buffer is DOUBLE-BUFFERED by epoch parity: records [2][world][B][2+H] doubles, then u64 flags [2][world][B].
+// A rank that has seen every flag of epoch e may already be publishing epoch e + 1 while a slower peer still reads its
+// epoch-e slots; they are different slots.  It cannot publish e + 2 before every peer has published e + 1, and a peer
+// publishes e + 1 only after its epoch-e kernel has finished: two parities are race-free with no acknowledgement.
+__device__ __forceinline__ double *peer_recs(double *buf, int world, int B, int rec_len, unsigned long long epoch) {
+    return buf + (size_t)(epoch & 1ull) * world * B * rec_len;
+}
+__device__ __forceinline__ unsigned long long *peer_flags(double *buf, int world, int B, int rec_len,
+                                                          unsigned long long epoch) {
+    return reinterpret_cast<unsigned long long *>(buf + (size_t)2 * world * B * rec_len) + (size_t)(epoch & 1ull) * world * B;
 }
 // phase stamps of the finalising block (nanoseconds of %globaltimer), read back with mpc_get_trace
 enum { TR_START = 0, TR_TILES_DONE = 1, TR_TICKET = 2, TR_MERGED = 3, TR_PUBLISHED = 4, TR_PEERS_IN = 5,
@@ -137,8 +161,38 @@ __device__ __forceinline__ void stamp(unsigned long long *trace, int i) {
 __device__ __forceinline__ void peer_signal_and_wait(const PeerTable &pt, const MppiArgs &a, int b, int q, int rec_len,
                                                      double *err_word) {
     const size_t slot = (size_t)a.rank * a.g.B + b;
-    peer_flag_exchange(peer_flags(pt.recs[q], a.world, a.g.B, rec_len) + slot,
-                       peer_flags(pt.recs[a.rank], a.world, a.g.B, rec_len) + (size_t)q * a.g.B + b, a.epoch, err_word);
+    peer_flag_exchange(peer_flags(pt.recs[q], a.world, a.g.B, rec_len, a.epoch) + slot,
+                       peer_flags(pt.recs[a.rank], a.world, a.g.B, rec_len, a.epoch) + (size_t)q * a.g.B + b, a.epoch,
+                       err_word);
+}
+
+// ---- float32 flavour of the per-tile softmin bookkeeping.  The reference minimum beta only has to be NEAR the minimum
+// (softmin weights are invariant under a shift of beta: it cancels between w_k and eta), so the warp minimum is taken on
+// the float32-rounded costs with five 32-bit shuffles instead of ten 64-bit ones, and the weights exp(-(S - beta)/lam)
+// are one MUFU.EX2 of the float32-rounded exponent (the difference S - beta itself is formed in float64): relative
+// weight error <= 2^-22 + 6e-8 |exponent|, far inside the float32 flavour's cost error divided by lam.
+__device__ __forceinline__ float warp_min_f32(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_sum_f32(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+// arrival ticket of a block: acq_rel at gpu scope.  With the block barrier before it, this publishes every thread's
+// record stores (release, cumulative over the barrier) and, for the last arriver, makes the other blocks' records
+// visible to the loads that follow the next barrier (acquire) — no separate __threadfence by all threads.
+__device__ __forceinline__ int ticket_acq_rel(int *p) {
+    int old;
+    asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;" : "=r"(old) : "l"(p) : "memory");
+    return old;
 }
 
 // ------------------------------------------------------------------------------------------------ record merging
@@ -321,8 +375,8 @@ __device__ __forceinline__ void block_apply(const MppiArgs &a, const EnvConst<ty
 // ================================================================================================ the solve kernel
 // Geometry (capi.cu): tiles are WARP tiles.  mode A (solves_per_block == 0): blocks_per_solve blocks share one solve,
 // block blk works on solve blk / blocks_per_solve.  mode B: a block owns solves_per_block whole solves.
-template <class Env, int NOISE, bool NOISY = false>  // NOISY: the model has sensor noise (one sample per thread only)
-__global__ void __launch_bounds__(MAX_WARPS * 32, 1)
+template <class Env, int NOISE, bool NOISY = false, bool WIDE = false>  // NOISY: the model has sensor noise (one sample per thread only)
+__global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MAXW * 32, 1)
     mppi_solve_kernel(const MppiArgs a, const EnvConst<typename Env::Vec> ec,
                       const __grid_constant__ CUtensorMap noise_map, const typename Env::S *__restrict__ noise_g,
                       const double *__restrict__ x0g, const double *__restrict__ g_z, double *__restrict__ Ug,
@@ -333,30 +387,35 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
     typedef typename Env::S R;
     constexpr int NS = Env::NS, NZ = Env::NS + 1, NG = Env::NG, PACK = VT<V>::N, CH = Env::CHUNK;
     constexpr int WT = WarpTile<V>::WT;
+    constexpr bool F32 = sizeof(R) == 4;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr bool STREAM = NOISE == NOISE_STREAM;
     // the descriptor's address in parameter space (the lambdas below capture the pointer, not the 128-byte object)
     const CUtensorMap *const map_ptr = &noise_map;
     const int H = a.g.H, W = blockDim.x >> 5, S = a.g.stages, tps = a.g.tiles_per_solve;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const bool mode_b = a.g.solves_per_block != 0;
     // STREAM: the ring is W private rings of `depth` chunk stages of `rows` time steps (S = W * depth)
     const int rows = STREAM ? a.g.stream_rows : H, depth = STREAM ? a.g.stream_depth : 0;
     const int nchunk = STREAM ? (H + rows - 1) / rows : 1;
     const size_t stage_elems = (size_t)rows * WT;
-    R *stages = reinterpret_cast<R *>(smem_raw);
-    R *sU = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sU(rows, S)) + (size_t)w * H;
+    const int rec_len = PART_HDR + H;
+    double *wrec_all = reinterpret_cast<double *>(smem_raw);  // [W][rec_len]: the warps' running (beta, eta, E[H])
+    double *wrec = wrec_all + (size_t)w * rec_len;
+    R *stages = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_ring(H, W));
+    // the plan in the rollout dtype: one copy per block (mode A: one solve per block) or per warp (mode B)
+    R *sU = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sU(H, rows, S, W)) + (mode_b ? (size_t)w * H : 0);
     R *sw = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sw(H, rows, S, W)) + (size_t)w * WT;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + RingSmem<V>::off_bar(H, rows, S, W));
     // gen[st] = tile whose load the stage's mbarrier currently tracks.  An mbarrier carries one bit of phase: a
     // warp that ran a whole ring turn ahead of a slow warp would see the parity of an OLDER completed phase and
     // read a stale tile.  Waiting for gen[st] == j first makes the wait exact for any interleaving of the warps.
     volatile int *gen = reinterpret_cast<volatile int *>(smem_raw + RingSmem<V>::off_gen(H, rows, S, W));
-    const int rec_len = PART_HDR + H;
 
     if (blockIdx.x == 0) stamp(a.trace, TR_START);
     // ---- this block's tile range ----------------------------------------------------------------------------
     int tile0, tile1, b_lo, b_hi;
-    if (a.g.solves_per_block == 0) {
+    if (!mode_b) {
         b_lo = b_hi = blockIdx.x / a.g.blocks_per_solve;
         const int part_idx = blockIdx.x - b_lo * a.g.blocks_per_solve;
         tile0 = b_lo * tps + part_idx * a.g.chunk;
@@ -368,12 +427,10 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
         tile1 = (b_hi + 1) * tps;
     }
 
-    // one TMA tensor copy (box [H][WT] of the [Bn][H][Kpad] noise tensor) of tile j into its stage, by lane 0;
-    // callers have passed a __syncwarp after the warp's last read of the stage
-    auto issue = [&](int j) {
+    // one TMA tensor copy (box [H][WT] of the [Bn][H][Kpad] noise tensor) of tile j = (solve b, warp tile kt) into
+    // stage st, by lane 0; callers have passed a __syncwarp after the warp's last read of the stage
+    auto issue = [&](int j, int st, int b, int kt) {
         if (lane == 0) {
-            const int st = (j - tile0) % S;
-            const int b = j / tps, kt = j - b * tps;
             mbar_expect_tx(&bars[st], (uint32_t)(stage_elems * sizeof(R)));
             __threadfence_block();
             gen[st] = j;
@@ -416,27 +473,35 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             }
             fence_mbar_init();
         }
-        __syncthreads();
+    }
+    // mode A: the block's single solve's plan, once per block (every warp reads the same copy)
+    if (!mode_b)
+        for (int t = tid; t < H; t += blockDim.x) sU[t] = (R)Ug[(size_t)b_lo * H + t];
+    for (int t = lane; t < rec_len; t += 32) wrec[t] = 0.0;  // E starts at zero (the first tile's scale_old is 0, 0 * NaN is not)
+    __syncthreads();
+    if (NOISE == NOISE_TENSOR || STREAM) {
         if (STREAM) {
             for (int i = 0; i < depth; ++i) issue_chunk();
         } else {
-            for (int i = w; i < S && tile0 + i < tile1; i += W) issue(tile0 + i);
+            for (int i = w; i < S && tile0 + i < tile1; i += W) {
+                const int j = tile0 + i, b = j / tps;
+                issue(j, i, b, j - b * tps);
+            }
         }
     }
 
-    // ---- per-warp running softmin state of the current solve; E rows lane, lane + 32, ... in registers ---------
+    // ---- per-warp running softmin state of the current solve; E rows lane, lane + 32, ... live in wrec (shared) ----
     int cur = b_lo;
     double beta_run = INFINITY, eta_run = 0.0;
-    double E[MAX_ROWS];
-#pragma unroll
-    for (int i = 0; i < MAX_ROWS; ++i) E[i] = 0.0;
     R gs[NG];
     R xinit[NS];
     const V pert = V((R)a.pert);
 
     auto load_solve = [&](int b) {
-        __syncwarp();
-        for (int t = lane; t < H; t += 32) sU[t] = (R)Ug[(size_t)b * H + t];
+        if (mode_b) {
+            __syncwarp();
+            for (int t = lane; t < H; t += 32) sU[t] = (R)Ug[(size_t)b * H + t];
+        }
         Env::prep_goal(ec, g_z + (size_t)b * H * NZ, gs);  // goal row 0 (model.py:34,38)
 #pragma unroll
         for (int i = 0; i < NS; ++i) xinit[i] = (R)x0g[(size_t)b * NS + i];
@@ -446,28 +511,31 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
     // mode B only: the warp's record of solve `cur` goes to global memory (slot = warp)
     auto flush_global = [&]() {
         double *rec = part + ((size_t)cur * a.g.max_parts + w) * rec_len;
+        __syncwarp();
         if (lane == 0) {
             rec[0] = beta_run;
             rec[1] = eta_run;
         }
-#pragma unroll
-        for (int i = 0; i < MAX_ROWS; ++i)
-            if (lane + 32 * i < H) rec[PART_HDR + lane + 32 * i] = E[i];
+        for (int t = lane; t < H; t += 32) {
+            rec[PART_HDR + t] = wrec[PART_HDR + t];
+            wrec[PART_HDR + t] = 0.0;
+        }
         beta_run = INFINITY;
         eta_run = 0.0;
-#pragma unroll
-        for (int i = 0; i < MAX_ROWS; ++i) E[i] = 0.0;
+        __syncwarp();
     };
     load_solve(cur);
 
+    // tile j = tile0 + w + i W of the block goes to ring stage st = (j - tile0) % S on turn q = (j - tile0) / S of the
+    // ring; (solve b, warp tile kt) = (j / tps, j % tps).  All four are carried incrementally: no division per tile.
+    int st = w, q = 0;  // w < W <= S
+    int b = (tile0 + w) / tps, kt = (tile0 + w) - b * tps;
     for (int j = tile0 + w; j < tile1; j += W) {
-        const int b = j / tps, kt = j - b * tps;
         while (cur < b) {  // mode B: every warp leaves a record (possibly empty) for every solve of the block
             flush_global();
             ++cur;
             if (cur == b) load_solve(cur);
         }
-        const int jr = j - tile0, st = jr % S;
         R *tile = (NOISE == NOISE_TENSOR) ? stages + st * stage_elems : stages + w * stage_elems;  // STREAM: unused
         const int kl = kt * WT + lane * PACK;  // first local sample index of this lane
         V x[NS];
@@ -496,7 +564,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             while (gen[st] != j) {
             }
             __threadfence_block();
-            mbar_wait(&bars[st], (uint32_t)((jr / S) & 1));
+            mbar_wait(&bars[st], (uint32_t)(q & 1));
             int t = 0;
             for (; t + CH <= H; t += CH) {
                 V acc = V((R)0);
@@ -579,13 +647,9 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                 }
             }
         }
-        double Smin = INFINITY;
 #pragma unroll
-        for (int l = 0; l < PACK; ++l) {
-            const bool valid = kl + l < a.g.K_local;
-            if (!valid) Sk[l] = INFINITY;
-            Smin = fmin(Smin, Sk[l]);
-        }
+        for (int l = 0; l < PACK; ++l)
+            if (!(kl + l < a.g.K_local)) Sk[l] = INFINITY;
         if (!a.store_costs) {
         } else if (PACK == 2) {
             if (kl + 1 < a.g.K_local)
@@ -596,21 +660,42 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             S_out[(size_t)b * a.g.Kpad + kl] = Sk[0];
         }
         // ---- online softmin: rescale the running sums to the new minimum (mppi.py:59-62) ------------------------
-        const double beta_new = fmin(beta_run, warp_min(Smin));
-        const double scale_old = (eta_run == 0.0) ? 0.0 : exp(a.neg_inv_lam * (beta_run - beta_new));
-        double wsum = 0.0;
+        double beta_new, scale_old;
         R wl[PACK];
+        if constexpr (F32) {
+            float m = INFINITY;
 #pragma unroll
-        for (int l = 0; l < PACK; ++l) {
-            const double wk = (Sk[l] == INFINITY) ? 0.0 : exp(a.neg_inv_lam * (Sk[l] - beta_new));
-            wl[l] = (R)wk;
-            wsum += wk;
+            for (int l = 0; l < PACK; ++l) m = fminf(m, (float)Sk[l]);
+            beta_new = fmin(beta_run, (double)warp_min_f32(m));
+            // warp-uniform: the running minimum only moves O(log tiles) times per warp
+            scale_old = (eta_run == 0.0) ? 0.0 : (beta_new == beta_run ? 1.0 : exp(a.neg_inv_lam * (beta_run - beta_new)));
+            float wsum = 0.f;
+#pragma unroll
+            for (int l = 0; l < PACK; ++l) {
+                const float ex = (float)(a.neg_inv_lam * (Sk[l] - beta_new)) * 1.44269504f;  // -inf for padding samples
+                wl[l] = (Sk[l] == INFINITY) ? 0.f : ex2_approx(ex);
+                wsum += wl[l];
+            }
+            eta_run = eta_run * scale_old + (double)warp_sum_f32(wsum);
+        } else {
+            double Smin = INFINITY;
+#pragma unroll
+            for (int l = 0; l < PACK; ++l) Smin = fmin(Smin, Sk[l]);
+            beta_new = fmin(beta_run, warp_min(Smin));
+            scale_old = (eta_run == 0.0) ? 0.0 : exp(a.neg_inv_lam * (beta_run - beta_new));
+            double wsum = 0.0;
+#pragma unroll
+            for (int l = 0; l < PACK; ++l) {
+                const double wk = (Sk[l] == INFINITY) ? 0.0 : exp(a.neg_inv_lam * (Sk[l] - beta_new));
+                wl[l] = (R)wk;
+                wsum += wk;
+            }
+            eta_run = eta_run * scale_old + warp_sum(wsum);
         }
+        beta_run = beta_new;
         if constexpr (STREAM) {
             // ---- E[t] += sum_k w_k eps[k][t] with the rows re-read from the noise tensor (L2; the tile went through
             // this SM a tile time ago), weights in registers, 32 rows per reduce-scatter --------------------------
-            eta_run = eta_run * scale_old + warp_sum(wsum);
-            beta_run = beta_new;
             V wv;
             if constexpr (PACK == 2)
                 wv = V(wl[0], wl[PACK - 1]);
@@ -626,44 +711,66 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                         const int t = 32 * i + r;
                         v[r] = (t < H) ? lane_dot(wv, load_lanes(grow + (size_t)t * a.g.Kpad, (V *)nullptr)) : (R)0;
                     }
-                    E[i] = E[i] * scale_old + (double)warp_rows_reduce_scatter(v, lane);
+                    const double acc = (double)warp_rows_reduce_scatter(v, lane);
+                    const int r = lane + 32 * i;
+                    if (r < H) wrec[PART_HDR + r] = wrec[PART_HDR + r] * scale_old + acc;
                 }
             }
         } else {
-        if constexpr (PACK == 2)
-            *reinterpret_cast<float2 *>(sw + lane * 2) = make_float2(wl[0], wl[PACK - 1]);
-        else
-            sw[lane] = wl[0];
-        eta_run = eta_run * scale_old + warp_sum(wsum);
-        beta_run = beta_new;
-        __syncwarp();  // weights (and the Philox tile) visible to the whole warp
-        // ---- E[t] += sum_k w_k eps[k][t], lane owns rows t = lane + 32 i -----------------------------------------
+            if constexpr (PACK == 2)
+                *reinterpret_cast<float2 *>(sw + lane * 2) = make_float2(wl[0], wl[PACK - 1]);
+            else
+                sw[lane] = wl[0];
+            __syncwarp();  // weights (and the Philox tile) visible to the whole warp
+            // ---- E[t] += sum_k w_k eps[k][t], lane owns rows t = lane + 32 i -------------------------------------
 #pragma unroll
-        for (int i = 0; i < MAX_ROWS; ++i) {
-            if (32 * i < H) {
-                const int r = lane + 32 * i;
-                double acc = 0.0;
-                if (r < H) acc = dot_row_rot(tile + (size_t)r * WT, sw, lane, (V *)nullptr);
-                E[i] = E[i] * scale_old + acc;
+            for (int i = 0; i < MAX_ROWS; ++i) {
+                if (32 * i < H) {
+                    const int r = lane + 32 * i;
+                    if (r < H) {
+                        const double acc = dot_row_rot(tile + (size_t)r * WT, sw, lane, (V *)nullptr);
+                        wrec[PART_HDR + r] = wrec[PART_HDR + r] * scale_old + acc;
+                    }
+                }
             }
         }
-        }
-        // ---- re-arm the stage with the tile S places ahead -------------------------------------------------------
+        // ---- re-arm the stage with the tile S places ahead, then step (st, q, b, kt) to this warp's next tile -------
         if (NOISE == NOISE_TENSOR) {
             __syncwarp();
-            if (j + S < tile1) issue(j + S);
+            if (j + S < tile1) {
+                int b2 = b, kt2 = kt + S;
+                while (kt2 >= tps) {
+                    kt2 -= tps;
+                    ++b2;
+                }
+                issue(j + S, st, b2, kt2);
+            }
+        }
+        st += W;
+        if (st >= S) {
+            st -= S;
+            ++q;
+        }
+        kt += W;
+        while (kt >= tps) {
+            kt -= tps;
+            ++b;
         }
     }
-    if (a.g.solves_per_block != 0) {
+    if (mode_b) {
         while (cur <= b_hi) {
             flush_global();
             ++cur;
         }
     }
 
-    // ---- tail: every stage is free after this barrier; the arena is reused from offset 0 -------------------------
+    // ---- tail: every stage is free after this barrier; the arena behind the records is reused ----------------------
     __shared__ unsigned long long s_wexit[MAX_WARPS];  // profiling: when each warp left the tile loop
     if (a.trace && lane == 0) s_wexit[w] = global_ns();
+    if (!mode_b && lane == 0) {
+        wrec[0] = beta_run;
+        wrec[1] = eta_run;
+    }
     __syncthreads();
     unsigned long long t_wmin = ~0ull, t_wmax = 0ull;
     if (a.trace && tid == 0)
@@ -673,52 +780,37 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
         }
     __shared__ double red[32];
     __shared__ int s_last;
-    double *arena = reinterpret_cast<double *>(smem_raw);
+    double *arena = reinterpret_cast<double *>(smem_raw + RingSmem<V>::off_ring(H, W));
     const int nt = blockDim.x;
-    if (a.g.solves_per_block == 0) {
-        // mode A: warp records -> shared memory -> one block record in global memory -> ticket -> last block merges
+    if (!mode_b) {
+        // mode A: warp records (shared) -> one block record in global memory -> ticket -> last block merges
         const int b = b_lo, nb = a.g.blocks_per_solve, part_idx = blockIdx.x - b * nb;
-        double *wrec = arena;                      // [W][rec_len]
-        double *sscale = wrec + (size_t)W * rec_len;  // [max(W, nb)]
+        double *sscale = arena;                    // [max(W, nb)]
         double *sUc = sscale + max(W, nb);         // [H]
         double *sG = sUc + H;                      // [H * NZ]
         double *sEw = sG + (size_t)H * NZ;         // [W][H]
         double *Eout = sEw + (size_t)W * H;        // [H]
-        {
-            double *rec = wrec + (size_t)w * rec_len;
-            if (lane == 0) {
-                rec[0] = beta_run;
-                rec[1] = eta_run;
-            }
-#pragma unroll
-            for (int i = 0; i < MAX_ROWS; ++i)
-                if (lane + 32 * i < H) rec[PART_HDR + lane + 32 * i] = E[i];
-        }
-        const unsigned long long t_a0 = a.trace ? global_ns() : 0ull;
-        __syncthreads();
         const unsigned long long t_a = a.trace ? global_ns() : 0ull;
         double bb = INFINITY;
-        for (int i = 0; i < W; ++i) bb = fmin(bb, wrec[(size_t)i * rec_len]);
-        if (tid < W) sscale[tid] = rec_scale(a.neg_inv_lam, wrec[(size_t)tid * rec_len], bb);
+        for (int i = 0; i < W; ++i) bb = fmin(bb, wrec_all[(size_t)i * rec_len]);
+        if (tid < W) sscale[tid] = rec_scale(a.neg_inv_lam, wrec_all[(size_t)tid * rec_len], bb);
         __syncthreads();
         double *grec = part + ((size_t)b * a.g.max_parts + part_idx) * rec_len;
         for (int t = tid; t < H; t += nt) {
             double e = 0.0;
-            for (int i = 0; i < W; ++i) e += sscale[i] * wrec[(size_t)i * rec_len + PART_HDR + t];
+            for (int i = 0; i < W; ++i) e += sscale[i] * wrec_all[(size_t)i * rec_len + PART_HDR + t];
             grec[PART_HDR + t] = e;
         }
         if (tid == 0) {
             double eta = 0.0;
-            for (int i = 0; i < W; ++i) eta += sscale[i] * wrec[(size_t)i * rec_len + 1];
+            for (int i = 0; i < W; ++i) eta += sscale[i] * wrec_all[(size_t)i * rec_len + 1];
             grec[0] = bb;
             grec[1] = eta;
         }
         const unsigned long long t_b = a.trace ? global_ns() : 0ull;
-        __threadfence();
-        __syncthreads();
-        const unsigned long long t_c = a.trace ? global_ns() : 0ull;
+        __syncthreads();  // every thread's record stores precede thread 0's release below
         if (tid == 0) {
-            const int ticket = atomicAdd(&done_count[b], 1);
+            const int ticket = ticket_acq_rel(&done_count[b]);
             s_last = (ticket == nb - 1);
             if (s_last) done_count[b] = 0;  // self-cleaning: ready for the next solve on this stream
         }
@@ -728,21 +820,19 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             a.trace[TR_TILES_DONE] = t_wmax;  // the last warp's exit from the tile loop
             a.trace[9] = t_a;
             a.trace[10] = t_b;
-            a.trace[11] = t_c;
             a.trace[12] = t_wmin;
             a.trace[13] = t_wmax;
-            a.trace[14] = t_a0;
         }
         stamp(a.trace, TR_TICKET);
-        __threadfence();
         double beta, eta;
         block_merge(a.neg_inv_lam, H, part + (size_t)b * a.g.max_parts * rec_len, nb, (size_t)rec_len, sscale, sEw, red,
                     Eout, &beta, &eta);
         stamp(a.trace, TR_MERGED);
+        double *const err_word = out + (size_t)a.g.B * (2 + H + (H + 1) * NS);
         if (a.p2p) {
             // in-kernel all-gather of the rank records over NVLink, then the same merge over `world` records
-            for (int q = 0; q < a.world; ++q) {
-                double *dst = pt.recs[q] + ((size_t)a.rank * a.g.B + b) * rec_len;
+            for (int qr = 0; qr < a.world; ++qr) {
+                double *dst = peer_recs(pt.recs[qr], a.world, a.g.B, rec_len, a.epoch) + ((size_t)a.rank * a.g.B + b) * rec_len;
                 for (int t = tid; t < H; t += nt) dst[PART_HDR + t] = Eout[t];
                 if (tid == 0) {
                     dst[0] = beta;
@@ -753,11 +843,11 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             // stores below, and those are st.release.sys (cumulative) — one fence per flag writer, not two in a row
             __syncthreads();
             stamp(a.trace, TR_PUBLISHED);
-            if (tid < a.world) peer_signal_and_wait(pt, a, b, tid, rec_len, out + (size_t)a.g.B * (2 + H + (H + 1) * NS));
+            if (tid < a.world) peer_signal_and_wait(pt, a, b, tid, rec_len, err_word);
             __syncthreads();
             stamp(a.trace, TR_PEERS_IN);
-            block_merge(a.neg_inv_lam, H, pt.recs[a.rank] + (size_t)b * rec_len, a.world, (size_t)a.g.B * rec_len, sscale,
-                        sEw, red, Eout, &beta, &eta);
+            block_merge(a.neg_inv_lam, H, peer_recs(pt.recs[a.rank], a.world, a.g.B, rec_len, a.epoch) + (size_t)b * rec_len,
+                        a.world, (size_t)a.g.B * rec_len, sscale, sEw, red, Eout, &beta, &eta);
             stamp(a.trace, TR_MERGED2);
             block_apply<Env>(a, ec, b, true, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG);
         } else {
@@ -770,7 +860,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
             const double *o = out + (size_t)b * stride;
             const int n_copy = a.want_traj ? (int)stride : 1 + H;
             for (int i = tid; i < n_copy; i += nt) a.host_out[i] = o[i];
-            if (tid < 2) a.host_out[stride + tid] = out[(size_t)a.g.B * stride + tid];  // peer-wait error words
+            if (tid < 2) a.host_out[stride + tid] = err_word[tid];  // peer-wait error words
             __threadfence_system();
             __syncthreads();
             if (tid == 0) st_release_sys(a.host_flag, a.host_epoch);
@@ -782,6 +872,7 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
         const int nsolve = b_hi - b_lo + 1, G = a.g.fin_group;
         double *sUc = arena;                       // [G][H]
         double *sG = sUc + (size_t)G * H;          // [G][H * NZ], or one zero row
+        double *const err_word = out + (size_t)a.g.B * (2 + H + (H + 1) * NS);
         for (int g0 = 0; g0 < nsolve; g0 += G) {
             const int ng = min(G, nsolve - g0);
             for (int sl = w; sl < ng; sl += W) {
@@ -808,8 +899,9 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                     for (int t0 = 0; t0 < H; t0 += 32) {
                         const int t = t0 + lane;
                         const double e = merged_row(t);
-                        for (int q = 0; q < nq; ++q) {
-                            double *dst = (a.p2p ? pt.recs[q] : rank_part) + ((size_t)a.rank * a.g.B + b) * rec_len;
+                        for (int qr = 0; qr < nq; ++qr) {
+                            double *dst = (a.p2p ? peer_recs(pt.recs[qr], a.world, a.g.B, rec_len, a.epoch) : rank_part) +
+                                          ((size_t)a.rank * a.g.B + b) * rec_len;
                             if (t < H) dst[PART_HDR + t] = e;
                             if (t0 == 0 && lane == 0) {
                                 dst[0] = beta;
@@ -821,10 +913,9 @@ __global__ void __launch_bounds__(MAX_WARPS * 32, 1)
                 if (a.p2p) {
                     __threadfence_system();
                     __syncwarp();
-                    if (lane < a.world)
-                        peer_signal_and_wait(pt, a, b, lane, rec_len, out + (size_t)a.g.B * (2 + H + (H + 1) * NS));
+                    if (lane < a.world) peer_signal_and_wait(pt, a, b, lane, rec_len, err_word);
                     __syncwarp();
-                    recs = pt.recs[a.rank] + (size_t)b * rec_len;
+                    recs = peer_recs(pt.recs[a.rank], a.world, a.g.B, rec_len, a.epoch) + (size_t)b * rec_len;
                     rstride = (size_t)a.g.B * rec_len;
                     cnt = a.world;
                     bj = (lane < cnt) ? __ldcg(recs + (size_t)lane * rstride) : INFINITY;

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define MPC_B200_ABI_VERSION 3
+#define MPC_B200_ABI_VERSION 4
 
 typedef struct mpc_handle mpc_handle;
 
@@ -74,8 +74,11 @@ typedef struct {
     int32_t n_elite;      /* CEM (cem.py:24) */
     int32_t resample;     /* PHILOX only: 0 = one fixed noise draw reused by every solve (the reference's MPPI
                              semantics, mppi.py:20-21), 1 = fresh draw per solve */
-    int32_t fast_math;    /* MPC_F32 only: 1 = MUFU.SIN/COS in the dynamics (abs err ~4e-7 per call) instead of the
-                             1-ulp polynomial sincos; 0 = accurate (default) */
+    int32_t fast_math;    /* MPC_F32 only: 0 = polynomial sincos (1.5e-7 abs, default); 1 = MUFU.SIN/COS in the dynamics
+                             (~4e-7 abs per call plus the rounding of the radian argument).  Acrobot (four RK4 stages per
+                             step, models/acrobot_model.py:270-282) also takes per-stage splits between the FMA pipe
+                             (polynomial) and the XU pipe (MUFU): 2 = stage 1 polynomial, stages 2-4 MUFU; 4 = MUFU with
+                             the unwrapped stage angles first reduced modulo one turn; 5 = 2 with the reduction of 4 */
     int32_t lanes;        /* MPC_F32 MPPI only: samples rolled out per thread, 1 or 2 (2 = packed f32x2 arithmetic,
                              FFMA2); 0 = library default.  Results do not depend on it. */
     double lam;           /* MPPI temperature (mppi.py:17) */
@@ -230,6 +233,13 @@ int mpc_mppi_apply_partials(mpc_handle *h, const double *recs, double *u0, doubl
  * stream without any host<->device copy or synchronisation. */
 int mpc_upload_inputs(mpc_handle *h, const double *x, const double *g_z, const double *U_in);
 int mpc_solve_enqueue(mpc_handle *h);
+/* The same with the nominal rollout of the clipped plan (Agent.simulate_trajectory, agent.py:97-108: the logging
+ * branch of predict_action, not part of _calc_action) switched on or off. */
+int mpc_solve_enqueue_ex(mpc_handle *h, int32_t want_traj);
+/* n device-resident solves, each between its own pair of CUDA events on the handle's stream, optionally with an
+ * (untimed) L2 flush after each, all enqueued before the single synchronisation at the end: ms_each [n] = the device
+ * time of every solve's own launches, free of host launch latency. */
+int mpc_time_solves(mpc_handle *h, int32_t n, int32_t want_traj, int32_t flush_l2, float *ms_each);
 int mpc_download_outputs(mpc_handle *h, double *u0, double *U_out, double *xs_out, double *cost_out);
 /* CUDA events on the handle's stream (torch.cuda.Event only sees torch's current stream). */
 int mpc_timer_start(mpc_handle *h);
@@ -237,7 +247,8 @@ int mpc_timer_stop(mpc_handle *h, float *ms_out); /* records, synchronises, retu
 int mpc_sync(mpc_handle *h);
 /* With profiling on, every MPPI solve brackets its rollout kernel (the dominant kernel) with its own event pair;
  * mpc_get_rollout_ms returns that kernel's device time for the last solve. */
-int mpc_set_profiling(mpc_handle *h, int32_t on);
+int mpc_set_profiling(mpc_handle *h, int32_t on); /* bit 0: profiling; bit 1: do NOT store the per-sample costs (then
+                                                     mpc_mppi_get_costs fails with MPC_ESTATE instead of returning stale data) */
 int mpc_get_rollout_ms(mpc_handle *h, float *ms_out);
 /* With profiling on, the block that finalises an MPPI solve stamps its phases with %globaltimer (ns): out[0] kernel
  * start, [1] all tiles done, [2] last block's ticket, [3] block records merged, [4] rank record published to the
