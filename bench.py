@@ -3,14 +3,15 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME] [--no-extra]
 
-One "step" = one MPPI solve (rollout of K samples x H steps + softmin update + nominal rollout).
+One "step" = one MPPI solve = MPPI._calc_action (mppi.py:54-75): rollout of K samples x H steps + softmin update.
 Headline workload (BASELINE.json configs[2], largest K): MPPI on Acrobot, H = 100, K = 2^20, lam = 0.5, std = 1,
 float32 rollout arithmetic with float64 accumulation, resident noise tensor (the reference's delta_u semantics,
 mppi.py:20-21).  Only the sample dimension shards: each of N ranks rolls out K/N samples and one all-gather of
 (min cost, sum w, sum w*eps[H]) per rank combines them => "strong" scaling (total work fixed).
 
-value   device-timed (CUDA events on the solver's stream, inputs resident in HBM, max over ranks)
-e2e     same metric through the host-buffer C-ABI call (H2D of state+plan, D2H of action+plan+trajectory inside)
+value   device-timed (CUDA events on the solver's stream, inputs resident in HBM, max over ranks): MPPI._calc_action
+e2e     same metric through the host-buffer C-ABI call (H2D of state+plan, D2H of action+plan+trajectory inside):
+        what Agent.predict_action costs, logging rollout of the clipped plan included
 The reference arm (--impl reference) times the CPU oracle port of the reference algorithm on all host threads
 (the reference itself is pure Python and is not on the GPU box).
 """
@@ -39,11 +40,13 @@ WORKLOADS = {
     "mppi_pendulum_h50_k65536": ("MPPI", "pendulum", 65536, 50, dict(lam=0.5, sigma=1.0)),
 }
 DEFAULT_WORKLOAD = "mppi_acrobot_h100_k1m"
-# float32 rollout flavour quoted per env: (fast_math, lanes).  fast_math = MUFU.SIN/COS instead of the polynomial sincos;
-# it is used where EVERY per-sample cost stays within the north_star's rel 1e-5 of the float64 oracle
-# (tests/test_gpu_parity.py::test_mppi_mufu_trig_flavour_meets_the_float32_bar, tools/variant_probe.py): Pendulum and
-# Acrobot.  CartPole keeps the polynomial (its chaotic tail leaves no margin).  lanes: Acrobot's MUFU flavour is XU-pipe
-# bound and runs best one sample per thread with 16 warps; the others use packed f32x2.
+# float32 rollout flavour quoted per env: (fast_math, lanes).  fast_math = MUFU.SIN/COS instead of the polynomial sincos.
+# Measured per-sample cost error against the float64 oracle on identical noise (profiles/r2b_parity_probe.jsonl,
+# tests/test_gpu_parity.py holds both flavours to the SAME bars): Pendulum max 4.5e-7 (either flavour); Acrobot H <= 50
+# max 2.5e-7; Acrobot H = 100 p99 2.2e-7 polynomial / 4.3e-7 MUFU with a chaotic tail beyond 1e-5 in BOTH (5 / 7 of
+# 65536 samples); CartPole p95 5e-6, ~1 % of the samples beyond 1e-5 in any float32 evaluation (MUFU doubles that, so
+# CartPole keeps the polynomial).  Every bench line carries a `parity` block measured in the same run.
+# lanes: Acrobot's MUFU flavour is XU-pipe bound and runs best one sample per thread; the others use packed f32x2.
 FLAVOUR = {"acrobot": (1, 1), "pendulum": (1, 2), "cartpole": (0, 2)}
 L2_BYTES = 126 << 20
 
@@ -172,15 +175,30 @@ class Dist:
 
 
 # --------------------------------------------------------------------------------------------- our arm
-def make_solver(capi, orc_params, agent, env, K, H, prm, dist, dtype="f32", noise="tensor", **kw):
+class One:
+    """A single-GPU view of this rank (extras that do not shard)."""
+    world, rank = 1, 0
+
+    def __init__(self, dist):
+        self.local_rank = dist.local_rank
+
+    def barrier(self):
+        pass
+
+    def max(self, v):
+        return v
+
+
+def make_solver(capi, agent, env, K, H, prm, dist, dtype="f32", noise="tensor", **kw):
     from mpc_b200.models import ENV_NAMES, env_spec
     if dtype == "f32" and agent == "MPPI":
-        if kw.get("fast_math", -1) < 0:
+        if kw.get("fast_math", -1) is None or kw.get("fast_math", -1) < 0:
             kw["fast_math"] = FLAVOUR[env][0]
         if not kw.get("lanes"):
             kw["lanes"] = FLAVOUR[env][1]
     else:
-        kw["fast_math"] = max(0, kw.get("fast_math", 0))
+        kw["fast_math"] = max(0, kw.get("fast_math", 0) or 0)
+        kw.pop("lanes", None)
     model = ENV_NAMES[env]()
     env_id, env_params = env_spec(model)
     lo, hi = float(model.bounds_low[0]), float(model.bounds_high[0])
@@ -188,7 +206,7 @@ def make_solver(capi, orc_params, agent, env, K, H, prm, dist, dtype="f32", nois
                     device=dist.local_rank, rank=dist.rank if dist.world > 1 else 0, world=dist.world, seed=0,
                     **prm, **kw)
     if dist.world > 1:
-        if agent == "MPPI" and os.environ.get("MPC_B200_EXCHANGE", "p2p") == "p2p":
+        if os.environ.get("MPC_B200_EXCHANGE", "p2p") == "p2p" or agent == "CEM":
             from mpc_b200 import parallel
             parallel.connect_p2p(s)  # in-kernel all-gather over NVLink peer memory: one launch per solve
         else:
@@ -198,32 +216,29 @@ def make_solver(capi, orc_params, agent, env, K, H, prm, dist, dtype="f32", nois
     return s
 
 
-def time_device(s, steps, warmup, dist, flush):
-    """Per-step CUDA-event timing on the solver's stream; L2 flushed (untimed) between steps when asked."""
-    for _ in range(warmup):
-        s.solve_enqueue()
-        if flush:
-            s.flush_l2()
+def time_device(s, steps, warmup, dist, flush, want_traj=False):
+    """K solves enqueued back to back on the solver's stream between a barrier + synchronise on both sides.  With the
+    untimed L2 flush between solves every solve has its own pair of CUDA events (the flush sits between two pairs) and
+    the step time is the sum of the K intervals; without a flush ONE pair brackets all K solves.  Max over ranks.
+    For MPPI the solve is ONE kernel, so time / K is also the solve kernel's duration (launch gap included).
+    Returns (total ms, launches in the timed region, wall seconds of the bracket)."""
+    s.time_solves(max(1, warmup), want_traj=want_traj, flush_l2=flush)
     s.sync()
     dist.barrier()
-    total_ms, roll_ms = 0.0, 0.0
     l0 = s.launch_count
-    n_flush = 0
     t_wall = time.perf_counter()
-    for _ in range(steps):
+    if flush:
+        total = sum(s.time_solves(steps, want_traj=want_traj, flush_l2=True))
+    else:
         s.timer_start()
-        s.solve_enqueue()
-        total_ms += s.timer_stop()
-        if s.is_mppi:
-            roll_ms += s.rollout_ms()
-        if flush:
-            s.flush_l2()
-            n_flush += 1
+        for _ in range(steps):
+            s.solve_enqueue(want_traj=want_traj)
+        total = s.timer_stop()
     s.sync()
     dist.barrier()
     wall = time.perf_counter() - t_wall
-    launches = s.launch_count - l0 - n_flush
-    return dist.max(total_ms), dist.max(roll_ms), launches, wall
+    launches = s.launch_count - l0 - (steps if flush else 0)
+    return dist.max(total), launches, wall
 
 
 def time_e2e(s, x, U, steps, warmup, dist):
@@ -243,16 +258,144 @@ def time_e2e(s, x, U, steps, warmup, dist):
     return dist.max(total), lat
 
 
+_PAR_CACHE = {}
+
+
+def parity_block(capi, dist, env, H, prm, K_par=65536, **flavour):
+    """Per-sample costs and plan of the benchmarked float32 flavour against the library's own float64 flavour (pinned
+    to the reference at 1e-12 by tests/, so `oracle/` stays out of this process) on the same Philox noise stream, for a
+    K_par-sample solve from the bench's start state.  Outside every timed region; one GPU (this rank)."""
+    one = One(dist)
+    x = np.array(START[env]) + 0.01
+    U = np.zeros(H)
+    key = (env, H, prm["lam"], prm["sigma"], K_par)
+    if key not in _PAR_CACHE:
+        r = make_solver(capi, "MPPI", env, K_par, H, prm, one, dtype="f64")
+        u0, Un, _, _ = r.mppi_solve(x, None, U, want_traj=False)
+        _PAR_CACHE[key] = (r.mppi_costs()[0].copy(), Un[0].copy(), float(u0[0]))
+        r.close()
+    S64, U64, u064 = _PAR_CACHE[key]
+    s = make_solver(capi, "MPPI", env, K_par, H, prm, one, dtype="f32", **flavour)
+    u0, Un, _, _ = s.mppi_solve(x, None, U, want_traj=False)
+    S = s.mppi_costs()[0]
+    s.close()
+    rel = np.abs(S - S64) / np.abs(S64)
+    return {"against": "float64 flavour of this library (pinned to the reference at rel 1e-12), same Philox noise, "
+                       "K=%d subset" % K_par,
+            "cost_rel_p50": float(np.quantile(rel, .5)), "cost_rel_p99": float(np.quantile(rel, .99)),
+            "cost_rel_max": float(rel.max()), "n_cost_rel_over_1e-5": int((rel > 1e-5).sum()),
+            "plan_abs_max": float(np.abs(Un[0] - U64).max()),
+            "u0_rel": float(abs(u0[0] - u064) / max(abs(u064), 1e-300))}
+
+
+def plan_hash(U):
+    b = np.ascontiguousarray(U, dtype=np.float64).view(np.uint64).ravel()
+    h = np.uint64(1469598103934665603)
+    with np.errstate(over="ignore"):
+        for v in b:
+            h = (h ^ v) * np.uint64(1099511628211)
+    return int(h >> np.uint64(12))  # 52 bits: exact in a float64 all-reduce
+
+
+def run_mppi_workload(capi, dist, name, steps, warmup, dtype="f32", noise="tensor", lanes=0, fast_math=-1,
+                      with_parity=True, with_e2e=True, fma_peak=None, peaks=None, peaks_src=""):
+    """One K-sharded MPPI workload on all ranks: device-timed value, e2e, both rooflines, phase stamps, parity of the
+    flavour against the float64 flavour, and at N > 1 the sharded plan against the same solve on one GPU."""
+    agent, env, K, H, prm = WORKLOADS[name]
+    s = make_solver(capi, agent, env, K, H, prm, dist, dtype=dtype, noise=noise, lanes=lanes, fast_math=fast_math)
+    s.set_profiling(True)
+    esz = 4 if dtype == "f32" else 8
+    shard_bytes = s.K_local * H * esz
+    flush = noise == "philox" or shard_bytes < 2 * L2_BYTES
+    x = np.array(START[env]) + 0.01
+    U = np.zeros(H)
+    s.upload_inputs(x, None, U)
+    clocks = ClockSampler(dist.local_rank)
+    clocks.start()
+    total_ms, launches, wall = time_device(s, steps, warmup, dist, flush)
+    clk = clocks.stop()
+    steps_total = float(K) * H * steps
+    value = steps_total / (total_ms * 1e-3)
+    try:
+        tr = s.trace()
+        trace_us = {k: round(v / 1e3, 1) for k, v in tr.items() if v is not None and k != "start"}
+    except Exception:
+        trace_us = None
+    out = {"value": value, "ms_per_step": total_ms / steps, "clocks": clk, "gpu_launches": launches,
+           "wall_s_timed_loop": wall, "solve_phases_us": trace_us, "K_per_gpu": s.K_local,
+           "lanes": s.lanes, "fast_math": int(s.fast_math), "flush": flush, "shard_bytes": shard_bytes,
+           "geometry": {k: s.geometry[k] for k in ("grid", "block", "smem", "stages", "stream_rows")}}
+    if with_e2e:
+        e2e_total, lat = time_e2e(s, x, U, steps, warmup, dist)
+        out["e2e"] = {"value": steps_total / e2e_total, "unit": "rollout-steps/s", "h2d_bytes_per_step": (s.ns + H) * 8,
+                      "d2h_bytes_per_step": (2 + H + (H + 1) * s.ns + 1) * 8,
+                      "p50_solve_ms": round(1e3 * statistics.median(lat), 4)}
+    # ---- rooflines of the solve kernel: algorithmic flops and bytes over its event-timed duration
+    kern_s = total_ms * 1e-3 / steps
+    local_steps = float(s.K_local) * H
+    ach_tf = local_steps * ALG_FLOPS[env] / kern_s / 1e12
+    ach_gb = local_steps * esz / kern_s / 1e9 if noise == "tensor" else 0.0
+    pipe = {"bound": "fp32_pipe" if dtype == "f32" else "fp64_pipe", "kernel": "mppi_solve_kernel", "achieved": ach_tf,
+            "peak": fma_peak, "unit": "TFLOP/s", "frac": ach_tf / fma_peak if fma_peak else None, "traffic": None,
+            "peak_source": "FMA-chain microbenchmark of this dtype run live (mpc_measure_fma_peak); "
+                           "MEASURED_PEAKS.json has no CUDA-core figure",
+            "alg_flops_per_step": ALG_FLOPS[env], "kernel_ms": kern_s * 1e3}
+    hbm = {"bound": "hbm", "kernel": "mppi_solve_kernel", "achieved": ach_gb, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+           "frac": ach_gb / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks_src,
+           "alg_bytes_per_step": esz if noise == "tensor" else 0, "kernel_ms": kern_s * 1e3}
+    ev = ncu_evidence(name, s.fast_math, s.lanes) if (noise == "tensor" and dist.world == 1 and dtype == "f32") else None
+    if ev:
+        for r in (pipe, hbm):
+            r["traffic"] = ev["dram_bytes_per_launch"]
+            r["traffic_source"] = "committed ncu --set full capture of this flavour (profiles/%s)" % ev.get("source")
+        pipe["traffic_over_algorithmic"] = ev["dram_bytes_per_launch"] / (local_steps * esz)
+        pipe["ncu"] = {k: ev[k] for k in ev if k != "dram_bytes_per_launch"}
+    # which roof binds: the one whose floor (work / peak) is the longer time
+    t_pipe = local_steps * ALG_FLOPS[env] / (fma_peak * 1e12) if fma_peak else 0.0
+    t_hbm = local_steps * esz / (peaks["hbm_gbs"] * 1e9) if noise == "tensor" else 0.0
+    if t_hbm > t_pipe:
+        out["roofline"], out["roofline_other"] = hbm, pipe
+    else:
+        out["roofline"], out["roofline_other"] = pipe, hbm
+    out["roofline"]["binding"] = "floor %.1f us vs %.1f us for the other roof" % (
+        1e6 * max(t_pipe, t_hbm), 1e6 * min(t_pipe, t_hbm))
+    # ---- N > 1: the sharded plan against the same solve on ONE GPU, and every rank's plan bit-equal
+    if dist.world > 1:
+        s.upload_inputs(x, None, U)
+        s.solve_enqueue(want_traj=False)
+        _, Un, _, _ = s.download_outputs()
+        h = plan_hash(Un)
+        hmin, hmax = -dist.max(-float(h)), dist.max(float(h))
+        sv = {"all_ranks_bit_equal": bool(hmin == hmax)}
+        if dist.rank == 0:
+            one = One(dist)
+            r = make_solver(capi, agent, env, K, H, prm, one, dtype=dtype, noise=noise, lanes=s.lanes,
+                            fast_math=s.fast_math)
+            r.upload_inputs(x, None, U)
+            r.solve_enqueue(want_traj=False)
+            _, U1, _, _ = r.download_outputs()
+            r.close()
+            sv.update(plan_max_abs=float(np.abs(Un - U1).max()), u0_abs=float(abs(Un[0, 0] - U1[0, 0])),
+                      note="same flavour, same Philox noise (indexed by global sample), K unsharded on rank 0's GPU; "
+                           "differences are the summation order of the weighted sum")
+        dist.barrier()
+        out["sharded_vs_single"] = sv
+    s.close()
+    if with_parity and dtype == "f32" and dist.rank == 0:
+        try:
+            out["parity"] = parity_block(capi, dist, env, H, prm, lanes=out["lanes"], fast_math=out["fast_math"])
+        except Exception as e:
+            out["parity"] = {"error": repr(e)}
+    return out
+
+
 def latency_extras(capi, dist, reps=200, warm=20):
     """p50 solve latency at K = 4096 (north_star: sub-ms) through the host-buffer call, 1 GPU."""
     out = {}
-
-    class One:  # single-GPU view
-        world, rank, local_rank = 1, 0, dist.local_rank
-    one = One()
+    one = One(dist)
     for env in ("pendulum", "cartpole", "acrobot"):
         H = 50
-        s = make_solver(capi, None, "MPPI", env, 4096, H, dict(lam=0.5, sigma=1.0), one)
+        s = make_solver(capi, "MPPI", env, 4096, H, dict(lam=0.5, sigma=1.0), one)
         x = np.array(START[env]) + 0.01
         U = np.zeros(H)
         for _ in range(warm):
@@ -264,50 +407,113 @@ def latency_extras(capi, dist, reps=200, warm=20):
             lat.append(time.perf_counter() - t)
         out["mppi_%s_k4096_h50_f32_p50_ms" % env] = round(1e3 * statistics.median(lat), 4)
         s.close()
-    # BASELINE configs[1]: CEM CartPole K=4096 H=50 n_elite=409 5 iterations
-    s = make_solver(capi, None, "CEM", "cartpole", 4096, 50, dict(sigma=1.0, max_iter=5, n_elite=409, epsilon=1e-5,
-                                                                 alpha=0.2), one, noise="philox")
+    return out
+
+
+def cem_extra(capi, dist, fma_peak, K=4096, reps=100, warm=10):
+    """BASELINE configs[1]: CEM CartPole, H = 50, elite ratio 0.1, 5 refit iterations, in-kernel Philox normals.  p50 of
+    the host-buffer call, device time per solve, the solve against the FP32 roofline, and float32 parity against the
+    library's float64 flavour on the same normals (elite-set overlap per iteration, mean)."""
+    one = One(dist)
+    H, iters, n_elite = 50, 5, max(1, K // 10)
+    prm = dict(sigma=1.0, max_iter=iters, n_elite=n_elite, epsilon=1e-5, alpha=0.2)
     x = np.array(START["cartpole"]) + 0.01
+    tag = "cem_cartpole_k%d_h50_5it" % K
+    out = {}
+    # parity first: fresh handles, so both draw the normals of solve 0
+    res = {}
+    for dt in ("f32", "f64"):
+        s = make_solver(capi, "CEM", "cartpole", K, H, prm, one, noise="philox", dtype=dt)
+        u0, Un, _, _, n_it = s.cem_solve(x, None, np.zeros(H))
+        res[dt] = (Un.copy(), [np.sort(s.cem_elites(i)) for i in range(n_it)], n_it)
+        s.close()
+    n_cmp = min(res["f32"][2], res["f64"][2])
+    out[tag + "_parity"] = {
+        "against": "float64 flavour of this library on the same Philox normals",
+        "elite_overlap_min": min(np.intersect1d(res["f32"][1][i], res["f64"][1][i]).size / n_elite for i in range(n_cmp)),
+        "mean_abs_max": float(np.abs(res["f32"][0] - res["f64"][0]).max()), "iterations": [res["f32"][2], res["f64"][2]]}
+    s = make_solver(capi, "CEM", "cartpole", K, H, prm, one, noise="philox")
     for _ in range(warm):
-        s.cem_solve(x, None, np.zeros(50))
+        s.cem_solve(x, None, np.zeros(H))
     lat = []
     for _ in range(reps):
         t = time.perf_counter()
-        *_, iters = s.cem_solve(x, None, np.zeros(50))
+        *_, n_it = s.cem_solve(x, None, np.zeros(H))
         lat.append(time.perf_counter() - t)
     p50 = statistics.median(lat)
-    out["cem_cartpole_k4096_h50_5it_f32_philox_p50_ms"] = round(1e3 * p50, 4)
-    out["cem_cartpole_k4096_h50_5it_steps_per_s"] = 4096 * 50 * iters / p50
+    s.upload_inputs(x, None, np.zeros(H))
+    dev_ms = statistics.median(s.time_solves(20, want_traj=False, flush_l2=False))
+    l0 = s.launch_count
+    s.solve_enqueue(want_traj=False)
+    s.sync()
+    launches = s.launch_count - l0
+    s.close()
+    out.update({tag + "_f32_philox_p50_ms": round(1e3 * p50, 4), tag + "_steps_per_s": K * H * n_it / p50,
+                tag + "_device_ms_per_solve": dev_ms, tag + "_launches_per_solve": launches})
+    ach = K * H * n_it * ALG_FLOPS["cartpole"] / (dev_ms * 1e-3) / 1e12
+    out[tag + "_roofline"] = {"bound": "fp32_pipe", "kernel": "all kernels of one CEM solve", "achieved": ach,
+                              "peak": fma_peak, "unit": "TFLOP/s", "frac": ach / fma_peak if fma_peak else None,
+                              "kernel_ms": dev_ms,
+                              "note": "K*H*iters = %d rollout-steps per solve: a latency-bound solve, not a "
+                                      "throughput one" % (K * H * n_it)}
+    return out
+
+
+def batch_extra(capi, dist):
+    """BASELINE configs[4]: 4096 independent CartPole MPPI solves (K = 1024, H = 50 each).  No data-path collective:
+    rank r owns solves [4096 r / N, 4096 (r + 1) / N) (replicas), one launch per rank; value = all solves / max time."""
+    Btot, K, H = 4096, 1024, 50
+    b0, b1 = Btot * dist.rank // dist.world, Btot * (dist.rank + 1) // dist.world
+    B = b1 - b0
+    one = One(dist)
+    s = make_solver(capi, "MPPI", "cartpole", K, H, dict(lam=0.5, sigma=1.0), one, batch=B)
+    rng = np.random.RandomState(0)
+    xs_all = np.array(START["cartpole"]) + rng.normal(0, 0.2, (Btot, 4))  # cartpole_swingup_model.py:50-51
+    xs = xs_all[b0:b1]
+    s.upload_inputs(xs, None, np.zeros((B, H)))
+    s.time_solves(3, want_traj=False, flush_l2=True)
+    dist.barrier()
+    each = s.time_solves(10, want_traj=False, flush_l2=True)
+    ms = dist.max(sum(each)) / 10
+    dist.barrier()
+    for _ in range(2):
+        s.mppi_solve(xs, None, np.zeros((B, H)), want_traj=True)
+    dist.barrier()
+    t = time.perf_counter()
+    for _ in range(5):
+        u0, Un, _, _ = s.mppi_solve(xs, None, np.zeros((B, H)), want_traj=True)
+    e2e_s = dist.max(time.perf_counter() - t) / 5
+    out = {"batch4096_cartpole_k1024_h50_f32_steps_per_s": Btot * K * H / (ms * 1e-3),
+           "batch4096_cartpole_k1024_h50_f32_ms_per_batch": ms,
+           "batch4096_cartpole_k1024_h50_f32_e2e_steps_per_s": Btot * K * H / e2e_s,
+           "batch4096_cartpole_k1024_h50_solves_per_rank": B,
+           "batch4096_cartpole_k1024_h50_scaling": "replicas: %d solves per rank, no collective" % B}
+    if dist.rank == 0:
+        # parity of the config's own size and dtype: three of the batch's solves against the float64 flavour
+        pick = [0, B // 2, B - 1]
+        r = make_solver(capi, "MPPI", "cartpole", K, H, dict(lam=0.5, sigma=1.0), one, dtype="f64", batch=len(pick))
+        _, U64, _, _ = r.mppi_solve(xs[pick], None, np.zeros((len(pick), H)), want_traj=False)
+        S64 = r.mppi_costs()
+        r.close()
+        S32 = s.mppi_costs()[pick]
+        rel = np.abs(S32 - S64) / np.abs(S64)
+        out["batch4096_cartpole_k1024_h50_parity"] = {
+            "against": "float64 flavour, same Philox noise, solves %s of this rank" % pick,
+            "cost_rel_p50": float(np.quantile(rel, .5)), "cost_rel_p99": float(np.quantile(rel, .99)),
+            "cost_rel_max": float(rel.max()), "plan_abs_max": float(np.abs(Un[pick] - U64).max())}
     s.close()
     return out
 
 
-def config_extras(capi, dist):
-    """The other BASELINE.json configs on one GPU (reported in `extra`, not the headline):
-    configs[4]: batch of 4096 independent CartPole MPPI solves (K = 1024, H = 50) in ONE launch;
-    configs[3]: MPPI Pendulum K = 65536, H = 50 over the temperature grid of scripts/mppi_temperature.py:23;
-    configs[0]-style closed loop: a 200-step Pendulum episode resident on the device (mpc_episode_run) next to the
-    same episode driven from the host one predict_action-sized call per step."""
+def temperature_extra(capi, dist):
+    """BASELINE configs[3]: MPPI Pendulum K = 65536, H = 50 over the temperature grid of scripts/mppi_temperature.py:23.
+    Latency of the host call per lambda, and what the small temperatures do to the float32 plan (the action
+    is a softmin of the costs, its error is the cost error times max|S| / lambda)."""
     out = {}
-    one = dist  # extras run on world == 1 only
-    # ---- configs[4]
-    B, K, H = 4096, 1024, 50
-    s = make_solver(capi, None, "MPPI", "cartpole", K, H, dict(lam=0.5, sigma=1.0), one, batch=B)
-    s.set_profiling(True)
-    rng = np.random.RandomState(0)
-    xs = np.array(START["cartpole"]) + rng.normal(0, 0.2, (B, 4))  # cartpole_swingup_model.py:50-51
-    s.upload_inputs(xs, None, np.zeros((B, H)))
-    ms, _, _, _ = time_device(s, 10, 3, one, flush=True)
-    out["batch4096_cartpole_k1024_h50_f32_steps_per_s"] = B * K * H * 10 / (ms * 1e-3)
-    out["batch4096_cartpole_k1024_h50_f32_ms_per_batch"] = ms / 10
-    t = time.perf_counter()
-    for _ in range(5):
-        s.mppi_solve(xs, None, np.zeros((B, H)), want_traj=True)
-    out["batch4096_cartpole_k1024_h50_f32_e2e_steps_per_s"] = B * K * H * 5 / (time.perf_counter() - t)
-    s.close()
-    # ---- configs[3]
+    one = One(dist)
     for lam in (0.001, 0.01, 0.1, 0.5, 1.0, 10.0):
-        s = make_solver(capi, None, "MPPI", "pendulum", 65536, 50, dict(lam=lam, sigma=1.0), one)
+        prm = dict(lam=lam, sigma=1.0)
+        s = make_solver(capi, "MPPI", "pendulum", 65536, 50, prm, one)
         x, U = np.array(START["pendulum"]), np.zeros(50)
         for _ in range(10):
             s.mppi_solve(x, None, U)
@@ -316,11 +522,21 @@ def config_extras(capi, dist):
             t = time.perf_counter()
             s.mppi_solve(x, None, U)
             lat.append(time.perf_counter() - t)
-        out["mppi_pendulum_k65536_h50_lam%g_p50_ms" % lam] = round(1e3 * statistics.median(lat), 4)
         s.close()
-    # ---- closed loop
+        out["mppi_pendulum_k65536_h50_lam%g_p50_ms" % lam] = round(1e3 * statistics.median(lat), 4)
+        p = parity_block(capi, dist, "pendulum", 50, prm, lanes=FLAVOUR["pendulum"][1], fast_math=FLAVOUR["pendulum"][0])
+        out["mppi_pendulum_k65536_h50_lam%g_parity" % lam] = {k: p[k] for k in ("cost_rel_p99", "cost_rel_max",
+                                                                                 "plan_abs_max", "u0_rel")}
+    return out
+
+
+def episode_extra(capi, dist):
+    """configs[0]-style closed loop: a 200-step Pendulum episode resident on the device (mpc_episode_run) next to the
+    same episode driven from the host, one predict_action-sized call per step."""
+    out = {}
+    one = One(dist)
     n = 200
-    s = make_solver(capi, None, "MPPI", "pendulum", 4096, 50, dict(lam=0.5, sigma=1.0), one)
+    s = make_solver(capi, "MPPI", "pendulum", 4096, 50, dict(lam=0.5, sigma=1.0), one)
     x0 = np.array(START["pendulum"])
     s.episode_run(x0, 20, U_in=np.zeros(50))
     t = time.perf_counter()
@@ -422,104 +638,74 @@ def run_ours(args, dist):
     mpc_b200.build_library()
     agent, env, K, H, prm = WORKLOADS[args.workload]
     peaks, peaks_src = measured_peaks()
-    s = make_solver(capi, None, agent, env, K, H, prm, dist, dtype=args.dtype, noise=args.noise, lanes=args.lanes,
-                    fast_math=args.fast_math)
-    s.set_profiling(True)
-    esz = 4 if args.dtype == "f32" else 8
-    shard_bytes = s.K_local * H * esz
-    flush = args.noise == "tensor" and shard_bytes < 2 * L2_BYTES or args.noise == "philox"
-    x = np.array(START[env]) + 0.01
-    U = np.zeros(H)
-    s.upload_inputs(x, None, U)
-
-    clocks = ClockSampler(dist.local_rank)
-    clocks.start()
-    total_ms, roll_ms, launches, wall = time_device(s, args.steps, args.warmup, dist, flush)
-    clk = clocks.stop()
-    steps_total = float(K) * H * args.steps
-    value = steps_total / (total_ms * 1e-3)
-
-    # phase stamps of the last timed solve's finalising block on rank 0 (us since its kernel start): where a solve's
-    # time goes when the shard is small (tiles_done = rollouts finished; peers_in = every rank's record has arrived)
-    try:
-        tr = s.trace()
-        trace_us = {k: round(v / 1e3, 1) for k, v in tr.items() if v is not None and k != "start"}
-    except Exception:
-        trace_us = None
-    e2e_total, lat = time_e2e(s, x, U, args.steps, args.warmup, dist)
-    e2e_value = steps_total / e2e_total
-    h2d = (s.ns + H) * 8
-    d2h = (2 + H + (H + 1) * s.ns + 1) * 8
-
-    # roofline of the dominant kernel (mppi_rollout_kernel): algorithmic flops / its own event-timed duration
-    roll_s = roll_ms * 1e-3 / args.steps
-    local_steps = float(s.K_local) * H
-    fma_peak = capi.measure_fma_peak(dist.local_rank, args.dtype) if dist.rank == 0 else 0.0
-    ach_tflops = local_steps * ALG_FLOPS[env] / roll_s / 1e12
-    roofline = {"bound": "fp32_pipe" if args.dtype == "f32" else "fp64_pipe", "kernel": "mppi_solve_kernel",
-                "achieved": ach_tflops, "peak": fma_peak, "unit": "TFLOP/s",
-                "frac": ach_tflops / fma_peak if fma_peak else None, "traffic": None,
-                "peak_source": "FMA-chain microbenchmark run live (mpc_measure_fma_peak); MEASURED_PEAKS.json has no "
-                               "CUDA-core figure", "alg_flops_per_step": ALG_FLOPS[env],
-                "kernel_ms": roll_ms / args.steps}
-    ev = ncu_evidence(args.workload, s.fast_math, s.lanes) if (args.noise == "tensor" and dist.world == 1) else None
-    if ev:
-        roofline["traffic"] = ev["dram_bytes_per_launch"]
-        roofline["traffic_over_algorithmic"] = ev["dram_bytes_per_launch"] / (local_steps * esz)
-        roofline["ncu"] = {k: ev[k] for k in ev if k != "dram_bytes_per_launch"}
-    hbm_ach = local_steps * esz / roll_s / 1e9 if args.noise == "tensor" else 0.0
-    roofline_hbm = {"bound": "hbm", "achieved": hbm_ach, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                    "frac": hbm_ach / peaks["hbm_gbs"], "traffic": ev["dram_bytes_per_launch"] if ev else None,
-                    "peak_source": peaks_src,
-                    "alg_bytes_per_step": esz if args.noise == "tensor" else 0}
-
+    fma_peak = {dt: capi.measure_fma_peak(dist.local_rank, dt) for dt in ("f32", "f64")}
+    common = dict(peaks=peaks, peaks_src=peaks_src)
+    r = run_mppi_workload(capi, dist, args.workload, args.steps, args.warmup, dtype=args.dtype, noise=args.noise,
+                          lanes=args.lanes, fast_math=args.fast_math, fma_peak=fma_peak[args.dtype], **common)
     line = {
-        "metric": "rollout_steps_per_sec", "value": value, "unit": "rollout-steps/s", "n_gpus": dist.world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+        "metric": "rollout_steps_per_sec", "value": r["value"], "unit": "rollout-steps/s", "n_gpus": dist.world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": args.workload, "agent": agent, "env": env, "K": K, "H": H, **prm,
-                   "noise": args.noise, "lanes_per_thread": s.lanes, "fast_math": bool(s.fast_math), "K_per_gpu": s.K_local,
-                   "cache": ("L2 flushed (256 MiB write) between timed steps" if flush else
-                             "noise shard %.0f MB per GPU > L2 (126 MB): no flush" % (shard_bytes / 1e6)),
+                   "noise": args.noise, "lanes_per_thread": r["lanes"], "fast_math": bool(r["fast_math"]),
+                   "K_per_gpu": r["K_per_gpu"],
+                   "timed_step": "one MPPI._calc_action: rollout of K x H + softmin update of the plan, one kernel; "
+                                 "K solves enqueued back to back, one CUDA-event pair each (e2e adds the host "
+                                 "buffers and the logging rollout of Agent.predict_action)",
+                   "cache": ("L2 flushed (256 MiB write, untimed) between timed steps" if r["flush"] else
+                             "noise shard %.0f MB per GPU > L2 (126 MB): no flush" % (r["shard_bytes"] / 1e6)),
                    "parallelism": "K-shard x%d, one all-gather of (beta, eta, E[H]) per solve (%s)" % (
                        dist.world, "single GPU" if dist.world == 1 else
                        ("inside the solve kernel over NVLink peer memory"
                         if os.environ.get("MPC_B200_EXCHANGE", "p2p") == "p2p" else "NCCL + merge kernel"))},
-        "clocks": clk, "gpu_launches": launches,
-        "e2e": {"value": e2e_value, "unit": "rollout-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "p50_solve_ms": round(1e3 * statistics.median(lat), 4)},
-        "roofline": roofline, "roofline_hbm": roofline_hbm, "wall_s_timed_loop": wall, "solve_phases_us": trace_us,
+        "clocks": r["clocks"], "gpu_launches": r["gpu_launches"], "e2e": r["e2e"],
+        "roofline": r["roofline"], "roofline_other": r["roofline_other"], "wall_s_timed_loop": r["wall_s_timed_loop"],
+        "solve_phases_us": r["solve_phases_us"], "geometry": r["geometry"],
     }
-    s.close()
+    for k in ("parity", "sharded_vs_single"):
+        if k in r:
+            line[k] = r[k]
+    if not args.no_extra:
+        extra = {}
+
+        def brief(w):
+            keep = {k: w[k] for k in ("value", "ms_per_step", "e2e", "solve_phases_us", "parity", "sharded_vs_single",
+                                      "K_per_gpu", "lanes", "fast_math") if k in w}
+            keep["roofline"] = {k: w["roofline"][k] for k in ("bound", "achieved", "peak", "unit", "frac", "kernel_ms")}
+            keep["roofline_other"] = {k: w["roofline_other"][k] for k in ("bound", "achieved", "peak", "unit", "frac")}
+            return keep
+        try:
+            # north_star's own target configuration (K = 2^20, H = 50), K-sharded over all ranks like the headline
+            for wl in ("mppi_pendulum_h50_k1m", "mppi_cartpole_h50_k1m"):
+                if wl != args.workload:
+                    extra[wl] = brief(run_mppi_workload(capi, dist, wl, 10, 3, fma_peak=fma_peak["f32"], **common))
+            extra.update(batch_extra(capi, dist))  # configs[4]: replicas over the ranks
+            if dist.world == 1:
+                # float64 (the reference's own arithmetic, parity unconditional) against the measured DFMA peak
+                for wl in (args.workload, "mppi_pendulum_h50_k1m", "mppi_cartpole_h50_k1m"):
+                    w = run_mppi_workload(capi, dist, wl, 5, 3, dtype="f64", with_parity=False, with_e2e=False,
+                                          fma_peak=fma_peak["f64"], **common)
+                    extra[wl + "_f64"] = brief(w)
+                for wl in ("mppi_pendulum_h50_k1m", "mppi_cartpole_h50_k1m", args.workload):
+                    w = run_mppi_workload(capi, dist, wl, 5, 3, noise="philox", with_parity=False, with_e2e=False,
+                                          fma_peak=fma_peak["f32"], **common)
+                    extra[wl + "_philox"] = brief(w)
+                if r["fast_math"]:  # the agents' default flavour (polynomial sincos) of the headline workload
+                    w = run_mppi_workload(capi, dist, args.workload, 5, 3, fast_math=0, lanes=2, with_e2e=False,
+                                          fma_peak=fma_peak["f32"], **common)
+                    extra[args.workload + "_polynomial_trig"] = brief(w)
+                extra.update(latency_extras(capi, dist))
+                extra.update(cem_extra(capi, dist, fma_peak["f32"]))
+                extra.update(temperature_extra(capi, dist))
+                extra.update(episode_extra(capi, dist))
+        except Exception as e:  # extras must never take the headline line down
+            import traceback
+            extra["error"] = repr(e) + " | " + traceback.format_exc().splitlines()[-2].strip()
+        line["extra"] = extra
     if dist.rank == 0:
         if dist.world == 1:
             cb, _, _ = cpu_baseline_sample(env, K, H, prm)
             line["cpu_baseline"] = cb
-            if not args.no_extra:
-                extra = {}
-                try:
-                    extra.update(latency_extras(capi, dist))
-                    extra.update(config_extras(capi, dist))
-                    one = dist
-                    for wl in ("mppi_pendulum_h50_k1m", "mppi_cartpole_h50_k1m"):
-                        a2, e2, K2, H2, p2 = WORKLOADS[wl]
-                        for noise in ("tensor", "philox"):
-                            s2 = make_solver(capi, None, a2, e2, K2, H2, p2, one, dtype="f32", noise=noise)
-                            s2.set_profiling(True)
-                            s2.upload_inputs(np.array(START[e2]) + 0.01, None, np.zeros(H2))
-                            ms, rms, _, _ = time_device(s2, 10, 3, one, flush=(noise == "philox"))
-                            extra["%s_%s_f32_steps_per_s" % (wl, noise)] = K2 * H2 * 10 / (ms * 1e-3)
-                            extra["%s_%s_f32_rollout_kernel_ms" % (wl, noise)] = rms / 10
-                            s2.close()
-                    s3 = make_solver(capi, None, agent, env, K, H, prm, one, dtype="f32", noise="philox")
-                    s3.set_profiling(True)
-                    s3.upload_inputs(x, None, U)
-                    ms, rms, _, _ = time_device(s3, 5, 3, one, flush=True)
-                    extra["%s_philox_f32_steps_per_s" % args.workload] = K * H * 5 / (ms * 1e-3)
-                    s3.close()
-                except Exception as e:  # extras must never take the headline line down
-                    extra["error"] = repr(e)
-                line["extra"] = extra
         print(json.dumps(line))
 
 

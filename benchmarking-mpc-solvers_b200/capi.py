@@ -462,8 +462,10 @@ class Solver:
         self._ck(self.L.mpc_timer_stop(self._h, C.byref(ms)))
         return ms.value
 
-    def set_profiling(self, on=True, store_costs=True):
-        self._ck(self.L.mpc_set_profiling(self._h, int(bool(on)) | (0 if store_costs else 2)))
+    def set_profiling(self, on=True, store_costs=True, rollout_events=False):
+        """on: phase stamps of the finalising block (trace()); store_costs=False: skip the per-sample cost store;
+        rollout_events: an event pair around every solve kernel (rollout_ms()) — two more stream operations per solve."""
+        self._ck(self.L.mpc_set_profiling(self._h, int(bool(on)) | (0 if store_costs else 2) | (4 if rollout_events else 0)))
 
     def rollout_ms(self):
         ms = C.c_float()

@@ -73,6 +73,7 @@ struct mpc_handle {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evr0 = nullptr, evr1 = nullptr;
     bool profiling = false;
+    bool rollout_events = false;  // mpc_set_profiling bit 2: an event pair around the solve kernel (mpc_get_rollout_ms)
     bool store_costs = true;      // mpc_set_profiling(h, 2) turns the per-sample cost store off (tools/trace_probe.py)
     bool prefer_stream = false;   // STREAM flavour whenever it gives more resident warps than whole tiles (see mpc_create)
     // device
@@ -81,9 +82,9 @@ struct mpc_handle {
     bool has_noise_map = false;
     double *d_in = nullptr;       // x0 [B][ns] | g_z [B][H][nz] | U [B][H]
     double *d_S = nullptr;        // [B][Kpad]
-    double *d_part = nullptr;     // [B][max_parts][2+H]
+    double *d_part = nullptr;     // [B][part_stride][2+H]: block (or warp) records, then the group records
     double *d_rank_part = nullptr;  // [world][B][2+H]
-    int *d_done = nullptr;        // [B] block arrival tickets of the solve kernel
+    int *d_done = nullptr;        // [B][1 + n_groups] block arrival tickets of the solve kernel
     // peer exchange (multi-GPU, in-kernel all-gather): this rank's buffer and every rank's mapped buffer
     double *d_xchg = nullptr;     // [2][world][B][2+H] doubles | u64 flags [2][world][B] (double-buffered by epoch parity)
     double *peer_recs[16] = {nullptr};
@@ -491,6 +492,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         }
         int max_smem = 0;
         CUC(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
+        max_smem -= 1024;  // the solve kernel's static shared memory (reduction scratch, profiling stamps) shares the limit
         const int nblk_cap = h->num_sms > 32 ? h->num_sms : 32;  // records the last block may have to merge
         // does a block of W warps with a ring of S stages of `rows` time steps fit in shared memory?
         auto fits = [&](int W, int S, int rows) {
@@ -569,6 +571,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
             g.blocks_per_solve = 1;
             g.chunk = tps;
             g.max_parts = W;
+            g.n_groups = 0;
             const long long per = (long long)cfg->H * (1 + h->nz) * 8;
             long long G = (96 * 1024) / per;
             if (G > g.solves_per_block) G = g.solves_per_block;
@@ -586,9 +589,11 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
             g.blocks_per_solve = nb;
             g.grid = g.B * nb;
             g.max_parts = nb;
+            g.n_groups = nb > MERGE_GROUP ? (nb + MERGE_GROUP - 1) / MERGE_GROUP : 0;  // two-level merge (mppi.cuh tail)
             g.fin_group = 1;
         }
         if (g.stream_rows) S = W * g.stream_depth;
+        g.part_stride = g.max_parts + g.n_groups;
         g.warps = W;
         g.stages = S;
         const int cap = g.max_parts > W ? g.max_parts : W;
@@ -641,12 +646,12 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     }
     if (cfg->agent == MPC_AGENT_MPPI) {
         CUC(cudaMalloc(&h->d_S, (size_t)g.B * g.Kpad * sizeof(double)));
-        CUC(cudaMalloc(&h->d_part, (size_t)g.B * g.max_parts * rec * sizeof(double)));
+        CUC(cudaMalloc(&h->d_part, (size_t)g.B * g.part_stride * rec * sizeof(double)));
         CUC(cudaMalloc(&h->d_rank_part, (size_t)cfg->world * g.B * rec * sizeof(double)));
         CUC(cudaMalloc(&h->d_trace, 16 * sizeof(unsigned long long)));
         CUC(cudaMemsetAsync(h->d_trace, 0, 16 * sizeof(unsigned long long), h->stream));
-        CUC(cudaMalloc(&h->d_done, (size_t)g.B * sizeof(int)));
-        CUC(cudaMemsetAsync(h->d_done, 0, (size_t)g.B * sizeof(int), h->stream));
+        CUC(cudaMalloc(&h->d_done, (size_t)g.B * (1 + g.n_groups) * sizeof(int)));
+        CUC(cudaMemsetAsync(h->d_done, 0, (size_t)g.B * (1 + g.n_groups) * sizeof(int), h->stream));
     } else {
         CUC(cudaMalloc(&h->d_sd, (size_t)g.H * sizeof(double)));
         CUC(cudaMalloc(&h->d_R, (size_t)cfg->max_iter * g.Kpad * sizeof(double)));
@@ -858,9 +863,9 @@ static int mppi_enqueue(mpc_handle *h, int want_traj, bool host_flag = false) {
         a.host_epoch = ++h->host_epoch;
     }
     const MppiBuffers b = mppi_bufs(h);
-    if (h->profiling) CU(h, cudaEventRecord(h->evr0, h->stream));
+    if (h->rollout_events) CU(h, cudaEventRecord(h->evr0, h->stream));
     CU(h, launch_mppi_solve(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
-    if (h->profiling) CU(h, cudaEventRecord(h->evr1, h->stream));
+    if (h->rollout_events) CU(h, cudaEventRecord(h->evr1, h->stream));
     h->launches++;
     if (h->cfg.world > 1 && !a.p2p) {
         const size_t cnt = (size_t)h->g.B * (PART_HDR + h->g.H);
@@ -1441,12 +1446,13 @@ int mpc_set_profiling(mpc_handle *h, int32_t on) {
     if (!h) return MPC_EINVAL;
     h->profiling = (on & 1) != 0;
     h->store_costs = (on & 2) == 0;
+    h->rollout_events = (on & 4) != 0;
     return MPC_OK;
 }
 
 int mpc_get_rollout_ms(mpc_handle *h, float *ms_out) {
     if (!h || !ms_out) return MPC_EINVAL;
-    if (!h->profiling) return fail(h, MPC_ESTATE, "profiling is off: call mpc_set_profiling(h, 1) before the solve");
+    if (!h->rollout_events) return fail(h, MPC_ESTATE, "rollout events are off: call mpc_set_profiling(h, 4) before the solve");
     CU(h, cudaSetDevice(h->cfg.device));
     CU(h, cudaEventSynchronize(h->evr1));
     CU(h, cudaEventElapsedTime(ms_out, h->evr0, h->evr1));

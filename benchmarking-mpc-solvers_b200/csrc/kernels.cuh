@@ -7,6 +7,7 @@ namespace mpc {
 
 constexpr int TILE = 128;       // padding unit of K (row stride of the noise tensor) and CEM block size
 constexpr int PART_HDR = 2;     // partial record = [beta, eta, E[0..H-1]]
+constexpr int MERGE_GROUP = 16; // records merged warp-locally in one L2 round trip; block records are merged in groups of it
 
 // NOISE_STREAM: the resident tensor again, but staged in small per-warp chunk rings and re-read (L2) by the weighted sum
 enum { NOISE_TENSOR = 0, NOISE_PHILOX = 1, NOISE_STREAM = 2 };
@@ -35,6 +36,8 @@ struct Geometry {
     int chunk;            // mode A: consecutive tiles per block
     int grid;             // solve-kernel blocks
     int max_parts;        // partial records per solve: blocks_per_solve (A) or warps (B)
+    int n_groups;         // mode A, more than MERGE_GROUP blocks per solve: groups of the two-level merge; else 0
+    int part_stride;      // records per solve in `part`: max_parts + n_groups (the group records follow the block records)
     int fin_group;        // mode B: solves finalised together (one thread per nominal rollout)
     int stream_rows;      // 0 = whole [H][wt] tiles in the ring; > 0 = STREAM: time steps per chunk of a warp's private ring
     int stream_depth;     // STREAM: chunk stages per warp
@@ -96,10 +99,10 @@ struct MppiBuffers {
     const double *g_z;     // [B][H][nz]
     double *U;             // [B][H]   device-resident plan (in: before, out: after)
     double *S;             // [B][Kpad]
-    double *part;          // [B][max_parts][2+H]
+    double *part;          // [B][part_stride][2+H]
     double *rank_part;     // [world][B][2+H]  (all-gather buffer; this rank writes slot `rank`)
     double *out;           // [B][out_stride]: u0, U[H], cost, xs[(H+1)*ns]
-    int *done_count;       // [B] arrival tickets of the solve kernel's blocks (self-cleaning)
+    int *done_count;       // [B][1 + n_groups] arrival tickets of the solve kernel's blocks (self-cleaning)
     double *const *peer_recs;  // host array [world] of the ranks' exchange buffers (p2p), else null
 };
 

@@ -46,7 +46,7 @@ struct WarpTile {
 };
 
 // Shared-memory layout.  Offset 0: the warps' running records [W][2 + H] doubles (beta, eta, E[H]) — they live through
-// the whole kernel (the weighted sum of every tile folds into them).  Then the tile loop's ring | U | weights |
+// the whole kernel (the weighted sum of every tile folds into them) — and the plan in float64 [H].  Then the tile loop's ring | U | weights |
 // mbarriers | gen; the tail reuses everything behind the records after a block barrier.
 template <typename V>
 struct RingSmem {
@@ -54,7 +54,10 @@ struct RingSmem {
     static constexpr int WT = WarpTile<V>::WT;
     static __host__ __device__ size_t a16(size_t b) { return (b + 15) / 16 * 16; }
     static __host__ __device__ size_t a128(size_t b) { return (b + 127) / 128 * 128; }
-    static __host__ __device__ size_t off_ring(int H, int W) { return a128((size_t)W * (PART_HDR + H) * sizeof(double)); }
+    // [H] doubles behind the records: the block's float64 copy of the plan (the finalising block applies the update
+    // to it without another trip to global memory)
+    static __host__ __device__ size_t off_Ud(int H, int W) { return (size_t)W * (PART_HDR + H) * sizeof(double); }
+    static __host__ __device__ size_t off_ring(int H, int W) { return a128(off_Ud(H, W) + (size_t)H * sizeof(double)); }
     // a stage holds `rows` time steps of one warp tile: rows = H (whole tiles), or the STREAM chunk
     static __host__ __device__ size_t stage_bytes(int rows) { return (size_t)rows * WT * sizeof(R); }
     static __host__ __device__ size_t off_sU(int H, int rows, int S, int W) { return off_ring(H, W) + S * stage_bytes(rows); }
@@ -206,7 +209,7 @@ __device__ __forceinline__ int ticket_acq_rel(int *p) {
 // meet in shared memory in a fixed order, so repeated solves are bit-identical.
 // Scratch: sscale[count], sEw[>= G][H] (callers size it [warps][H]; G <= warps), red[32].  All threads return beta / eta.
 constexpr int MERGE_BATCH = 20;
-constexpr int MERGE_SMALL = 16;  // up to this many records are merged warp-locally (no block reductions)
+constexpr int MERGE_SMALL = MERGE_GROUP;  // up to this many records are merged warp-locally (no block reductions)
 __device__ __forceinline__ void block_merge(const double neg_inv_lam, const int H, const double *src, const int count,
                                             const size_t stride, double *sscale, double *sEw, double *red,
                                             double *Eout, double *beta_out, double *eta_out) {
@@ -339,7 +342,9 @@ template <class Env>
 __device__ __forceinline__ void block_apply(const MppiArgs &a, const EnvConst<typename Env::Vec> &ec, const int b,
                                             const bool final_stage, const double beta, const double eta,
                                             const double *Eout, double *rank_part, const double *x0g,
-                                            const double *g_z, double *Ug, double *out, double *sUc, double *sG) {
+                                            const double *g_z, double *Ug, double *out, double *sUc, double *sG,
+                                            const double *Usrc = nullptr) {  // the plan before the update, if the
+                                                                              // caller holds a copy of Ug[b] (shared memory)
     constexpr int NS = Env::NS, NZ = Env::NS + 1;
     const int H = a.g.H, tid = threadIdx.x, nt = blockDim.x, rec_len = PART_HDR + H;
     if (a.record_only && !final_stage) {
@@ -352,10 +357,11 @@ __device__ __forceinline__ void block_apply(const MppiArgs &a, const EnvConst<ty
         return;
     }
     double *U = Ug + (size_t)b * H;
+    const double *Uold = Usrc ? Usrc : U;
     double *o = out + (size_t)b * (size_t)(2 + H + (H + 1) * NS);
     const double inv_eta = 1.0 / eta;
     for (int t = tid; t < H; t += nt) {
-        const double un = U[t] + inv_eta * Eout[t];  // w = (1/eta)*tmp ; planned_us += erg   mppi.py:62,69
+        const double un = Uold[t] + inv_eta * Eout[t];  // w = (1/eta)*tmp ; planned_us += erg   mppi.py:62,69
         U[t] = un;
         o[1 + t] = un;
         if (t == 0) o[0] = un;                       // u0 = planned_us[0]  (mppi.py:71)
@@ -402,6 +408,7 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
     const int rec_len = PART_HDR + H;
     double *wrec_all = reinterpret_cast<double *>(smem_raw);  // [W][rec_len]: the warps' running (beta, eta, E[H])
     double *wrec = wrec_all + (size_t)w * rec_len;
+    double *sUd = reinterpret_cast<double *>(smem_raw + RingSmem<V>::off_Ud(H, W));  // mode A: the plan in float64
     R *stages = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_ring(H, W));
     // the plan in the rollout dtype: one copy per block (mode A: one solve per block) or per warp (mode B)
     R *sU = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sU(H, rows, S, W)) + (mode_b ? (size_t)w * H : 0);
@@ -476,7 +483,11 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
     }
     // mode A: the block's single solve's plan, once per block (every warp reads the same copy)
     if (!mode_b)
-        for (int t = tid; t < H; t += blockDim.x) sU[t] = (R)Ug[(size_t)b_lo * H + t];
+        for (int t = tid; t < H; t += blockDim.x) {
+            const double u = Ug[(size_t)b_lo * H + t];
+            sUd[t] = u;
+            sU[t] = (R)u;
+        }
     for (int t = lane; t < rec_len; t += 32) wrec[t] = 0.0;  // E starts at zero (the first tile's scale_old is 0, 0 * NaN is not)
     __syncthreads();
     if (NOISE == NOISE_TENSOR || STREAM) {
@@ -510,7 +521,7 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
     };
     // mode B only: the warp's record of solve `cur` goes to global memory (slot = warp)
     auto flush_global = [&]() {
-        double *rec = part + ((size_t)cur * a.g.max_parts + w) * rec_len;
+        double *rec = part + ((size_t)cur * a.g.part_stride + w) * rec_len;
         __syncwarp();
         if (lane == 0) {
             rec[0] = beta_run;
@@ -795,7 +806,10 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
         for (int i = 0; i < W; ++i) bb = fmin(bb, wrec_all[(size_t)i * rec_len]);
         if (tid < W) sscale[tid] = rec_scale(a.neg_inv_lam, wrec_all[(size_t)tid * rec_len], bb);
         __syncthreads();
-        double *grec = part + ((size_t)b * a.g.max_parts + part_idx) * rec_len;
+        // records of solve b: [max_parts] block records, then [n_groups] group records
+        double *const solve_part = part + (size_t)b * a.g.part_stride * rec_len;
+        int *const tickets = done_count + (size_t)b * (1 + a.g.n_groups);  // [0] the solve's, [1 + g] group g's
+        double *grec = solve_part + (size_t)part_idx * rec_len;
         for (int t = tid; t < H; t += nt) {
             double e = 0.0;
             for (int i = 0; i < W; ++i) e += sscale[i] * wrec_all[(size_t)i * rec_len + PART_HDR + t];
@@ -808,25 +822,50 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
             grec[1] = eta;
         }
         const unsigned long long t_b = a.trace ? global_ns() : 0ull;
-        __syncthreads();  // every thread's record stores precede thread 0's release below
-        if (tid == 0) {
-            const int ticket = ticket_acq_rel(&done_count[b]);
-            s_last = (ticket == nb - 1);
-            if (s_last) done_count[b] = 0;  // self-cleaning: ready for the next solve on this stream
+        // arrive: the block barrier orders every thread's record stores before thread 0's acq_rel ticket; the block
+        // whose ticket completes the count sees the other blocks' records after the second barrier.  Self-cleaning.
+        auto arrive_last = [&](int *counter, int expected) {
+            __syncthreads();
+            if (tid == 0) {
+                const int ticket = ticket_acq_rel(counter);
+                s_last = (ticket == expected - 1);
+                if (s_last) *counter = 0;
+            }
+            __syncthreads();
+            return s_last != 0;
+        };
+        double beta, eta;
+        const double *final_src = solve_part;
+        int final_count = nb;
+        if (a.g.n_groups > 0) {
+            // Two-level merge: a merge of many records is a chain of dependent L2 round trips in ONE block on the
+            // critical path of every solve (5-8 us for 148 records).  Groups of MERGE_SMALL consecutive blocks: the last
+            // block of a group to arrive merges the group's records warp-locally (every load in flight at once, one
+            // round trip) into a group record; the last GROUP to arrive merges the <= MERGE_SMALL group records the same
+            // way.  Membership and summation order are fixed, so repeated solves stay bit-identical.
+            const int g = part_idx / MERGE_SMALL, gcount = min(MERGE_SMALL, nb - g * MERGE_SMALL);
+            if (!arrive_last(&tickets[1 + g], gcount)) return;
+            block_merge(a.neg_inv_lam, H, solve_part + (size_t)g * MERGE_SMALL * rec_len, gcount, (size_t)rec_len, sscale,
+                        sEw, red, Eout, &beta, &eta);
+            double *rec2 = solve_part + (size_t)(a.g.max_parts + g) * rec_len;
+            for (int t = tid; t < H; t += nt) rec2[PART_HDR + t] = Eout[t];
+            if (tid == 0) {
+                rec2[0] = beta;
+                rec2[1] = eta;
+            }
+            final_src = solve_part + (size_t)a.g.max_parts * rec_len;
+            final_count = a.g.n_groups;
         }
-        __syncthreads();
-        if (!s_last) return;
+        if (!arrive_last(&tickets[0], a.g.n_groups > 0 ? a.g.n_groups : nb)) return;
         if (a.trace && tid == 0) {
-            a.trace[TR_TILES_DONE] = t_wmax;  // the last warp's exit from the tile loop
+            a.trace[TR_TILES_DONE] = t_wmax;  // the last warp's exit from the tile loop (of the finalising block)
             a.trace[9] = t_a;
             a.trace[10] = t_b;
             a.trace[12] = t_wmin;
             a.trace[13] = t_wmax;
         }
         stamp(a.trace, TR_TICKET);
-        double beta, eta;
-        block_merge(a.neg_inv_lam, H, part + (size_t)b * a.g.max_parts * rec_len, nb, (size_t)rec_len, sscale, sEw, red,
-                    Eout, &beta, &eta);
+        block_merge(a.neg_inv_lam, H, final_src, final_count, (size_t)rec_len, sscale, sEw, red, Eout, &beta, &eta);
         stamp(a.trace, TR_MERGED);
         double *const err_word = out + (size_t)a.g.B * (2 + H + (H + 1) * NS);
         if (a.p2p) {
@@ -849,9 +888,9 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
             block_merge(a.neg_inv_lam, H, peer_recs(pt.recs[a.rank], a.world, a.g.B, rec_len, a.epoch) + (size_t)b * rec_len,
                         a.world, (size_t)a.g.B * rec_len, sscale, sEw, red, Eout, &beta, &eta);
             stamp(a.trace, TR_MERGED2);
-            block_apply<Env>(a, ec, b, true, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG);
+            block_apply<Env>(a, ec, b, true, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG, sUd);
         } else {
-            block_apply<Env>(a, ec, b, false, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG);
+            block_apply<Env>(a, ec, b, false, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG, sUd);
         }
         if (a.host_out && !(a.record_only)) {
             // outputs straight into the caller-visible pinned buffer, then the completion flag (system-scope release)
@@ -878,7 +917,7 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
             for (int sl = w; sl < ng; sl += W) {
                 const int b = b_lo + g0 + sl;
                 // one warp, one solve: merge `cnt` (<= 32) records, lane j holds record j's scale
-                const double *recs = part + (size_t)b * a.g.max_parts * rec_len;
+                const double *recs = part + (size_t)b * a.g.part_stride * rec_len;
                 size_t rstride = rec_len;
                 int cnt = W;
                 double bj = (lane < cnt) ? recs[(size_t)lane * rstride] : INFINITY;

@@ -245,10 +245,11 @@ int mpc_download_outputs(mpc_handle *h, double *u0, double *U_out, double *xs_ou
 int mpc_timer_start(mpc_handle *h);
 int mpc_timer_stop(mpc_handle *h, float *ms_out); /* records, synchronises, returns elapsed ms */
 int mpc_sync(mpc_handle *h);
-/* With profiling on, every MPPI solve brackets its rollout kernel (the dominant kernel) with its own event pair;
- * mpc_get_rollout_ms returns that kernel's device time for the last solve. */
-int mpc_set_profiling(mpc_handle *h, int32_t on); /* bit 0: profiling; bit 1: do NOT store the per-sample costs (then
-                                                     mpc_mppi_get_costs fails with MPC_ESTATE instead of returning stale data) */
+/* Profiling switches.  bit 0: the finalising block stamps its phases (mpc_get_trace); bit 1: do NOT store the
+ * per-sample costs (then mpc_mppi_get_costs fails with MPC_ESTATE instead of returning stale data); bit 2: every MPPI
+ * solve brackets its kernel with its own event pair — two more stream operations per solve — and mpc_get_rollout_ms
+ * returns that kernel's device time for the last solve. */
+int mpc_set_profiling(mpc_handle *h, int32_t on);
 int mpc_get_rollout_ms(mpc_handle *h, float *ms_out);
 /* With profiling on, the block that finalises an MPPI solve stamps its phases with %globaltimer (ns): out[0] kernel
  * start, [1] all tiles done, [2] last block's ticket, [3] block records merged, [4] rank record published to the

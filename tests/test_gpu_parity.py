@@ -6,6 +6,23 @@
 Tolerances (BASELINE.json north_star): float64 mode rel 1e-12 on costs; float32 mode rel 1e-5 on costs.
 Actions/plans are a softmin of the costs, so their error is the cost error amplified by max|S|/lam (SURVEY.md H1);
 the bound used for them is written next to each assertion.
+
+THE FLOAT32 BARS, in one place (f32_cost_bar below; measured: profiles/r2b_parity_probe.jsonl,
+profiles/r2d_parity_probe_golden_energetic.jsonl).  A float32 rollout of a chaotic system cannot follow the float64
+one sample by sample: rounding differences grow with the local Lyapunov exponent, whatever the arithmetic flavour.
+Both trig flavours — polynomial sincos (the agents' default) and MUFU (`fast_math`, what bench.py quotes for Pendulum
+and Acrobot) — are held to the SAME bars, and their quantiles are compared with each other in
+test_mppi_mufu_flavour_is_not_worse_in_kind:
+  * Pendulum, every regime and horizon tested: EVERY sample within rel 1e-5 (measured max 4.5e-7).
+  * Near the equilibrium the planning starts from (`_rand_case`: state N(0, 0.2) around the start, plan in +-0.5):
+    Acrobot up to H = 50 every sample within 1e-5 (measured max 2.5e-7); Acrobot at H = 100 at most 0.05 % of the
+    samples (or one of a small K) beyond 1e-5 (measured 5 / 7 of 65536, polynomial / MUFU); CartPole p95 within 1e-5
+    (about 1 % of the samples leave it in ANY float32 evaluation; MUFU doubles that share, so CartPole always runs the
+    polynomial in bench.py).
+  * Energetic regime (the reference-generated fixtures with plans up to +-1.5, swing-up states): Acrobot and CartPole
+    p90 within 1e-5, max 2e-3 for the fixtures; for H = 100 Acrobot swing-ups the tail reaches 1e-1 for 0.01 % of the
+    samples in EITHER flavour while the median stays below 3e-7 — float64 mode (rel 1e-12 on every sample) is the
+    mode for sample-exact parity, and the plan (a softmin average) is checked against its conditioning bound.
 """
 import json
 import os
@@ -25,6 +42,24 @@ START = {"pendulum": np.array([np.pi, 0.0]), "cartpole": np.array([0.0, 0.0, np.
          "acrobot": np.array([0.0, 0.0, 0.0, 0.0])}
 F64_COST_RTOL = 1e-12
 F32_COST_RTOL = 1e-5
+
+
+def f32_cost_bar(env, H, rel, what="", energetic=False):
+    """Assert the float32 per-sample cost bar of (env, H, regime) stated in the module docstring on the relative
+    errors `rel` (against the float64 oracle / reference on the identical noise)."""
+    n_over = int((rel > F32_COST_RTOL).sum())
+    msg = "%s %s H=%d: p50 %.1e p95 %.1e max %.1e, %d of %d beyond 1e-5" % (
+        what, env, H, np.quantile(rel, .5), np.quantile(rel, .95), rel.max(), n_over, rel.size)
+    if env == "pendulum":
+        assert rel.max() <= F32_COST_RTOL, msg
+    elif energetic:
+        assert np.quantile(rel, 0.90) <= F32_COST_RTOL and rel.max() <= 2e-3, msg
+    elif env == "acrobot" and H <= 50:
+        assert rel.max() <= F32_COST_RTOL, msg
+    elif env == "acrobot":
+        assert n_over <= max(1, int(5e-4 * rel.size)) and rel.max() <= 2e-3, msg
+    else:
+        assert np.quantile(rel, 0.95) <= F32_COST_RTOL and rel.max() <= 2e-3, msg
 
 
 def _load(golden_dir, name):
@@ -84,10 +119,7 @@ def test_mppi_golden_cases(golden_dir, dtype):
             if dtype == "f64":
                 np.testing.assert_allclose(S, Sref, rtol=rt, err_msg="case %d solve %d" % (ci, sv))
             else:
-                # float32: rel 1e-5 for the bulk; chaotic divergence lets a small tail exceed it
-                rel = np.abs(S - Sref) / np.abs(Sref)
-                assert np.quantile(rel, 0.95) <= rt, "case %d: p95 rel err %.2e" % (ci, np.quantile(rel, 0.95))
-                assert rel.max() <= 2e-3, "case %d: max rel err %.2e" % (ci, rel.max())
+                f32_cost_bar(mt["env"], H, np.abs(S - Sref) / np.abs(Sref), "golden case %d" % ci, energetic=True)
             if dtype == "f64":
                 tol = _plan_tol(Sref, mt["lam"], rt)
                 np.testing.assert_allclose(Unew[0], d[p + "U_out"][sv].reshape(-1), rtol=tol, atol=tol,
@@ -124,8 +156,7 @@ def test_mppi_vs_oracle_tensor_noise(env, dtype):
             tol = _plan_tol(S_ref, lam, F64_COST_RTOL)
             np.testing.assert_allclose(Unew[0], U_ref, rtol=tol, atol=tol)
         else:
-            assert np.quantile(rel, 0.95) <= F32_COST_RTOL, np.quantile(rel, 0.95)
-            assert rel.max() <= 2e-3, rel.max()
+            f32_cost_bar(env, H, rel, "K=%d" % K)
             # plan: conditioning bound eps32 * max|S| / lam
             tol = 6e-8 * float(np.max(np.abs(S_ref))) / lam * 4 + 1e-5
             np.testing.assert_allclose(Unew[0], U_ref, atol=tol, rtol=0)
@@ -143,24 +174,57 @@ def test_mppi_vs_oracle_tensor_noise(env, dtype):
         s.close()
 
 
-@pytest.mark.parametrize("env,H,lanes", [("pendulum", 50, 2), ("acrobot", 100, 1), ("acrobot", 100, 2)])
-def test_mppi_mufu_trig_flavour_meets_the_float32_bar(env, H, lanes):
-    """fast_math = 1 (MUFU.SIN/COS instead of the polynomial sincos) is what bench.py quotes for Pendulum and Acrobot.
-    It is held to a bar at least as strict as the accurate flavour's (test_mppi_vs_oracle_tensor_noise): per-sample
-    costs within rel 1e-5 of the float64 oracle at the 99th percentile on the identical noise tensor at the bench
-    horizon, and the chaotic tail (a handful of samples out of 8192, which ANY float32 evaluation has) bounded."""
-    K, lam = 8192, 0.5
-    x, U, eps = _rand_case(env, K, H, seed=17)
+@pytest.mark.parametrize("env,H,K,seed", [("pendulum", 50, 8192, 17), ("pendulum", 50, 65536, 3), ("acrobot", 50, 8192, 17),
+                                          ("acrobot", 100, 8192, 17), ("acrobot", 100, 65536, 3)])
+@pytest.mark.parametrize("fast_math,lanes", [(0, 2), (1, 1), (1, 2)])
+def test_mppi_float32_flavours_meet_the_same_bar(env, H, K, seed, fast_math, lanes):
+    """The float32 flavours bench.py and the agents use — polynomial sincos (default) and MUFU.SIN/COS (fast_math = 1,
+    bench.py's choice for Pendulum and Acrobot), one or two samples per thread — against the float64 oracle on the
+    identical noise tensor at the BASELINE horizons, all held to the one bar of the module docstring: every sample
+    within 1e-5 where that is reachable in float32 (Pendulum; Acrobot to H = 50), the stated quantile at H = 100."""
+    lam = 0.5
+    x, U, eps = _rand_case(env, K, H, seed=seed)
     S_ref, U_ref, _ = orc.mppi_solve(orc.model(env), x, U, eps, lam, 1.0, nthreads=0)
-    s = _solver("MPPI", env, K, H, dtype="f32", lam=lam, sigma=1.0, fast_math=True, lanes=lanes)
+    s = _solver("MPPI", env, K, H, dtype="f32", lam=lam, sigma=1.0, fast_math=fast_math, lanes=lanes)
     s.set_noise(eps)
     u0, Unew, xs, cost = s.mppi_solve(x, None, U)
     rel = np.abs(s.mppi_costs()[0] - S_ref) / np.abs(S_ref)
-    assert np.quantile(rel, 0.99) <= F32_COST_RTOL, np.quantile(rel, 0.99)
-    assert rel.max() <= 1e-4, rel.max()
+    f32_cost_bar(env, H, rel, "fast_math=%d lanes=%d" % (fast_math, lanes))
     tol = 6e-8 * float(np.max(np.abs(S_ref))) / lam * 4 + 1e-5
     np.testing.assert_allclose(Unew[0], U_ref, atol=tol, rtol=0)
     s.close()
+
+
+@pytest.mark.parametrize("env,H", [("acrobot", 100), ("acrobot", 50), ("pendulum", 50)])
+def test_mppi_mufu_flavour_is_not_worse_in_kind(env, H):
+    """Energetic regime (swing-up states, plans of amplitude 1.5): float32 follows the float64 oracle in the median
+    (<= 1e-5; measured <= 3e-7) but not in the tail, for the polynomial and the MUFU flavour alike — the MUFU flavour's
+    error quantiles stay within 3x the polynomial's (+ the 1e-7 of MUFU's absolute error), i.e. the tail is the
+    dynamics', not the flavour's.  The plan stays on its conditioning bound in both, except for the H = 100 Acrobot
+    swing-up, where the handful of diverged low-cost samples move the softmin average by up to ~6e-2 (measured, either
+    flavour): there the two flavours are only required to miss the float64 plan by a comparable amount."""
+    K, lam = 16384, 0.5
+    rng = np.random.RandomState(3)
+    x = START[env] + rng.normal(0, 0.5, orc.STATE_SIZE[env])
+    U = rng.uniform(-1.5, 1.5, H)
+    eps = rng.normal(0, 1.0, (K, H))
+    S_ref, U_ref, _ = orc.mppi_solve(orc.model(env), x, U, eps, lam, 1.0, nthreads=0)
+    q, plan_err = {}, {}
+    for fast_math in (0, 1):
+        s = _solver("MPPI", env, K, H, dtype="f32", lam=lam, sigma=1.0, fast_math=fast_math, lanes=2)
+        s.set_noise(eps)
+        u0, Unew, xs, cost = s.mppi_solve(x, None, U)
+        rel = np.abs(s.mppi_costs()[0] - S_ref) / np.abs(S_ref)
+        q[fast_math] = [np.quantile(rel, v) for v in (0.5, 0.9, 0.99)]
+        assert q[fast_math][0] <= F32_COST_RTOL, (fast_math, q[fast_math])
+        plan_err[fast_math] = float(np.abs(Unew[0] - U_ref).max())
+        if not (env == "acrobot" and H > 50):
+            tol = 6e-8 * float(np.max(np.abs(S_ref))) / lam * 4 + 1e-5
+            assert plan_err[fast_math] <= tol, (fast_math, plan_err[fast_math], tol)
+        s.close()
+    for a, b in zip(q[1], q[0]):
+        assert a <= 3 * b + 1e-7, (q[1], q[0])
+    assert plan_err[1] <= 5 * plan_err[0] + 1e-4 and plan_err[1] <= 0.5, plan_err
 
 
 @pytest.mark.parametrize("env", ENVS)
@@ -194,9 +258,12 @@ def test_mppi_stream_flavour_equals_whole_tile_flavour(env, dtype, monkeypatch):
         assert rel.max() <= 1e-9, rel.max()
         tol = _plan_tol(S_ref, lam, 1e-9)
     else:
-        # float32 over 101 chaotic CartPole steps: the 1e-5 bar holds for the median only
-        qq = 0.5 if env == "cartpole" else 0.95
-        assert np.quantile(rel, qq) <= F32_COST_RTOL, np.quantile(rel, qq)
+        # float32 over 101 chaotic CartPole steps: the 1e-5 bar holds for the median only; the other
+        # two keep the bar of their horizon class
+        if env == "cartpole":
+            assert np.quantile(rel, 0.5) <= F32_COST_RTOL, np.quantile(rel, 0.5)
+        else:
+            f32_cost_bar(env, H, rel, "stream")
         tol = 6e-8 * float(np.max(np.abs(S_ref))) / lam * 4 + 1e-5
     np.testing.assert_allclose(res["1"][1], U_ref, atol=tol, rtol=tol)
     # identical costs => identical weights; the two flavours differ only in the summation order of w * eps
@@ -253,7 +320,7 @@ def test_mppi_vs_oracle_philox_noise(env, dtype):
         tol = _plan_tol(S_ref, lam, F64_COST_RTOL)
         np.testing.assert_allclose(Unew[0], U_ref, rtol=tol, atol=tol)
     else:
-        assert np.quantile(rel, 0.95) <= F32_COST_RTOL
+        f32_cost_bar(env, H, rel, "philox")
     # the tensor path fed the materialised noise gives the same plan as the in-kernel path
     s2 = _solver("MPPI", env, K, H, dtype=dtype, lam=lam, sigma=sigma)
     s2.set_noise(eps)
@@ -445,6 +512,19 @@ def test_mppi_full_size_properties():
 
 
 # ------------------------------------------------------------------------------------------- CEM
+def _cem_f32_iteration(s, it, Rref, el_ref, env, H, n_elite):
+    """One float32 CEM iteration against the reference's: rewards on the env's float32 bar, elite set >= 99 % identical
+    and every disputed sample within 1e-4 (relative) of the elite threshold."""
+    R = s.cem_rewards(it)
+    f32_cost_bar(env, H, np.abs(R - Rref) / np.abs(Rref), "CEM iteration %d" % it, energetic=True)
+    el = np.sort(s.cem_elites(it))
+    assert np.intersect1d(el, el_ref).size >= 0.99 * n_elite - 1, "iteration %d: elite overlap" % it
+    diff = np.setxor1d(el, el_ref)
+    if diff.size:
+        thr = np.sort(Rref)[::-1][n_elite - 1]
+        assert np.all(np.abs(Rref[diff] - thr) <= 1e-4 * abs(thr)), "iteration %d: elite sets differ off-tie" % it
+
+
 @pytest.mark.parametrize("dtype", ["f64", "f32"])
 def test_cem_golden_cases(golden_dir, dtype):
     d, meta = _load(golden_dir, "cem_cases.npz")
@@ -474,9 +554,18 @@ def test_cem_golden_cases(golden_dir, dtype):
             np.testing.assert_allclose(s.cem_std(), d[p + "sd"][iters - 1][:, 0], rtol=1e-10, atol=1e-13)
             assert u0[0] == pytest.approx(float(d[p + "u0"][0]), rel=1e-12, abs=1e-13)
         else:
-            R = s.cem_rewards(0)
-            rel = np.abs(R - d[p + "rewards"][0]) / np.abs(d[p + "rewards"][0])
-            assert np.quantile(rel, 0.95) <= F32_COST_RTOL
+            # float32 rollouts: rewards on the float32 bar of the env; elite sets identical to the reference's except
+            # for samples within float32 cost error of the elite threshold.  Iterations chain (mu, std feed the next
+            # rollouts), so they are compared for as long as the elite sets stay identical (all of them, measured).
+            same = True
+            for it in range(iters):
+                _cem_f32_iteration(s, it, d[p + "rewards"][it], d[p + "elites"][it], mt["env"], H, mt["n_elite"])
+                same = np.array_equal(np.sort(s.cem_elites(it)), d[p + "elites"][it])
+                if not same:
+                    break
+            if same:
+                np.testing.assert_allclose(U, d[p + "mu"][iters - 1][:, 0], rtol=0, atol=1e-5)
+                np.testing.assert_allclose(s.cem_std(), d[p + "sd"][iters - 1][:, 0], rtol=0, atol=1e-5)
         s.close()
 
 
@@ -504,6 +593,40 @@ def test_cem_vs_oracle_config2_shape(env):
             thr = np.sort(ref["rewards"][it])[::-1][n_elite - 1]
             assert np.all(np.abs(ref["rewards"][it][diff] - thr) <= 1e-11 * abs(thr)), "elite sets differ off-tie"
     np.testing.assert_allclose(U, ref["mu"], rtol=1e-11, atol=1e-13)
+    s.close()
+
+
+@pytest.mark.parametrize("env", ENVS)
+@pytest.mark.parametrize("fast_math", [0, 1])
+def test_cem_float32_vs_oracle_config2_shape(env, fast_math):
+    """float32 CEM — the flavour bench.py's configs[1] number uses — at the config's own size (K = 4096, H = 50,
+    n_elite = 409, 5 iterations) against the float64 oracle on identical normals: per-iteration rewards on the float32
+    bar of the env, elite sets >= 99 % identical with every disputed sample within float32 cost error of the elite
+    threshold, mean and std within 1e-5 absolute (measured: overlap 100 %, mean 4e-8; profiles/r2b_parity_probe.jsonl).
+    The iterations are compared one by one although they chain (mu, std feed the next rollouts): with identical
+    elites the float64 refit is identical, so the chain stays on the oracle's."""
+    K, H, iters, n_elite = 4096, 50, 5, 409
+    rng = np.random.RandomState(11)
+    x = START[env] + rng.normal(0, 0.2, orc.STATE_SIZE[env])
+    z = rng.standard_normal((iters, K, H))
+    ref = orc.cem_solve(orc.model(env), x, np.zeros(H), z, n_elite, 1e-5, 0.2, 1.0, nthreads=0)
+    s = _solver("CEM", env, K, H, dtype="f32", sigma=1.0, max_iter=iters, n_elite=n_elite, epsilon=1e-5, alpha=0.2,
+                fast_math=fast_math)
+    s.cem_begin(x, None, np.zeros(H))
+    for it in range(iters):
+        s.cem_iterate(z[it])
+    u0, U, xs, cost = s.cem_end()
+    same = True
+    for it in range(iters):
+        _cem_f32_iteration(s, it, ref["rewards"][it], ref["elites"][it], env, H, n_elite)
+        same = np.array_equal(np.sort(s.cem_elites(it)), ref["elites"][it])
+        if not same:
+            break
+    assert same or it >= 1, "elite sets differ already in the first iteration"
+    tol = 1e-5 if same else 1e-3
+    np.testing.assert_allclose(U, ref["mu"], rtol=0, atol=tol)
+    np.testing.assert_allclose(s.cem_std(), ref["sd_hist"][-1], rtol=0, atol=tol)
+    assert u0[0] == pytest.approx(ref["u0"], abs=tol)
     s.close()
 
 

@@ -30,7 +30,7 @@ for env in ("pendulum", "cartpole", "acrobot"):
                 s.mppi_solve(x, None, U, want_traj=traj)
                 lat.append(time.perf_counter() - t)
             res[traj] = 1e3 * statistics.median(lat)
-        s.set_profiling(True)
+        s.set_profiling(True, rollout_events=True)
         s.upload_inputs(x, None, U)
         ks = []
         for _ in range(20):

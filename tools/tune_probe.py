@@ -26,7 +26,7 @@ def solver(env, K, H, **kw):
 
 
 def time_solver(s, env, H, n=8, flush=True):
-    s.set_profiling(True)
+    s.set_profiling(True, rollout_events=True)
     s.upload_inputs(START[env] + 0.01, None, np.zeros(H))
     for _ in range(3):
         s.solve_enqueue()

@@ -57,7 +57,7 @@ def timing(K=1 << 20):
                     s = solver(env, K, H, dtype="f32", noise=noise, lam=0.5, sigma=1.0, lanes=lanes, fast_math=fast)
                     if noise == "tensor":
                         s.fill_noise()
-                    s.set_profiling(True)
+                    s.set_profiling(True, rollout_events=True)
                     s.upload_inputs(START[env] + 0.01, None, np.zeros(H))
                     for _ in range(3):
                         s.solve_enqueue()
