@@ -221,15 +221,24 @@ def time_device(s, steps, warmup, dist, flush, want_traj=False):
     untimed L2 flush between solves every solve has its own pair of CUDA events (the flush sits between two pairs) and
     the step time is the sum of the K intervals; without a flush ONE pair brackets all K solves.  Max over ranks.
     For MPPI the solve is ONE kernel, so time / K is also the solve kernel's duration (launch gap included).
-    Returns (total ms, launches in the timed region, wall seconds of the bracket)."""
+    K sharded over several GPUs: one untimed solve goes first after the barrier — its in-kernel exchange lines the
+    ranks' device timelines up (a host barrier leaves them tens of microseconds apart).
+    Returns (total ms, launches in the timed region, wall seconds of the bracket, per-solve ms of this rank or None)."""
     s.time_solves(max(1, warmup), want_traj=want_traj, flush_l2=flush)
     s.sync()
     dist.barrier()
     l0 = s.launch_count
     t_wall = time.perf_counter()
+    each = None
+    extra_launches = 0
     if flush:
-        total = sum(s.time_solves(steps, want_traj=want_traj, flush_l2=True))
+        each = s.time_solves(steps, want_traj=want_traj, flush_l2=True)
+        total = sum(each)
+        extra_launches = steps + (2 if dist.world > 1 else 0)  # the flushes (+ the untimed aligning solve and its flush)
     else:
+        if dist.world > 1:
+            s.solve_enqueue(want_traj=want_traj)  # untimed: its in-kernel exchange aligns the ranks' device timelines
+            extra_launches = 1
         s.timer_start()
         for _ in range(steps):
             s.solve_enqueue(want_traj=want_traj)
@@ -237,8 +246,8 @@ def time_device(s, steps, warmup, dist, flush, want_traj=False):
     s.sync()
     dist.barrier()
     wall = time.perf_counter() - t_wall
-    launches = s.launch_count - l0 - (steps if flush else 0)
-    return dist.max(total), launches, wall
+    launches = s.launch_count - l0 - extra_launches
+    return dist.max(total), launches, wall, each
 
 
 def time_e2e(s, x, U, steps, warmup, dist):
@@ -312,7 +321,7 @@ def run_mppi_workload(capi, dist, name, steps, warmup, dtype="f32", noise="tenso
     s.upload_inputs(x, None, U)
     clocks = ClockSampler(dist.local_rank)
     clocks.start()
-    total_ms, launches, wall = time_device(s, steps, warmup, dist, flush)
+    total_ms, launches, wall, each = time_device(s, steps, warmup, dist, flush)
     clk = clocks.stop()
     steps_total = float(K) * H * steps
     value = steps_total / (total_ms * 1e-3)
@@ -323,6 +332,7 @@ def run_mppi_workload(capi, dist, name, steps, warmup, dtype="f32", noise="tenso
         trace_us = None
     out = {"value": value, "ms_per_step": total_ms / steps, "clocks": clk, "gpu_launches": launches,
            "wall_s_timed_loop": wall, "solve_phases_us": trace_us, "K_per_gpu": s.K_local,
+           "step_ms_min_median_max": [min(each), statistics.median(each), max(each)] if each else None,
            "lanes": s.lanes, "fast_math": int(s.fast_math), "flush": flush, "shard_bytes": shard_bytes,
            "geometry": {k: s.geometry[k] for k in ("grid", "block", "smem", "stages", "stream_rows")}}
     if with_e2e:
@@ -661,6 +671,7 @@ def run_ours(args, dist):
         "clocks": r["clocks"], "gpu_launches": r["gpu_launches"], "e2e": r["e2e"],
         "roofline": r["roofline"], "roofline_other": r["roofline_other"], "wall_s_timed_loop": r["wall_s_timed_loop"],
         "solve_phases_us": r["solve_phases_us"], "geometry": r["geometry"],
+        "step_ms_min_median_max": r["step_ms_min_median_max"],
     }
     for k in ("parity", "sharded_vs_single"):
         if k in r:
@@ -669,8 +680,8 @@ def run_ours(args, dist):
         extra = {}
 
         def brief(w):
-            keep = {k: w[k] for k in ("value", "ms_per_step", "e2e", "solve_phases_us", "parity", "sharded_vs_single",
-                                      "K_per_gpu", "lanes", "fast_math") if k in w}
+            keep = {k: w[k] for k in ("value", "ms_per_step", "step_ms_min_median_max", "e2e", "solve_phases_us", "parity",
+                                      "sharded_vs_single", "K_per_gpu", "lanes", "fast_math") if k in w}
             keep["roofline"] = {k: w["roofline"][k] for k in ("bound", "achieved", "peak", "unit", "frac", "kernel_ms")}
             keep["roofline_other"] = {k: w["roofline_other"][k] for k in ("bound", "achieved", "peak", "unit", "frac")}
             return keep

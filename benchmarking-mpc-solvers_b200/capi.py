@@ -476,8 +476,12 @@ class Solver:
         """Phase stamps (ns) of the last solve's finalising block, relative to the kernel start (profiling on)."""
         buf = (C.c_uint64 * 16)()
         self._ck(self.L.mpc_get_trace(self._h, buf))
-        names = ["start", "tiles_done", "ticket", "merged", "published", "peers_in", "merged2", "applied", "end",
-                 "recs_in_smem", "rec_written", "fenced", "first_warp_out", "last_warp_out", "recs_stored"]
+        if self.is_mppi:
+            names = ["start", "tiles_done", "ticket", "merged", "published", "peers_in", "merged2", "applied", "end",
+                     "recs_in_smem", "rec_written", "fenced", "first_warp_out", "last_warp_out", "recs_stored"]
+        else:  # single-launch CEM: block 0's phases of iteration 1, then the tail
+            names = ["start", "it1_begin", "it1_rollout_done", "it1_keys_barrier", "it1_threshold", "it1_partial_sums",
+                     "it1_sums_barrier", "it1_updated", "iterations_done", "end", "it1_samples_sorted", "it1_keys_located"]
         t0 = buf[0]
         return {n: (int(buf[i]) - int(t0)) if buf[i] else None for i, n in enumerate(names)}
 

@@ -102,12 +102,20 @@ struct mpc_handle {
     int cem_iter = 0;
     bool cem_open = false;
     int cem_n_cand = 0;           // candidates per rank and iteration (multi-GPU)
+    // the whole solve as one cooperative launch (cem_fused.cuh): single GPU, Philox noise
+    bool cem_fused = false;
+    bool cem_coop = true;         // MPC_B200_CEM_COOP=0: a plain launch instead of cudaLaunchCooperativeKernel
+    int cem_grid = 0, cem_spb = 0;
+    double *d_cem_slots = nullptr;
+    int *d_cem_stage = nullptr, *d_cem_hist = nullptr, *d_cem_tie = nullptr;
+    unsigned *d_cem_bar = nullptr;
     int cem_z_stride = 0;         // row stride of the standard-normal tensor
     // host (pinned)
     double *h_in = nullptr, *h_out = nullptr;
     unsigned long long *h_flag = nullptr;  // pinned completion word the solve kernel raises (host-flag path)
     unsigned long long host_epoch = 0;
     bool host_flag_on = true;              // MPC_B200_HOSTFLAG=0 selects the D2H copy + stream synchronise instead
+    bool inline_inputs = true;             // MPC_B200_INLINE=0: always stage state / plan through the pinned buffer
     size_t in_elems = 0, out_elems = 0, out_stride = 0;
     float *d_flush = nullptr;
     double *d_episode = nullptr;  // histories of mpc_episode_run
@@ -278,6 +286,7 @@ static MppiBuffers mppi_bufs(const mpc_handle *h) {
     b.out = h->d_out;
     b.done_count = h->d_done;
     b.peer_recs = h->peer_recs;
+    b.inl = nullptr;
     return b;
 }
 
@@ -321,6 +330,7 @@ static CemBuffers cem_bufs(const mpc_handle *h) {
     b.out = h->d_out;
     b.peer_recs = h->peer_recs;
     b.err_word = h->d_out + (size_t)h->g.B * h->out_stride + 1;
+    b.inl = nullptr;
     return b;
 }
 
@@ -382,6 +392,11 @@ int mpc_destroy(mpc_handle *h) {
     cudaFree(h->d_keys);
     cudaFree(h->d_elite);
     cudaFree(h->d_sel);
+    cudaFree(h->d_cem_slots);
+    cudaFree(h->d_cem_stage);
+    cudaFree(h->d_cem_hist);
+    cudaFree(h->d_cem_tie);
+    cudaFree(h->d_cem_bar);
     cudaFree(h->d_flush);
     cudaFree(h->d_episode);
     if (h->h_in) cudaFreeHost(h->h_in);
@@ -622,6 +637,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     CUC(cudaMallocHost(&h->h_flag, 64));
     *h->h_flag = 0ull;
     if (const char *e = getenv("MPC_B200_HOSTFLAG")) h->host_flag_on = atoi(e) != 0;
+    if (const char *e = getenv("MPC_B200_INLINE")) h->inline_inputs = atoi(e) != 0;
     memset(h->h_in, 0, h->in_elems * sizeof(double));
     h->g_zero_on_device = true;
     // CEM over several GPUs: elites are global, so the standard normals of an iteration (TENSOR noise) are resident in
@@ -661,6 +677,33 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         CUC(cudaMemsetAsync(h->d_sel, 0, 8 * sizeof(int), h->stream));
         CUC(cudaMemsetAsync(h->d_R, 0, (size_t)cfg->max_iter * g.Kpad * sizeof(double), h->stream));
         CUC(cudaMemsetAsync(h->d_elite, 0, (size_t)cfg->max_iter * cfg->n_elite * sizeof(int), h->stream));
+        // One persistent cooperative launch per solve (cem_fused.cuh) when the normals are generated in the kernel and
+        // K is not sharded: blocks own contiguous sample ranges, at most one block per SM.  MPC_B200_CEM_FUSED=0 keeps
+        // the per-iteration kernels (profiling / comparison).
+        h->cem_fused = cfg->noise == MPC_NOISE_PHILOX && cfg->world == 1 && cfg->H <= CEM_FUSED_MAX_H;
+        if (const char *e = getenv("MPC_B200_CEM_FUSED")) h->cem_fused = h->cem_fused && atoi(e) != 0;
+        if (const char *e = getenv("MPC_B200_CEM_COOP")) h->cem_coop = atoi(e) != 0;
+        if (h->cem_fused) {
+            int coop = 0;
+            CUC(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, cfg->device));
+            if (!coop) h->cem_fused = false;
+        }
+        if (h->cem_fused) {
+            int grid = (g.K_local + 31) / 32;
+            if (grid > h->num_sms) grid = h->num_sms;
+            int spb = ((g.K_local + grid - 1) / grid + 31) / 32 * 32;
+            grid = (g.K_local + spb - 1) / spb;
+            h->cem_grid = grid;
+            h->cem_spb = spb;
+            CUC(cudaMalloc(&h->d_cem_slots, (size_t)grid * (2 + 2 * g.H) * sizeof(double)));
+            CUC(cudaMalloc(&h->d_cem_stage, (size_t)g.Kpad * sizeof(int)));
+            CUC(cudaMalloc(&h->d_cem_hist, (size_t)cfg->max_iter * 8 * 256 * sizeof(int)));
+            CUC(cudaMalloc(&h->d_cem_tie, (size_t)grid * sizeof(int)));
+            CUC(cudaMalloc(&h->d_trace, 16 * sizeof(unsigned long long)));
+            CUC(cudaMemsetAsync(h->d_trace, 0, 16 * sizeof(unsigned long long), h->stream));
+            CUC(cudaMalloc(&h->d_cem_bar, 2 * sizeof(unsigned)));
+            CUC(cudaMemsetAsync(h->d_cem_bar, 0, 2 * sizeof(unsigned), h->stream));
+        }
     }
     CUC(cudaStreamSynchronize(h->stream));
 #undef CUC
@@ -776,6 +819,20 @@ static int stage_inputs(mpc_handle *h, const double *x, const double *g_z, const
     return MPC_OK;
 }
 
+// Batch-1 host calls with the usual zero goal: state and plan travel as kernel parameters (InlineInputs) and no copy is
+// enqueued at all.  Returns false when the call does not qualify (the caller stages through the pinned buffer then).
+static bool stage_inline(mpc_handle *h, const double *x, const double *g_z, const double *U_in, InlineInputs *inl) {
+    const Geometry &g = h->g;
+    if (!h->inline_inputs || g.B != 1 || g_z || !h->g_zero_on_device || !x || g.H > INLINE_MAX_H || h->ns > 4) return false;
+    inl->on = 1;
+    for (int i = 0; i < h->ns; ++i) inl->x0[i] = x[i];
+    if (U_in) {
+        inl->on |= 2;
+        memcpy(inl->U, U_in, (size_t)g.H * sizeof(double));
+    }
+    return true;
+}
+
 // A peer never delivered within the bounded wait: report MPC_ENCCL once and clear the device-side error words, so that
 // the handle is usable again after the caller has dealt with it.  The resident plan U was updated from a partial
 // merge by the timed-out kernel: the caller must pass U_in on its next solve (every reference-style caller does).
@@ -850,7 +907,7 @@ static int await_host_flag(mpc_handle *h, int want_traj, double *u0, double *U_o
 }
 
 // ---------------------------------------------------------------------------------------------- MPPI
-static int mppi_enqueue(mpc_handle *h, int want_traj, bool host_flag = false) {
+static int mppi_enqueue(mpc_handle *h, int want_traj, bool host_flag = false, const InlineInputs *inl = nullptr) {
     if (h->cfg.agent != MPC_AGENT_MPPI) return fail(h, MPC_ESTATE, "not an MPPI handle");
     if (!h->noise_ready) return fail(h, MPC_ESTATE, "noise tensor not set: call mpc_set_noise or mpc_fill_noise first");
     if (h->cfg.world > 1 && !h->comm && !h->p2p_ready)
@@ -862,7 +919,8 @@ static int mppi_enqueue(mpc_handle *h, int want_traj, bool host_flag = false) {
         a.host_flag = h->h_flag;
         a.host_epoch = ++h->host_epoch;
     }
-    const MppiBuffers b = mppi_bufs(h);
+    MppiBuffers b = mppi_bufs(h);
+    b.inl = inl;
     if (h->rollout_events) CU(h, cudaEventRecord(h->evr0, h->stream));
     CU(h, launch_mppi_solve(h->cfg.dtype, h->cfg.noise, h->g.variant, h->ep, a, b, h->stream));
     if (h->rollout_events) CU(h, cudaEventRecord(h->evr1, h->stream));
@@ -884,12 +942,16 @@ int mpc_mppi_solve(mpc_handle *h, const double *x, const double *g_z, const doub
     if (!h) return MPC_EINVAL;
     CU(h, cudaSetDevice(h->cfg.device));
     const int want_traj = (xs_out || cost_out) ? 1 : 0;
-    int rc = stage_inputs(h, x, g_z, U_in);
+    InlineInputs inl;
+    // (not on the NCCL transport: its second kernel applies the update to the plan in global memory)
+    const bool inlined = h->g.solves_per_block == 0 && (h->cfg.world == 1 || h->p2p_ready) &&
+                         stage_inline(h, x, g_z, U_in, &inl);
+    int rc = inlined ? MPC_OK : stage_inputs(h, x, g_z, U_in);
     if (rc) return rc;
     // host-flag completion: batch = 1 and the tail that applies the update runs inside the solve kernel (one GPU,
     // or the in-kernel peer exchange) — the kernel writes the outputs into pinned host memory and raises a flag
     const bool use_flag = h->host_flag_on && h->g.B == 1 && (h->cfg.world == 1 || h->p2p_ready);
-    rc = mppi_enqueue(h, want_traj, use_flag);
+    rc = mppi_enqueue(h, want_traj, use_flag, inlined ? &inl : nullptr);
     if (rc) return rc;
     if (!use_flag) return fetch_outputs(h, want_traj, u0, U_out, xs_out, cost_out);
     return await_host_flag(h, want_traj, u0, U_out, xs_out, cost_out);
@@ -953,6 +1015,70 @@ static int cem_enqueue_iter(mpc_handle *h, int iter) {
     CU(h, launch_cem_select(a, b, h->stream));
     CU(h, launch_cem_refit(h->cfg.dtype, h->cfg.noise, a, b, h->stream));
     h->launches += 3;
+    return MPC_OK;
+}
+
+// The whole solve as one cooperative launch (cem_fused.cuh).  host_flag: the kernel also writes the outputs into the
+// pinned host buffer and raises the completion word (batch-1 host call: no D2H copy, no stream synchronise).
+static int cem_fused_enqueue(mpc_handle *h, int want_traj, bool host_flag, const InlineInputs *inl = nullptr) {
+    CemFusedArgs fa;
+    memset(&fa, 0, sizeof fa);
+    fa.a = cem_args(h, 0, want_traj);
+    fa.max_iter = h->cfg.max_iter;
+    fa.spb = h->cem_spb;
+    fa.all_pairs = (h->g.K_local <= CEM_FUSED_ALLPAIRS_K && h->cem_spb == 32) ? 1 : 0;
+    fa.cached = (h->cem_spb == 32 && (size_t)h->g.H * 32 * (h->cfg.dtype == MPC_F32 ? 4 : 8) <= 64 * 1024) ? 1 : 0;
+    fa.noise_draw0 = (uint32_t)((h->solves * (uint64_t)h->cfg.max_iter) & 0xffffffffu);
+    fa.trace = h->profiling ? h->d_trace : nullptr;
+    if (host_flag) {
+        fa.host_out = h->h_out;
+        fa.host_flag = h->h_flag;
+        fa.host_epoch = ++h->host_epoch;
+    }
+    CemFusedScratch sc;
+    sc.slots = h->d_cem_slots;
+    sc.stage = h->d_cem_stage;
+    sc.hist = h->d_cem_hist;
+    sc.tie_cnt = h->d_cem_tie;
+    sc.bar = h->d_cem_bar;
+    CemBuffers cb = cem_bufs(h);
+    cb.inl = inl;
+    CU(h, launch_cem_fused(h->cfg.dtype, h->g.variant, h->ep, fa, cb, sc, h->cem_grid, h->cem_coop ? 1 : 0, h->stream));
+    h->launches++;
+    h->solves++;
+    h->cem_open = false;
+    return MPC_OK;
+}
+
+static int cem_await_host_flag(mpc_handle *h, int want_traj, double *u0, double *U_out, double *xs_out, double *cost_out,
+                               int32_t *iters_out) {
+    volatile unsigned long long *flag = h->h_flag;
+    const unsigned long long want = h->host_epoch;
+    unsigned spins = 0;
+    while (*flag != want) {
+        if ((++spins & 0x3fffu) == 0) {
+            cudaError_t q = cudaStreamQuery(h->stream);
+            if (q == cudaSuccess) {
+                if (*flag == want) break;
+                return fail(h, MPC_ECUDA, "CEM solve kernel finished without raising its completion flag");
+            }
+            if (q != cudaErrorNotReady) return fail(h, MPC_ECUDA, "CEM solve kernel: %s", cudaGetErrorString(q));
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+    }
+    __atomic_thread_fence(__ATOMIC_ACQUIRE);
+    const Geometry &g = h->g;
+    const double *o = h->h_out;
+    if (u0) u0[0] = o[0];
+    if (U_out) memcpy(U_out, o + 1, g.H * sizeof(double));
+    if (want_traj) {
+        if (cost_out) cost_out[0] = o[1 + g.H];
+        if (xs_out) memcpy(xs_out, o + 2 + g.H, (size_t)(g.H + 1) * h->ns * sizeof(double));
+    }
+    h->last_iters = (int)o[h->out_stride];
+    if (iters_out) *iters_out = h->last_iters;
     return MPC_OK;
 }
 
@@ -1033,6 +1159,29 @@ int mpc_cem_solve(mpc_handle *h, const double *x, const double *g_z, const doubl
     if (h->cfg.agent != MPC_AGENT_CEM) return fail(h, MPC_ESTATE, "not a CEM handle");
     if (h->cfg.noise != MPC_NOISE_PHILOX)
         return fail(h, MPC_ESTATE, "mpc_cem_solve needs PHILOX noise; use begin/iterate/end with host noise");
+    if (h->cem_fused) {
+        CU(h, cudaSetDevice(h->cfg.device));
+        const int want_traj = (xs_out || cost_out) ? 1 : 0;
+        InlineInputs inl;
+        const bool inlined = stage_inline(h, x, g_z, U_in, &inl);
+        int rc = inlined ? MPC_OK : stage_inputs(h, x, g_z, U_in);
+        if (rc) return rc;
+        rc = cem_fused_enqueue(h, want_traj, h->host_flag_on, inlined ? &inl : nullptr);
+        if (rc) return rc;
+        if (h->host_flag_on) return cem_await_host_flag(h, want_traj, u0, U_out, xs_out, cost_out, iters_out);
+        CU(h, cudaMemcpyAsync(h->h_out, h->d_out, h->out_elems * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+        const double *o = h->h_out;
+        if (u0) u0[0] = o[0];
+        if (U_out) memcpy(U_out, o + 1, h->g.H * sizeof(double));
+        if (want_traj) {
+            if (cost_out) cost_out[0] = o[1 + h->g.H];
+            if (xs_out) memcpy(xs_out, o + 2 + h->g.H, (size_t)(h->g.H + 1) * h->ns * sizeof(double));
+        }
+        h->last_iters = (int)o[h->out_stride];
+        if (iters_out) *iters_out = h->last_iters;
+        return MPC_OK;
+    }
     int rc = mpc_cem_begin(h, x, g_z, U_in);
     if (rc) return rc;
     for (int it = 0; it < h->cfg.max_iter; ++it) {  // later iterations return at once when the done flag is set
@@ -1146,6 +1295,7 @@ int mpc_episode_run(mpc_handle *h, const double *x0, const double *U_in, const m
     // one solve of either agent, enqueued only
     auto enqueue_solve = [&](int want_traj) -> int {
         if (mppi) return mppi_enqueue(h, want_traj);
+        if (h->cem_fused) return cem_fused_enqueue(h, want_traj, false);
         CU(h, launch_cem_reset(cem_args(h, 0, 0), cem_bufs(h), h->stream));
         h->launches++;
         for (int it = 0; it < h->cfg.max_iter; ++it) {
@@ -1370,6 +1520,7 @@ extern "C" int mpc_flush_l2(mpc_handle *h);
 static int solve_enqueue(mpc_handle *h, int want_traj) {
     if (h->cfg.agent == MPC_AGENT_MPPI) return mppi_enqueue(h, want_traj);
     if (h->cfg.noise != MPC_NOISE_PHILOX) return fail(h, MPC_ESTATE, "device-resident CEM solve needs PHILOX noise");
+    if (h->cem_fused) return cem_fused_enqueue(h, want_traj, false);
     CU(h, launch_cem_reset(cem_args(h, 0, 0), cem_bufs(h), h->stream));
     h->launches++;
     for (int it = 0; it < h->cfg.max_iter; ++it) {
@@ -1405,6 +1556,14 @@ int mpc_time_solves(mpc_handle *h, int32_t n, int32_t want_traj, int32_t flush_l
     // every solve between its own pair of events, nothing but the (untimed) L2 flush between two pairs, and no host
     // synchronisation until all n are enqueued: the device queue never runs dry, so an event pair brackets the solve's
     // own launches and not the host's launch latency
+    if (h->cfg.world > 1) {
+        // K sharded over several GPUs: one untimed solve first.  Its in-kernel exchange lines the ranks' device
+        // timelines up (a host barrier leaves them tens of microseconds apart, which the first timed solve of the
+        // early ranks would otherwise spend waiting for the late ones).
+        int rc = solve_enqueue(h, want_traj ? 1 : 0);
+        if (rc) return rc;
+        if (flush_l2 && (rc = mpc_flush_l2(h))) return rc;
+    }
     for (int i = 0; i < n; ++i) {
         CU(h, cudaEventRecord(h->ev_pool[2 * i], h->stream));
         int rc = solve_enqueue(h, want_traj ? 1 : 0);
@@ -1461,7 +1620,7 @@ int mpc_get_rollout_ms(mpc_handle *h, float *ms_out) {
 
 int mpc_get_trace(mpc_handle *h, uint64_t out[16]) {
     if (!h || !out) return MPC_EINVAL;
-    if (!h->d_trace) return fail(h, MPC_ESTATE, "no trace buffer (MPPI handles only)");
+    if (!h->d_trace) return fail(h, MPC_ESTATE, "no trace buffer (MPPI handles and single-launch CEM handles only)");
     CU(h, cudaSetDevice(h->cfg.device));
     CU(h, cudaMemcpyAsync(out, h->d_trace, 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));

@@ -265,6 +265,8 @@ DECL_0(cudaError_t, launch_transpose_noise, const double *, void *, int, int, in
 DECL_0(cudaError_t, launch_philox_fill, void *, int, int, int, int, double, uint64_t, uint32_t, cudaStream_t)
 DECL_E(cudaError_t, launch_cem_rollout, int, int, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
 DECL_0(cudaError_t, launch_cem_refit, int, const CemArgs &, const CemBuffers &, cudaStream_t)
+DECL_E(cudaError_t, launch_cem_fused, int, const EnvParamsHost &, const CemFusedArgs &, const CemBuffers &,
+       const CemFusedScratch &, int, int, cudaStream_t)
 DECL_E(cudaError_t, launch_cem_finish, const EnvParamsHost &, const CemArgs &, const CemBuffers &, cudaStream_t)
 DECL_E(cudaError_t, launch_simulate, const EnvParamsHost &, int, double, double, int, const double *, const double *,
        const double *, double *, double *, cudaStream_t)
@@ -324,6 +326,10 @@ cudaError_t launch_philox_blocks(double *dst, int K_local, int k_begin, int n_bl
 cudaError_t launch_cem_rollout(int dtype, int noise, int variant, const EnvParamsHost &ep, const CemArgs &a,
                                const CemBuffers &b, cudaStream_t s) {
     return BY_DTYPE_ENV(launch_cem_rollout, ep.env, noise, variant, ep, a, b, s);
+}
+cudaError_t launch_cem_fused(int dtype, int variant, const EnvParamsHost &ep, const CemFusedArgs &fa, const CemBuffers &b,
+                             const CemFusedScratch &sc, int grid, int coop, cudaStream_t s) {
+    return BY_DTYPE_ENV(launch_cem_fused, ep.env, variant, ep, fa, b, sc, grid, coop, s);
 }
 cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
     PeerTable pt;

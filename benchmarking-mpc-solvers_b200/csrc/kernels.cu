@@ -332,6 +332,10 @@ __global__ void cem_finish_kernel(const CemArgs a, const EnvConst<typename Env::
     }
 }
 
+}  // namespace mpc
+#include "cem_fused.cuh"
+namespace mpc {
+
 // ================================================================================================ small kernels
 template <class Env>
 __global__ void simulate_kernel(const EnvConst<typename Env::Vec> ec, int H, double lo, double hi, int do_clip,
@@ -551,8 +555,13 @@ static cudaError_t mppi_solve_go(const MppiArgs &a, const EnvParamsHost &ep, con
     memset(&pt, 0, sizeof pt);
     if (a.p2p)
         for (int r = 0; r < a.world && r < MAX_WORLD; ++r) pt.recs[r] = b.peer_recs[r];
+    InlineInputs inl;
+    if (b.inl)
+        inl = *b.inl;
+    else
+        inl.on = 0;
     kern<<<a.g.grid, a.g.warps * 32, smem, s>>>(a, make_env<V>(ep), map, (const typename Env::S *)b.noise, b.x0, b.g_z, b.U,
-                                                 b.S, b.part, b.rank_part, b.out, b.done_count, pt);
+                                                 b.S, b.part, b.rank_part, b.out, b.done_count, pt, inl);
     return cudaGetLastError();
 }
 
@@ -695,6 +704,65 @@ cudaError_t FN(launch_cem_rollout)(int noise, int variant, const EnvParamsHost &
                                                                          b.mu, b.sd, b.R, b.keys, b.sel);
     });
     return cudaGetLastError();
+}
+
+cudaError_t FN(launch_cem_fused)(int variant, const EnvParamsHost &ep, const CemFusedArgs &fa, const CemBuffers &b,
+                                 const CemFusedScratch &sc, int grid, int coop, cudaStream_t s) {
+    cudaError_t e = cudaErrorInvalidValue;
+    with_scalar_env(unit_trig(variant) != 0, [&](auto env) {
+        typedef decltype(env) E;
+        typedef typename E::Vec V;
+        auto kern = cem_solve_kernel<E>;
+        const size_t smem = cem_fused_smem<R_>(fa.a.g.H, fa.a.g.ns, fa.cached != 0);
+        static size_t smem_set[64] = {0};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (smem > 48 * 1024 && smem > smem_set[dev & 63]) {
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return;
+            smem_set[dev & 63] = smem;
+        }
+        // Every block must be resident (they meet at grid barriers).  The grid is at most one block per SM and a block
+        // fits an empty SM by construction; that is checked against the occupancy calculator once per device and
+        // shape.  `coop` (the default) launches with cudaLaunchCooperativeKernel, which fails instead of deadlocking
+        // if the device cannot hold the grid; MPC_B200_CEM_COOP=0 selects a plain launch (measured: no difference in
+        // host time, 118 vs 120 us p50 for BASELINE configs[1]).
+        static size_t checked_smem[64] = {0};
+        static int per_sm[64] = {0}, sms[64] = {0};
+        if (per_sm[dev & 63] == 0 || checked_smem[dev & 63] != smem) {
+            int n = 0, nsm = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, CEMF_THREADS, smem);
+            if (e != cudaSuccess) return;
+            cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+            per_sm[dev & 63] = n;
+            sms[dev & 63] = nsm;
+            checked_smem[dev & 63] = smem;
+        }
+        if (per_sm[dev & 63] < 1 || grid > per_sm[dev & 63] * sms[dev & 63]) {
+            e = cudaErrorCooperativeLaunchTooLarge;
+            return;
+        }
+        EnvConst<V> ecv = make_env<V>(ep);
+        InlineInputs inl;
+        if (b.inl)
+            inl = *b.inl;
+        else
+            inl.on = 0;
+        if (!coop) {
+            kern<<<grid, CEMF_THREADS, smem, s>>>(fa, ecv, b.x0, b.g_z, b.mu, b.sd, b.R, b.keys, b.elite_idx, b.sel, b.out, sc,
+                                                  inl);
+            e = cudaGetLastError();
+            return;
+        }
+        const double *x0 = b.x0, *g_z = b.g_z;
+        double *mu = b.mu, *sd = b.sd, *R = b.R, *out = b.out;
+        unsigned long long *keys = b.keys;
+        int *elite = b.elite_idx, *sel = b.sel;
+        void *args[] = {(void *)&fa, (void *)&ecv, (void *)&x0, (void *)&g_z, (void *)&mu, (void *)&sd, (void *)&R,
+                        (void *)&keys, (void *)&elite, (void *)&sel, (void *)&out, (void *)&sc, (void *)&inl};
+        e = cudaLaunchCooperativeKernel((void *)kern, dim3(grid), dim3(CEMF_THREADS), args, smem, s);
+    });
+    return e;
 }
 
 cudaError_t FN(launch_cem_finish)(const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {

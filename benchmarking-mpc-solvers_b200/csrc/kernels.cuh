@@ -47,6 +47,15 @@ struct Geometry {
     size_t smem_rollout;  // dynamic shared memory of the solve kernel
 };
 
+// State and plan of a batch-1 host call passed as kernel parameters (constant bank) instead of through a host-to-device
+// copy that the launch would have to wait for: ~5 us off every predict_action-sized call.
+constexpr int INLINE_MAX_H = 128;
+struct InlineInputs {
+    int on;                    // bit 0: x0 is valid, bit 1: U is valid
+    double x0[4];
+    double U[INLINE_MAX_H];
+};
+
 struct MppiArgs {
     Geometry g;
     double neg_inv_lam;   // -(1/lam)                       mppi.py:60
@@ -92,6 +101,27 @@ struct CemArgs {
     uint32_t noise_draw;  // solve counter * max_iter + iteration
 };
 
+// CEM as one persistent cooperative launch (cem_fused.cuh): single GPU, Philox noise
+struct CemFusedArgs {
+    CemArgs a;            // iter unused
+    int max_iter;
+    int spb;              // samples per block (multiple of 32)
+    int all_pairs;        // K <= CEM_FUSED_ALLPAIRS_K: rank by counting, no radix passes
+    int cached;           // one warp's worth of samples per block (spb = 32): the samples live in shared memory
+    uint32_t noise_draw0; // model-noise draw of iteration 0: solve counter * max_iter
+    unsigned long long *trace;  // null, or 16 words: %globaltimer stamps of block 0 (mpc_get_trace)
+    double *host_out;     // null, or mapped pinned memory receiving the outputs + completion flag (batch-1 host call)
+    unsigned long long *host_flag;
+    unsigned long long host_epoch;
+};
+struct CemFusedScratch {
+    double *slots;        // [grid][2 + 2 H]: elite count, -, sum (x - c) [H], sum (x - c)^2 [H]
+    int *stage;           // [Kpad] a block's elite indices before their global offset is known
+    int *hist;            // [max_iter][8][256] radix histograms (zeroed by the kernel)
+    int *tie_cnt;         // [grid] keys equal to the threshold key per block (exact-tie split, rare)
+    unsigned *bar;        // [2] grid barrier: arrival count, generation (persist across launches)
+};
+
 struct MppiBuffers {
     const void *noise;     // R [Bn][H][Kpad]
     const void *noise_map; // host copy of the CUtensorMap over `noise` (rank 3: Kpad, H, Bn; box wt x H x 1)
@@ -104,6 +134,7 @@ struct MppiBuffers {
     double *out;           // [B][out_stride]: u0, U[H], cost, xs[(H+1)*ns]
     int *done_count;       // [B][1 + n_groups] arrival tickets of the solve kernel's blocks (self-cleaning)
     double *const *peer_recs;  // host array [world] of the ranks' exchange buffers (p2p), else null
+    const InlineInputs *inl;   // host pointer or null: state / plan of this solve as kernel parameters
 };
 
 struct CemBuffers {
@@ -119,6 +150,7 @@ struct CemBuffers {
     double *out;           // u0, U[H], cost, xs
     double *const *peer_recs;  // host array [world] of the ranks' exchange buffers (world > 1)
     double *err_word;      // set when a peer did not deliver in time
+    const InlineInputs *inl;   // single-launch solve only: host pointer or null
 };
 
 // closed-loop control step on the device (episode_step_kernel, kernels.cu)
@@ -162,6 +194,12 @@ cudaError_t launch_cem_select(const CemArgs &a, const CemBuffers &b, cudaStream_
 cudaError_t launch_cem_refit(int dtype, int noise, const CemArgs &a, const CemBuffers &b, cudaStream_t s);
 cudaError_t launch_cem_finish(int dtype, const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s);
 cudaError_t launch_cem_reset(const CemArgs &a, const CemBuffers &b, cudaStream_t s);
+// the whole CEM solve in one cooperative launch of `grid` blocks (cem_fused.cuh); smem = launch_cem_fused_smem(...)
+cudaError_t launch_cem_fused(int dtype, int variant, const EnvParamsHost &ep, const CemFusedArgs &fa, const CemBuffers &b,
+                             const CemFusedScratch &sc, int grid, int coop, cudaStream_t s);
+constexpr int CEM_FUSED_THREADS = 512;
+constexpr int CEM_FUSED_ALLPAIRS_K = 4096;  // up to this K the elites are found by all-pairs rank counting
+constexpr int CEM_FUSED_MAX_H = 512;
 cudaError_t launch_simulate(int dtype, const EnvParamsHost &ep, int H, double lo, double hi, int do_clip,
                             const double *x0, const double *us, const double *g_z, double *xs, double *cost,
                             cudaStream_t s);

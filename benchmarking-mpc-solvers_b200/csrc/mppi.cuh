@@ -388,7 +388,8 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
                       const double *__restrict__ x0g, const double *__restrict__ g_z, double *__restrict__ Ug,
                       double *__restrict__ S_out, double *__restrict__ part, double *__restrict__ rank_part,
                       double *__restrict__ out, int *__restrict__ done_count,
-                      const __grid_constant__ PeerTable pt) {  // indexed by rank at run time: stays in parameter space
+                      const __grid_constant__ PeerTable pt,     // indexed by rank at run time: stays in parameter space
+                      const __grid_constant__ InlineInputs inl) {  // batch-1 host call: state / plan as parameters
     typedef typename Env::Vec V;
     typedef typename Env::S R;
     constexpr int NS = Env::NS, NZ = Env::NS + 1, NG = Env::NG, PACK = VT<V>::N, CH = Env::CHUNK;
@@ -484,7 +485,7 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
     // mode A: the block's single solve's plan, once per block (every warp reads the same copy)
     if (!mode_b)
         for (int t = tid; t < H; t += blockDim.x) {
-            const double u = Ug[(size_t)b_lo * H + t];
+            const double u = (inl.on & 2) ? inl.U[t] : Ug[(size_t)b_lo * H + t];
             sUd[t] = u;
             sU[t] = (R)u;
         }
@@ -515,7 +516,7 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
         }
         Env::prep_goal(ec, g_z + (size_t)b * H * NZ, gs);  // goal row 0 (model.py:34,38)
 #pragma unroll
-        for (int i = 0; i < NS; ++i) xinit[i] = (R)x0g[(size_t)b * NS + i];
+        for (int i = 0; i < NS; ++i) xinit[i] = (R)((inl.on & 1) ? inl.x0[i] : x0g[(size_t)b * NS + i]);
         Env::enter(ec, xinit);
         __syncwarp();
     };
@@ -868,6 +869,7 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
         block_merge(a.neg_inv_lam, H, final_src, final_count, (size_t)rec_len, sscale, sEw, red, Eout, &beta, &eta);
         stamp(a.trace, TR_MERGED);
         double *const err_word = out + (size_t)a.g.B * (2 + H + (H + 1) * NS);
+        const double *const x0p = (inl.on & 1) ? inl.x0 : x0g;  // inline inputs come with batch 1: b == 0
         if (a.p2p) {
             // in-kernel all-gather of the rank records over NVLink, then the same merge over `world` records
             for (int qr = 0; qr < a.world; ++qr) {
@@ -888,9 +890,9 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
             block_merge(a.neg_inv_lam, H, peer_recs(pt.recs[a.rank], a.world, a.g.B, rec_len, a.epoch) + (size_t)b * rec_len,
                         a.world, (size_t)a.g.B * rec_len, sscale, sEw, red, Eout, &beta, &eta);
             stamp(a.trace, TR_MERGED2);
-            block_apply<Env>(a, ec, b, true, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG, sUd);
+            block_apply<Env>(a, ec, b, true, beta, eta, Eout, rank_part, x0p, g_z, Ug, out, sUc, sG, sUd);
         } else {
-            block_apply<Env>(a, ec, b, false, beta, eta, Eout, rank_part, x0g, g_z, Ug, out, sUc, sG, sUd);
+            block_apply<Env>(a, ec, b, false, beta, eta, Eout, rank_part, x0p, g_z, Ug, out, sUc, sG, sUd);
         }
         if (a.host_out && !(a.record_only)) {
             // outputs straight into the caller-visible pinned buffer, then the completion flag (system-scope release)

@@ -238,7 +238,8 @@ int mpc_solve_enqueue(mpc_handle *h);
 int mpc_solve_enqueue_ex(mpc_handle *h, int32_t want_traj);
 /* n device-resident solves, each between its own pair of CUDA events on the handle's stream, optionally with an
  * (untimed) L2 flush after each, all enqueued before the single synchronisation at the end: ms_each [n] = the device
- * time of every solve's own launches, free of host launch latency. */
+ * time of every solve's own launches, free of host launch latency.  world > 1: one untimed solve is enqueued first so
+ * that its in-kernel exchange aligns the ranks' device timelines. */
 int mpc_time_solves(mpc_handle *h, int32_t n, int32_t want_traj, int32_t flush_l2, float *ms_each);
 int mpc_download_outputs(mpc_handle *h, double *u0, double *U_out, double *xs_out, double *cost_out);
 /* CUDA events on the handle's stream (torch.cuda.Event only sees torch's current stream). */
