@@ -29,7 +29,7 @@ SYMBOLS = [
     "mpc_cem_solve", "mpc_cem_get_rewards", "mpc_cem_get_elites", "mpc_cem_get_std", "mpc_simulate", "mpc_model_step",
     "mpc_comm_create_id", "mpc_comm_init", "mpc_mppi_rollout_partial", "mpc_mppi_apply_partials", "mpc_upload_inputs", "mpc_solve_enqueue", "mpc_solve_enqueue_ex", "mpc_time_solves", "mpc_download_outputs",
     "mpc_timer_start", "mpc_timer_stop", "mpc_sync", "mpc_set_profiling", "mpc_get_rollout_ms", "mpc_launch_count", "mpc_get_geometry", "mpc_measure_fma_peak",
-    "mpc_flush_l2", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace", "mpc_episode_run", "mpc_philox_model_noise", "mpc_cem_get_iterations",
+    "mpc_flush_l2", "mpc_debug_tickets", "mpc_pin_host_buffer", "mpc_unpin_host_buffer", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace", "mpc_episode_run", "mpc_philox_model_noise", "mpc_cem_get_iterations",
 ]
 
 
@@ -115,6 +115,9 @@ def load():
     L.mpc_get_geometry.argtypes = [hp, C.POINTER(C.c_int32)]
     L.mpc_measure_fma_peak.argtypes = [C.c_int32, C.c_int32, _dp]
     L.mpc_flush_l2.argtypes = [hp]
+    L.mpc_debug_tickets.argtypes = [hp, C.POINTER(C.c_int32)]
+    L.mpc_pin_host_buffer.argtypes = [C.c_void_p, C.c_size_t]
+    L.mpc_unpin_host_buffer.argtypes = [C.c_void_p]
     _lib = L
     return L
 
@@ -188,6 +191,9 @@ class Solver:
 
     def close(self):
         if self._h is not None:
+            for a in getattr(self, "_pinned", []):
+                self.L.mpc_unpin_host_buffer(a.ctypes.data)
+            self._pinned = []
             self.L.mpc_destroy(self._h)
             self._h = None
 
@@ -246,15 +252,27 @@ class Solver:
                 gp = ptr["g"]
         return arrs, ptr, gp, up
 
-    def mppi_solve(self, x, g_z=None, U_in=None, want_traj=True):
+    def mppi_solve(self, x, g_z=None, U_in=None, want_traj=True, copy=True):
         arrs, ptr, gp, up = self._stage_hot(x, g_z, U_in)
-        if self.B > 1:  # batches: outputs are megabytes, let the library write the caller's arrays directly
-            u0, U = np.empty(self.B), np.empty((self.B, self.H))
-            xs = np.empty((self.B, self.H + 1, self.ns)) if want_traj else None
-            cost = np.empty(self.B) if want_traj else None
-            self._ck(self.L.mpc_mppi_solve(self._h, ptr["x"], gp, up, u0.ctypes.data, U.ctypes.data,
-                                           xs.ctypes.data if want_traj else None, cost.ctypes.data if want_traj else None))
-            return u0, U, xs, cost
+        if self.B > 1:
+            # batches: the outputs are megabytes.  The library copies every field straight from the device into these
+            # arrays (pinned once: direct DMA); copy=False hands out the solver-owned arrays themselves, valid until
+            # the next solve of this handle
+            bo = getattr(self, "_batch_out", None)
+            if bo is None:
+                bo = self._batch_out = dict(u0=np.empty(self.B), U=np.empty((self.B, self.H)),
+                                            xs=np.empty((self.B, self.H + 1, self.ns)), cost=np.empty(self.B))
+                self._pinned = getattr(self, "_pinned", [])
+                for a in bo.values():
+                    if self.L.mpc_pin_host_buffer(a.ctypes.data, a.nbytes) == MPC_OK:
+                        self._pinned.append(a)
+            self._ck(self.L.mpc_mppi_solve(self._h, ptr["x"], gp, up, bo["u0"].ctypes.data, bo["U"].ctypes.data,
+                                           bo["xs"].ctypes.data if want_traj else None,
+                                           bo["cost"].ctypes.data if want_traj else None))
+            if copy:
+                return (bo["u0"].copy(), bo["U"].copy(), bo["xs"].copy() if want_traj else None,
+                        bo["cost"].copy() if want_traj else None)
+            return bo["u0"], bo["U"], (bo["xs"] if want_traj else None), (bo["cost"] if want_traj else None)
         if want_traj:
             self._ck(self.L.mpc_mppi_solve(self._h, ptr["x"], gp, up, ptr["u0"], ptr["Uo"], ptr["xs"], ptr["cost"]))
             return arrs["u0"].copy(), arrs["Uo"].copy(), arrs["xs"].copy(), arrs["cost"].copy()
@@ -484,6 +502,11 @@ class Solver:
                      "it1_sums_barrier", "it1_updated", "iterations_done", "end", "it1_samples_sorted", "it1_keys_located"]
         t0 = buf[0]
         return {n: (int(buf[i]) - int(t0)) if buf[i] else None for i, n in enumerate(names)}
+
+    def nonzero_tickets(self):
+        n = C.c_int32(0)
+        self._ck(self.L.mpc_debug_tickets(self._h, C.byref(n)))
+        return n.value
 
     def sync(self):
         self._ck(self.L.mpc_sync(self._h))

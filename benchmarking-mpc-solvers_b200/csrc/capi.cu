@@ -226,6 +226,8 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         c[19] = I2;
         c[20] = lc2 * lc2;
         c[21] = l1 * lc2;
+        c[22] = p[16] != 0.0 ? 0.0 : c[4];  // book_or_nips == "nips" drops the w1^2 sin(th2) term (acrobot_model.py:124-128)
+        if (p[16] != 0.0) out->f32_unsupported = "the 'nips' Acrobot equations are implemented in float64 mode only";
         for (int i = 0; i < 9; ++i) f[i] = c[i];
         f[9] = p[0] / 2;
         f[10] = p[0] / 6;
@@ -454,6 +456,11 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         delete h;
         return fail(nullptr, MPC_EINVAL, fold_rc == -1 ? "bad env" : "the float32 flavour folds sqrt(W_i) into the cost "
                     "residuals and needs non-negative cost weights; use MPC_F64");
+    }
+    if (cfg->dtype == MPC_F32 && h->ep.f32_unsupported) {
+        const char *why = h->ep.f32_unsupported;
+        delete h;
+        return fail(nullptr, MPC_EINVAL, "%s", why);
     }
     h->ns = (cfg->env == MPC_ENV_PENDULUM) ? 2 : 4;
     h->nz = h->ns + 1;
@@ -846,31 +853,44 @@ static int peer_timeout(mpc_handle *h, const char *what) {
 
 static int fetch_outputs(mpc_handle *h, int want_traj, double *u0, double *U_out, double *xs_out, double *cost_out) {
     const Geometry &g = h->g;
-    const size_t per = want_traj ? h->out_stride : (size_t)(1 + g.H);
-    if (g.B == 1) {
-        CU(h, cudaMemcpyAsync(h->h_out, h->d_out, (per + (want_traj ? 1 : 0)) * sizeof(double), cudaMemcpyDeviceToHost,
-                              h->stream));
-    } else if (want_traj) {
-        CU(h, cudaMemcpyAsync(h->h_out, h->d_out, h->out_elems * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    } else {
-        CU(h, cudaMemcpy2DAsync(h->h_out, h->out_stride * sizeof(double), h->d_out, h->out_stride * sizeof(double),
-                                per * sizeof(double), g.B, cudaMemcpyDeviceToHost, h->stream));
-    }
     // the peer waits' error words live behind the last solve's outputs: slot 0 MPPI (CEM: iterations), slot 1 CEM
     const size_t err_at = (size_t)g.B * h->out_stride + (h->cfg.agent == MPC_AGENT_CEM ? 1 : 0);
     if (h->p2p_ready)
         CU(h, cudaMemcpyAsync(h->h_out + err_at, h->d_out + err_at, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (g.B == 1) {
+        const size_t per = want_traj ? h->out_stride : (size_t)(1 + g.H);
+        CU(h, cudaMemcpyAsync(h->h_out, h->d_out, (per + (want_traj ? 1 : 0)) * sizeof(double), cudaMemcpyDeviceToHost,
+                              h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+        if (h->p2p_ready && h->h_out[err_at] != 0.0) return peer_timeout(h, "record");
+        const double *o = h->h_out;
+        if (u0) u0[0] = o[0];
+        if (U_out) memcpy(U_out, o + 1, g.H * sizeof(double));
+        if (want_traj) {
+            if (cost_out) cost_out[0] = o[1 + g.H];
+            if (xs_out) memcpy(xs_out, o + 2 + g.H, (size_t)(g.H + 1) * h->ns * sizeof(double));
+        }
+        return MPC_OK;
+    }
+    // Batches: megabytes of outputs.  The per-solve records [u0 | U[H] | cost | xs] are de-interleaved BY THE COPY
+    // ENGINE straight into the caller's arrays (one strided copy per field) — no staging buffer, no host-side scatter.
+    // Pinned caller arrays (mpc_pin_host_buffer) make these true DMA transfers.
+    const size_t sp = h->out_stride * sizeof(double);
+    auto field = [&](double *dst, size_t off, size_t n) -> int {
+        if (dst)
+            CU(h, cudaMemcpy2DAsync(dst, n * sizeof(double), h->d_out + off, sp, n * sizeof(double), g.B,
+                                    cudaMemcpyDeviceToHost, h->stream));
+        return MPC_OK;
+    };
+    int rc;
+    if ((rc = field(u0, 0, 1))) return rc;
+    if ((rc = field(U_out, 1, g.H))) return rc;
+    if (want_traj) {
+        if ((rc = field(cost_out, 1 + g.H, 1))) return rc;
+        if ((rc = field(xs_out, 2 + g.H, (size_t)(g.H + 1) * h->ns))) return rc;
+    }
     CU(h, cudaStreamSynchronize(h->stream));
     if (h->p2p_ready && h->h_out[err_at] != 0.0) return peer_timeout(h, "record");
-    for (int b = 0; b < g.B; ++b) {
-        const double *o = h->h_out + (size_t)b * h->out_stride;
-        if (u0) u0[b] = o[0];
-        if (U_out) memcpy(U_out + (size_t)b * g.H, o + 1, g.H * sizeof(double));
-        if (want_traj) {
-            if (cost_out) cost_out[b] = o[1 + g.H];
-            if (xs_out) memcpy(xs_out + (size_t)b * (g.H + 1) * h->ns, o + 2 + g.H, (size_t)(g.H + 1) * h->ns * sizeof(double));
-        }
-    }
     return MPC_OK;
 }
 
@@ -1636,6 +1656,20 @@ int mpc_sync(mpc_handle *h) {
 
 int64_t mpc_launch_count(const mpc_handle *h) { return h ? h->launches : 0; }
 
+// Self-check of the solve kernel's arrival tickets: they are self-cleaning, so between solves every counter is zero.
+int mpc_debug_tickets(mpc_handle *h, int32_t *nonzero_out) {
+    if (!h || !nonzero_out) return MPC_EINVAL;
+    *nonzero_out = 0;
+    if (!h->d_done) return MPC_OK;
+    CU(h, cudaSetDevice(h->cfg.device));
+    const size_t n = (size_t)h->g.B * (1 + h->g.n_groups);
+    std::vector<int> v(n);
+    CU(h, cudaMemcpyAsync(v.data(), h->d_done, n * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    for (int x : v) *nonzero_out += x != 0;
+    return MPC_OK;
+}
+
 int mpc_get_geometry(const mpc_handle *h, int32_t out[8]) {
     if (!h || !out) return MPC_EINVAL;
     out[0] = h->g.grid;
@@ -1646,6 +1680,29 @@ int mpc_get_geometry(const mpc_handle *h, int32_t out[8]) {
     out[5] = h->g.k_begin;
     out[6] = h->g.stages;
     out[7] = h->g.stream_rows;
+    return MPC_OK;
+}
+
+// Page-lock / release a caller-owned host buffer (cudaHostRegister): output arrays of batched solves registered once
+// receive their results by direct DMA.
+int mpc_pin_host_buffer(void *p, size_t bytes) {
+    if (!p || !bytes) return MPC_EINVAL;
+    cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterDefault);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) {
+        cudaGetLastError();
+        return MPC_OK;
+    }
+    if (e != cudaSuccess) return fail(nullptr, MPC_ECUDA, "cudaHostRegister: %s", cudaGetErrorString(e));
+    return MPC_OK;
+}
+
+int mpc_unpin_host_buffer(void *p) {
+    if (!p) return MPC_EINVAL;
+    cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(nullptr, MPC_ECUDA, "cudaHostUnregister: %s", cudaGetErrorString(e));
+    }
     return MPC_OK;
 }
 

@@ -343,7 +343,7 @@ struct Acrobot {
 };
 
 // parity layout c: 0 dt  1 A  2 B  3 C  4 D  5 P1  6 P2  7 max_vel1  8 max_vel2   9..13 W0..W4
-//   14 m1 lc1^2  15 l1^2 + lc2^2  16 2 l1 lc2  17 m2  18 I1  19 I2  20 lc2^2  21 l1 lc2
+//   14 m1 lc1^2  15 l1^2 + lc2^2  16 2 l1 lc2  17 m2  18 I1  19 I2  20 lc2^2  21 l1 lc2  22 D ("book") or 0 ("nips")
 template <int TRIG>
 struct Acrobot<double, TRIG> {
     static constexpr int NS = 4, NG = 5, CHUNK = 1;
@@ -372,7 +372,9 @@ struct Acrobot<double, TRIG> {
         const double d2 = k.c[17] * (k.c[20] + k.c[21] * cth2) + k.c[19];
         const double phi2 = k.c[6] * cos(th1 + th2 - half_pi);
         const double phi1 = ((-k.c[4] * (w2 * w2)) * sth2 - ((k.c[2] * w2) * w1) * sth2) + k.c[5] * cos(th1 - half_pi) + phi2;
-        const double acc2 = (((a + (d2 / d1) * phi1) - (k.c[4] * (w1 * w1)) * sth2) - phi2) / (k.c[3] - (d2 * d2) / d1);
+        // c[22] = D for the "book" equations, 0 for "nips" (acrobot_model.py:124-132: the nips form has no w1^2 term;
+        // subtracting its exact zero leaves the reference's value bit for bit)
+        const double acc2 = (((a + (d2 / d1) * phi1) - (k.c[22] * (w1 * w1)) * sth2) - phi2) / (k.c[3] - (d2 * d2) / d1);
         const double acc1 = -(d2 * acc2 + phi1) / d1;
         d[0] = w1;
         d[1] = w2;

@@ -17,6 +17,7 @@ struct EnvParamsHost {
     int env;
     double c[24];  // folded constants, float64 parity layout (see fold_env_params)
     double f[24];  // folded constants, float32 throughput layout (narrowed when the kernel is launched)
+    const char *f32_unsupported;  // null, or why these parameters have no float32 flavour
 };
 
 // Geometry of one handle's shard; identical for every solve.  MPPI tiles are WARP tiles of wt samples (mppi.cuh).

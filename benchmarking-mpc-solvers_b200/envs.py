@@ -8,6 +8,12 @@ Differences from the reference, on purpose:
     pandas 2); `history["state"].to_numpy()` — the one access pattern Experiment.run uses (Experiment.py:98-100) — works.
   * `step` does not print (env.py:36,40) and does not mutate the caller's action array in place (env.py:39 `u +=`).
   * rendering (pyglet / OpenGL) is out of scope: unavailable on this box.
+  * `reset(state)`: the reference sets `true_state = state.copy()` but leaves `self.state` — what `Experiment.run`
+    hands to the FIRST `predict_action` (Experiment.py:81) — on the degenerate uniform draw of env.py:53-54
+    (`low = -ones * bounds_low = +2`, `high = +2` for the Pendulum, so `[2, 2]`; `[1, 1, 1, 1]` for the other two), so
+    the first action of every reference episode is planned from the wrong state.  Here `state` is
+    set to the start state.  `Environment.reference_reset_quirk = True` (class or instance attribute) reproduces the
+    reference bit for bit; tests/test_host_cpu.py covers both behaviours.
 """
 import numpy as np
 
@@ -51,6 +57,7 @@ class History:
 
 class Environment:
     """envs/env.py:7-69."""
+    reference_reset_quirk = False  # True: reset(state) leaves `self.state` on the uniform draw, as env.py:52-59 does
 
     def __init__(self, name=None):
         self.name = "BaseEnvironment" if name is None else name
@@ -99,7 +106,8 @@ class Environment:
         self.true_state = self.state = self.model.np_random.uniform(low=lo, high=hi)
         if state is not None:
             self.true_state = np.array(state, dtype=np.float64).copy()
-            self.state = self.true_state  # Experiment.py:81 reads env.state before the first step
+            if not self.reference_reset_quirk:
+                self.state = self.true_state  # Experiment.py:81 reads env.state before the first step
         self.last_u = None
         self.history = History()
         return self.true_state

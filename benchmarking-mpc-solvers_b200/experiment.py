@@ -121,6 +121,10 @@ class Experiment:
         self.experiment_results = res
         return res
 
+    def __call__(self, warmstart=None):  # Experiment.py:143-158: every reference script runs `exp(50)`
+        """Runs `run` (the reference's host loop) and returns its result dictionary."""
+        return self.run(warmstart=warmstart)
+
     # ------------------------------------------------------------------------------------------ resident on the GPU
     def run_device(self, warmstart=None, seed=0):
         """Same episode, same result dictionary, one host synchronisation for the whole control loop.  Environment

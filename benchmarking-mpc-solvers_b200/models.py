@@ -186,12 +186,16 @@ def env_spec(model):
         return capi.ENV_CARTPOLE, [float(v) for v in p]
     if "AcrobotModel" in names:
         if getattr(model, "torque_noise_max", 0) > 0:
-            raise ValueError("AcrobotModel.torque_noise_max > 0 is not supported (reference default is 0)")
-        if getattr(model, "book_or_nips", "book") != "book":
-            raise ValueError("only the 'book' Acrobot equations are implemented (the reference default)")
+            raise ValueError("AcrobotModel.torque_noise_max > 0 is not supported: the reference draws it from the "
+                             "model's own RNG inside forked workers (acrobot_model.py:138-140), which no run "
+                             "reproduces; default 0, set by no reference script")
+        kind = getattr(model, "book_or_nips", "book")
+        if kind not in ("book", "nips"):
+            raise ValueError("AcrobotModel.book_or_nips must be 'book' or 'nips'")
+        # "nips" (acrobot_model.py:124-128) is implemented in float64 mode; a float32 handle refuses it in mpc_create
         p = [model.dt, model.LINK_MASS_1, model.LINK_MASS_2, model.LINK_LENGTH_1, model.LINK_COM_POS_1,
              model.LINK_COM_POS_2, model.LINK_MOI, model.LINK_MOI, 9.8, model.MAX_VEL_1, model.MAX_VEL_2] + \
-            _diag(model.W, 5, "AcrobotModel")
+            _diag(model.W, 5, "AcrobotModel") + [1.0 if kind == "nips" else 0.0]
         return capi.ENV_ACROBOT, [float(v) for v in p]
     raise TypeError("unsupported model %r: the CUDA path implements PendulumModel, CartPoleSwingUpModel and "
                     "AcrobotModel" % type(model).__name__)

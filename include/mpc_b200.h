@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define MPC_B200_ABI_VERSION 4
+#define MPC_B200_ABI_VERSION 5
 
 typedef struct mpc_handle mpc_handle;
 
@@ -57,7 +57,8 @@ typedef enum { MPC_NOISE_TENSOR = 0, MPC_NOISE_PHILOX = 1 } mpc_noise;
 /* Model parameters, read from the reference model instance by the host binding:
  *  pendulum: g m l dt max_speed max_torque W0 W1 W2                        (pendulum_model.py:8-22)
  *  cartpole: g m_c m_p l force_mag dt b x_threshold W0..W4 (diag of self.W)  (cartpole_swingup_model.py:23-46)
- *  acrobot : dt m1 m2 l1 lc1 lc2 I1 I2 g max_vel1 max_vel2 W0..W4          (acrobot_model.py:60-97,107) */
+ *  acrobot : dt m1 m2 l1 lc1 lc2 I1 I2 g max_vel1 max_vel2 W0..W4 nips     (acrobot_model.py:60-97,107; nips != 0
+ *            selects the book_or_nips == "nips" equations of :124-128, MPC_F64 only; 0 / absent = "book") */
 typedef struct {
     uint32_t struct_size; /* sizeof(mpc_config), for ABI checking */
     int32_t agent;        /* mpc_agent */
@@ -258,12 +259,20 @@ int mpc_get_rollout_ms(mpc_handle *h, float *ms_out);
 int mpc_get_trace(mpc_handle *h, uint64_t out[16]);
 /* Number of kernel launches issued by this handle so far. */
 int64_t mpc_launch_count(const mpc_handle *h);
+/* Self-check (tests): number of non-zero arrival tickets of the MPPI solve kernel; they clean themselves, so it is 0
+ * between solves. */
+int mpc_debug_tickets(mpc_handle *h, int32_t *nonzero_out);
 /* Geometry chosen for the rollout kernel: out[0]=grid, out[1]=block, out[2]=dynamic smem bytes, out[3]=tiles,
  * out[4]=K_local, out[5]=k_begin, out[6]=ring stages, out[7]=time steps per stage of the STREAM flavour (0: whole
  * [H][tile] stages). */
 int mpc_get_geometry(const mpc_handle *h, int32_t out[8]);
 /* FP32 / FP64 FMA-pipe peak of the device measured with a dependent-free FMA chain (TFLOP/s, 2 flops per FMA). */
 int mpc_measure_fma_peak(int32_t device, int32_t dtype, double *tflops_out);
+/* Page-lock / release a caller-owned host buffer (cudaHostRegister).  Batched solves (batch > 1) copy every output
+ * field straight from the device into the caller's arrays, one strided copy per field; arrays registered once receive
+ * them by direct DMA instead of through the driver's staging. */
+int mpc_pin_host_buffer(void *p, size_t bytes);
+int mpc_unpin_host_buffer(void *p);
 /* Flush L2 by writing a buffer larger than it. */
 int mpc_flush_l2(mpc_handle *h);
 

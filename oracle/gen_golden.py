@@ -102,6 +102,21 @@ def gen_step_kat():
     print("step_kat: ok")
 
 
+def gen_step_kat_nips():
+    """Acrobot with book_or_nips = "nips" (acrobot_model.py:124-128) on the states / controls / goals of step_kat.npz."""
+    d = np.load(os.path.join(OUT, "step_kat.npz"))
+    model = AcrobotModel()
+    model.book_or_nips = "nips"
+    xs, us, gs = d["acrobot_x"], d["acrobot_u"], d["acrobot_g"]
+    cost, xn = np.zeros(len(xs)), np.zeros_like(xs)
+    for i in range(len(xs)):
+        xn[i] = model.predict(xs[i].copy(), us[i].copy(), goal=np.repeat(gs[i][None, :], 2, axis=0))
+        cost[i] = -model.get_reward()
+    np.savez(os.path.join(OUT, "step_kat_nips.npz"), acrobot_cost=cost, acrobot_xn=xn)
+    print("step_kat_nips: ok, differs from book in %d of %d next states" % (
+        int(np.any(xn != d["acrobot_xn"], axis=1).sum()), len(xs)))
+
+
 def gen_mppi_cases():
     """MPPI._calc_action (mppi.py:54-75) with the agent's own delta_u; costs captured from the pool."""
     cases = [
@@ -265,7 +280,11 @@ def gen_episode_cases():
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "nips":  # only the added fixture; the others stay byte-identical
+        gen_step_kat_nips()
+        sys.exit(0)
     gen_step_kat()
+    gen_step_kat_nips()
     gen_mppi_cases()
     gen_cem_cases()
     gen_episode_cases()

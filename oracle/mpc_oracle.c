@@ -34,7 +34,7 @@
 /* Parameter vectors (filled by oracle/oracle.py from the reference constructors' defaults):
  *  pendulum: g m l dt max_speed max_torque W0 W1 W2                       pendulum_model.py:8-22
  *  cartpole: g m_c m_p l force_mag dt b x_threshold W0..W4 (self.W diag)  cartpole_swingup_model.py:23-46
- *  acrobot : dt m1 m2 l1 lc1 lc2 I1 I2 g max_vel1 max_vel2 W0..W4         acrobot_model.py:60-97,107 */
+ *  acrobot : dt m1 m2 l1 lc1 lc2 I1 I2 g max_vel1 max_vel2 W0..W4 nips   acrobot_model.py:60-97,107,124 */
 typedef struct {
     int env;
     int ns;
@@ -106,7 +106,7 @@ static void cartpole_step(const double *p, const double *x, double u, const doub
 
 /* ---------------------------------------------------------------- acrobot */
 static void acrobot_dsdt(const double *p, const double *s, double *ds) {
-    /* "book" branch of _dsdt                                               acrobot_model.py:99-132 */
+    /* _dsdt, "book" branch (default) or "nips" branch (p[16] != 0)          acrobot_model.py:99-132 */
     const double m1 = p[1], m2 = p[2], l1 = p[3], lc1 = p[4], lc2 = p[5], I1 = p[6], I2 = p[7], g = p[8];
     const double a = s[4];
     const double theta1 = s[0], theta2 = s[1], dtheta1 = s[2], dtheta2 = s[3];
@@ -116,8 +116,12 @@ static void acrobot_dsdt(const double *p, const double *s, double *ds) {
     double phi1 = -m2 * l1 * lc2 * (dtheta2 * dtheta2) * sin(theta2) -
                   2 * m2 * l1 * lc2 * dtheta2 * dtheta1 * sin(theta2) +
                   (m1 * lc1 + m2 * l1) * g * cos(theta1 - M_PI / 2) + phi2;
-    double ddtheta2 = (a + d2 / d1 * phi1 - m2 * l1 * lc2 * (dtheta1 * dtheta1) * sin(theta2) - phi2) /
-                      (m2 * (lc2 * lc2) + I2 - (d2 * d2) / d1);
+    double ddtheta2;
+    if (p[16] != 0.0) /* book_or_nips == "nips"                              acrobot_model.py:124-128 */
+        ddtheta2 = (a + d2 / d1 * phi1 - phi2) / (m2 * (lc2 * lc2) + I2 - (d2 * d2) / d1);
+    else
+        ddtheta2 = (a + d2 / d1 * phi1 - m2 * l1 * lc2 * (dtheta1 * dtheta1) * sin(theta2) - phi2) /
+                   (m2 * (lc2 * lc2) + I2 - (d2 * d2) / d1);
     double ddtheta1 = -(d2 * ddtheta2 + phi1) / d1;
     ds[0] = dtheta1;
     ds[1] = dtheta2;

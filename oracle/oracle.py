@@ -29,7 +29,8 @@ def default_params(env, g=10.0):
     if env == "cartpole":
         return [9.82, 0.5, 0.5, 0.6, 10.0, 0.05, 0.1, 2.4, -1.0, -0.0, -5.0, -0.0, -0.0]
     if env == "acrobot":
-        return [0.2, 1.0, 1.0, 1.0, 0.5, 0.5, 1.0, 1.0, 9.8, 4 * np.pi, 9 * np.pi, 1.0, 0.0, 0.0, 0.0, 0.0]
+        return [0.2, 1.0, 1.0, 1.0, 0.5, 0.5, 1.0, 1.0, 9.8, 4 * np.pi, 9 * np.pi, 1.0, 0.0, 0.0, 0.0, 0.0,
+                0.0]  # last: book_or_nips == "nips" flag (acrobot_model.py:124), "book" by default
     raise ValueError(env)
 
 

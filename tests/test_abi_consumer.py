@@ -28,7 +28,7 @@ def test_header_is_c99_and_consumer_links_and_fails_loudly_without_a_device(tmp_
     exe = _build(tmp_path)
     r = subprocess.run([exe, "probe"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
-    assert r.stdout.startswith("abi 4")
+    assert r.stdout.startswith("abi 5")
     assert "device present" in r.stdout or "no CPU path" in r.stdout or "create failed: -2" in r.stdout
 
 

@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), "libmpcb200.so does not export %s" % name
     assert sorted(capi.SYMBOLS) == declared, "capi.SYMBOLS out of sync with include/mpc_b200.h"
-    assert capi.load().mpc_abi_version() == 4
+    assert capi.load().mpc_abi_version() == 5
 
 
 def test_config_struct_size_is_checked():

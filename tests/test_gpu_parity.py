@@ -99,6 +99,35 @@ def test_model_step_kat(golden_dir, env, dtype):
     s.close()
 
 
+def test_model_step_kat_acrobot_nips(golden_dir):
+    """AcrobotModel.book_or_nips = "nips" (acrobot_model.py:124-128): float64 mode follows the reference's fixture to
+    1e-12, through the model class and through a rollout; a float32 handle refuses it loudly."""
+    d, _ = _load(golden_dir, "step_kat.npz")
+    n, _ = _load(golden_dir, "step_kat_nips.npz")
+    params = orc.default_params("acrobot")[:16] + [1.0]
+    s = capi.Solver("MPPI", 2, params, K=1, H=1, bounds=orc.BOUNDS["acrobot"], dtype="f64", noise="philox")
+    cost, xn = s.model_step(d["acrobot_x"], d["acrobot_u"][:, 0], d["acrobot_g"])
+    np.testing.assert_allclose(cost, n["acrobot_cost"], rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(xn, n["acrobot_xn"], rtol=1e-12, atol=1e-12)
+    s.close()
+    m = mpc_b200.AcrobotModel()
+    m.book_or_nips = "nips"
+    x2 = m.predict(d["acrobot_x"][5], d["acrobot_u"][5])
+    np.testing.assert_allclose(x2, n["acrobot_xn"][5], rtol=1e-12, atol=1e-12)
+    m.close()
+    # rollouts: MPPI costs against the oracle with the same flag
+    K, H = 300, 20
+    x, U, eps = _rand_case("acrobot", K, H, seed=2)
+    S_ref, U_ref, _ = orc.mppi_solve(orc.model("acrobot", params=params), x, U, eps, 0.5, 1.0)
+    s = capi.Solver("MPPI", 2, params, K=K, H=H, bounds=orc.BOUNDS["acrobot"], dtype="f64", lam=0.5, sigma=1.0)
+    s.set_noise(eps)
+    s.mppi_solve(x, None, U)
+    np.testing.assert_allclose(s.mppi_costs()[0], S_ref, rtol=F64_COST_RTOL)
+    s.close()
+    with pytest.raises(capi.MpcError, match="nips"):
+        capi.Solver("MPPI", 2, params, K=64, H=5, bounds=orc.BOUNDS["acrobot"], dtype="f32", noise="philox")
+
+
 # ------------------------------------------------------------------------------------------- MPPI, golden
 @pytest.mark.parametrize("dtype", ["f64", "f32"])
 def test_mppi_golden_cases(golden_dir, dtype):
@@ -414,6 +443,40 @@ def test_mppi_peer_exchange_two_gpus(batch):
         np.testing.assert_allclose(outs[0][1], U_ref, rtol=1e-11, atol=1e-11)
         np.testing.assert_allclose(outs[0][2], xs_ref, rtol=1e-9, atol=1e-9)
     for s in ranks + [ref]:
+        s.close()
+
+
+@pytest.mark.skipif(_device_count() < 2, reason="needs two GPUs (run under gpurun --gpus 2)")
+def test_mppi_peer_exchange_with_a_delayed_rank():
+    """The exchange slots are double-buffered by epoch parity: a rank that has seen every record of solve e may publish
+    solve e + 1 while a slower rank is still reading solve e.  Rank 1 is held back by delay kernels (L2 flushes, ~45 us
+    each) between its solves while rank 0's solves are enqueued back to back; the chain of plans must equal the
+    single-GPU chain and be identical on both ranks."""
+    env, K, H, lam = "pendulum", 2048, 30, 0.5
+    rng = np.random.RandomState(4)
+    x = START[env] + rng.normal(0, 0.2, 2)
+    U = rng.uniform(-0.5, 0.5, H)
+    kw = dict(dtype="f64", lam=lam, noise="philox", seed=3)
+    one = _solver("MPPI", env, K, H, **kw)
+    ranks = [_solver("MPPI", env, K, H, device=r, rank=r, world=2, **kw) for r in range(2)]
+    capi.Solver.p2p_link(ranks)
+    n = 8
+    one.upload_inputs(x, None, U)
+    for _ in range(n):
+        one.solve_enqueue(want_traj=False)
+    _, U_ref, _, _ = one.download_outputs()
+    for s in ranks:
+        s.upload_inputs(x, None, U)
+    for i in range(n):           # rank 0: back to back
+        ranks[0].solve_enqueue(want_traj=False)
+    for i in range(n):           # rank 1: a few hundred microseconds behind, more with every solve
+        for _ in range(1 + i):
+            ranks[1].flush_l2()
+        ranks[1].solve_enqueue(want_traj=False)
+    outs = [s.download_outputs() for s in ranks]
+    assert np.array_equal(outs[0][1], outs[1][1])
+    np.testing.assert_allclose(outs[0][1], U_ref, rtol=1e-10, atol=1e-12)
+    for s in ranks + [one]:
         s.close()
 
 
