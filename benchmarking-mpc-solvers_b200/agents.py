@@ -7,7 +7,8 @@ sampling inner loop executed by libmpcb200.so on a B200.
 `model` may be one of this package's models or an instance of the reference's own model classes.
 Extra, optional params keys (defaults reproduce the reference): "dtype" ("f64" | "f32"), "noise" ("tensor": host
 numpy noise exactly as the reference draws it | "philox": generated in-kernel), "fast_math" (f32: MUFU trig),
-"lanes" (f32 MPPI: samples per thread, 1 | 2), "seed", "resample", "device",
+"lanes" (f32 MPPI: samples per thread, 1 | 2), "seed", "resample", "device", "per_step_goal" (sample rollouts use goal
+row t at step t — an extension; the reference's rollouts only see row 0),
 "devices" (list: ONE process drives several GPUs, K sharded over them — no torchrun needed),
 "rank"/"world"/"comm_id" (K-sharding across GPUs, one process per GPU).
 
@@ -23,7 +24,7 @@ use; `rebind_agent_base()` re-evaluates the choice (tests install the import shi
 import numpy as np
 
 from . import capi
-from .models import env_spec
+from .models import cost_matrix, env_spec
 
 
 class Agent:
@@ -126,7 +127,7 @@ def _make_agent_classes(base):
                     seed=params.get("seed", 0), resample=params.get("resample", False),
                     fast_math=params.get("fast_math", False), lanes=params.get("lanes", 0),
                     model_noise_std=float(getattr(self.model, "sensor_std", 0.0)) if getattr(self.model, "sensor_noise", False) else 0.0,
-                    **kw)
+                    W=cost_matrix(self.model), per_step_goal=params.get("per_step_goal", False), **kw)
                 self._traj = None
                 return
             if devices is not None and len(devices) == 1:
@@ -140,7 +141,9 @@ def _make_agent_classes(base):
                 fast_math=params.get("fast_math", False), lanes=params.get("lanes", 0),
                 # a model with sensor noise adds it in every predict of the rollouts (model.py:42-43, noise_tests.py:44)
                 model_noise_std=float(getattr(self.model, "sensor_std", 0.0)) if getattr(self.model, "sensor_noise", False) else 0.0,
-                **kw)
+                # a non-diagonal model.W, or params["per_step_goal"] (sample rollouts follow the goal TRAJECTORY: an
+                # opt-in extension, the reference's rollouts use row 0), select the generic-cost flavour of the kernels
+                W=cost_matrix(self.model), per_step_goal=params.get("per_step_goal", False), **kw)
             if params.get("world", 1) > 1:
                 if "comm_id" in params:   # NCCL all-gather + merge kernel (MPPI)
                     self._solver.comm_init(params["comm_id"])

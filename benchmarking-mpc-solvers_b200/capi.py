@@ -42,6 +42,7 @@ class MpcConfig(C.Structure):
         ("lam", C.c_double), ("sigma", C.c_double), ("epsilon", C.c_double), ("alpha", C.c_double),
         ("bounds_low", C.c_double), ("bounds_high", C.c_double), ("seed", C.c_uint64),
         ("env_params", C.c_double * MAX_ENV_PARAMS), ("model_noise_std", C.c_double),
+        ("full_W", C.c_int32), ("per_step_goal", C.c_int32), ("W", C.c_double * 25),
     ]
 
 
@@ -142,7 +143,8 @@ class Solver:
 
     def __init__(self, agent, env, env_params, K, H, *, dtype="f64", noise="tensor", lam=1.0, sigma=1.0,
                  max_iter=1, n_elite=1, epsilon=0.0, alpha=0.0, bounds=(-1.0, 1.0), batch=1, device=0, rank=0,
-                 world=1, seed=0, resample=False, fast_math=False, lanes=0, model_noise_std=0.0):
+                 world=1, seed=0, resample=False, fast_math=False, lanes=0, model_noise_std=0.0, W=None,
+                 per_step_goal=False):
         self._h = None
         L = load()
         cfg = MpcConfig()
@@ -156,6 +158,15 @@ class Solver:
         cfg.max_iter, cfg.n_elite, cfg.resample = int(max_iter), int(n_elite), int(bool(resample))
         cfg.fast_math, cfg.lanes = int(fast_math), int(lanes)  # fast_math: 0 / 1, Acrobot also 2, 4, 5 (mpc_b200.h)
         cfg.model_noise_std = float(model_noise_std)
+        cfg.per_step_goal = int(bool(per_step_goal))
+        if W is not None:  # the model's whole cost matrix (generic-cost flavour: any W, not only diagonal ones)
+            Wm = np.asarray(W, dtype=np.float64)
+            nz = 3 if int(env) == ENV_PENDULUM else 5
+            if Wm.shape != (nz, nz):
+                raise ValueError("W must be %dx%d for this env" % (nz, nz))
+            cfg.full_W = 1
+            for i, v in enumerate(Wm.reshape(-1)):
+                cfg.W[i] = float(v)
         cfg.lam, cfg.sigma, cfg.epsilon, cfg.alpha = float(lam), float(sigma), float(epsilon), float(alpha)
         cfg.bounds_low, cfg.bounds_high = float(bounds[0]), float(bounds[1])
         cfg.seed = int(seed) & 0xFFFFFFFFFFFFFFFF

@@ -158,6 +158,7 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
     memset(out, 0, sizeof *out);
     out->env = env;
     double *c = out->c, *f = out->f;
+    bool neg = false;
     if (env == MPC_ENV_PENDULUM) {  // pendulum_model.py:14-21,28-38
         const double g = p[0], m = p[1], l = p[2];
         c[0] = -3 * g / (2 * l);
@@ -172,8 +173,8 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         f[3] = p[4];
         f[4] = p[5];
         for (int i = 0; i < 3; ++i) {
-            if (p[6 + i] < 0) return -2;
-            f[5 + i] = sqrt(p[6 + i]);
+            if (p[6 + i] < 0) neg = true;
+            f[5 + i] = sqrt(fabs(p[6 + i]));
         }
     } else if (env == MPC_ENV_CARTPOLE) {  // cartpole_swingup_model.py:25-33,63-85
         const double g = p[0], m_c = p[1], m_p = p[2], l = p[3], b = p[6];
@@ -203,8 +204,8 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         f[11] = 6 * b / l;
         f[12] = 1.0;
         for (int i = 0; i < 5; ++i) {
-            if (-p[8 + i] < 0) return -2;
-            f[13 + i] = sqrt(-p[8 + i]);
+            if (-p[8 + i] < 0) neg = true;
+            f[13 + i] = sqrt(fabs(p[8 + i]));
         }
     } else if (env == MPC_ENV_ACROBOT) {  // acrobot_model.py:100-132
         const double m1 = p[1], m2 = p[2], l1 = p[3], lc1 = p[4], lc2 = p[5], I1 = p[6], I2 = p[7], g = p[8];
@@ -231,9 +232,9 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
         for (int i = 0; i < 9; ++i) f[i] = c[i];
         f[9] = p[0] / 2;
         f[10] = p[0] / 6;
-        if (p[11] < 0 || p[15] < 0) return -2;
-        f[11] = sqrt(p[11]);
-        f[12] = sqrt(p[15]);
+        if (p[11] < 0 || p[15] < 0) neg = true;
+        f[11] = sqrt(fabs(p[11]));
+        f[12] = sqrt(fabs(p[15]));
         f[13] = p[12]; f[14] = p[13]; f[15] = p[14];
         f[16] = p[0] / (2 * M_PI);  // the float flavour integrates the angles in half-turns (envs.cuh)
         f[17] = p[0] / M_PI;
@@ -241,7 +242,7 @@ static int fold_env_params(int env, const double *p, EnvParamsHost *out) {
     } else {
         return -1;
     }
-    return 0;
+    return neg ? -2 : 0;  // -2: a negative cost weight, which the folded float32 cost (sqrt(W_i) residuals) cannot take
 }
 
 
@@ -263,6 +264,7 @@ static MppiArgs mppi_args(const mpc_handle *h, int want_traj) {
     a.noise_batched = 0;
     a.want_traj = want_traj;
     a.goal_zero = h->g_zero_on_device ? 1 : 0;
+    a.per_step_goal = h->cfg.per_step_goal ? 1 : 0;
     a.store_costs = h->store_costs ? 1 : 0;
     a.p2p = (h->cfg.world > 1 && h->p2p_ready) ? 1 : 0;
     a.record_only = (h->cfg.world > 1 && !a.p2p) ? 1 : 0;
@@ -315,6 +317,7 @@ static CemArgs cem_args(const mpc_handle *h, int iter, int want_traj) {
     a.epoch = h->epoch;
     a.model_noise = h->cfg.model_noise_std > 0 ? h->cfg.model_noise_std : 0.0;
     a.noise_draw = (uint32_t)((h->solves * (uint64_t)h->cfg.max_iter + (uint64_t)iter) & 0xffffffffu);
+    a.per_step_goal = h->cfg.per_step_goal ? 1 : 0;
     return a;
 }
 
@@ -452,10 +455,37 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     if (!h) return fail(nullptr, MPC_ENOMEM, "out of host memory");
     h->cfg = *cfg;
     const int fold_rc = fold_env_params(cfg->env, cfg->env_params, &h->ep);
-    if (fold_rc == -1 || (fold_rc == -2 && cfg->dtype == MPC_F32)) {
+    if (fold_rc == -1) {
         delete h;
-        return fail(nullptr, MPC_EINVAL, fold_rc == -1 ? "bad env" : "the float32 flavour folds sqrt(W_i) into the cost "
-                    "residuals and needs non-negative cost weights; use MPC_F64");
+        return fail(nullptr, MPC_EINVAL, "bad env");
+    }
+    // generic cost: the symmetrised upper triangle of the effective cost matrix (sign: CartPole's _state_cost returns
+    // -costs, cartpole_swingup_model.py:104)
+    h->ep.generic = (cfg->full_W || cfg->per_step_goal) ? 1 : 0;
+    if (h->ep.generic) {
+        const int nz = (cfg->env == MPC_ENV_PENDULUM) ? 3 : 5;
+        const double sgn = cfg->env == MPC_ENV_CARTPOLE ? -1.0 : 1.0;
+        const int d0 = cfg->env == MPC_ENV_PENDULUM ? 6 : (cfg->env == MPC_ENV_CARTPOLE ? 8 : 11);  // W_i in env_params
+        int idx = 0;
+        for (int i = 0; i < nz; ++i)
+            for (int j = i; j < nz; ++j) {
+                double v;
+                if (cfg->full_W)
+                    v = (i == j) ? cfg->W[i * nz + i] : cfg->W[i * nz + j] + cfg->W[j * nz + i];
+                else
+                    v = (i == j) ? cfg->env_params[d0 + i] : 0.0;
+                h->ep.w[idx++] = sgn * v;
+            }
+        if (cfg->model_noise_std > 0) {
+            delete h;
+            return fail(nullptr, MPC_EINVAL, "the generic-cost flavour (full_W / per_step_goal) does not combine with model noise");
+        }
+        h->ep.f32_unsupported = nullptr;  // nothing is folded through sqrt(W) here
+    }
+    if (cfg->dtype == MPC_F32 && !h->ep.generic && fold_rc == -2) {
+        delete h;
+        return fail(nullptr, MPC_EINVAL, "the float32 flavour folds sqrt(W_i) into the cost residuals and needs non-negative "
+                    "cost weights; use MPC_F64 or the generic cost (full_W)");
     }
     if (cfg->dtype == MPC_F32 && h->ep.f32_unsupported) {
         const char *why = h->ep.f32_unsupported;
@@ -493,13 +523,14 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
     g.H = cfg->H;
     g.B = cfg->batch;
     // rollout flavour: float32 rolls out two samples per thread (packed f32x2) unless asked otherwise
-    const int lanes = (cfg->dtype == MPC_F32 && cfg->agent == MPC_AGENT_MPPI && !(cfg->model_noise_std > 0))
-                          ? (cfg->lanes ? cfg->lanes : 2) : 1;  // the noisy-model flavour rolls out one sample per thread
+    const int lanes = (cfg->dtype == MPC_F32 && cfg->agent == MPC_AGENT_MPPI && !(cfg->model_noise_std > 0) && !h->ep.generic)
+                          ? (cfg->lanes ? cfg->lanes : 2) : 1;  // noisy-model and generic-cost flavours: one sample per thread
     // fast_math: 0 polynomial trig, 1 MUFU; Acrobot also 2, 4, 5 = per-stage splits (envs.cuh, STREAM flavour only)
     int trig = cfg->dtype == MPC_F32 ? cfg->fast_math : 0;
     if (trig < 0 || trig > 5 || trig == 3) trig = trig ? 1 : 0;
     if (cfg->env != MPC_ENV_ACROBOT && trig > 1) trig = 1;
-    g.variant = trig | (lanes == 2 ? 8 : 0);
+    if (h->ep.generic) trig = 0;
+    g.variant = trig | (lanes == 2 ? 8 : 0) | (h->ep.generic ? 32 : 0);
     g.wt = 32 * lanes;
     g.tiles_per_solve = g.Kpad / g.wt;
     g.total_tiles = g.B * g.tiles_per_solve;
@@ -537,7 +568,8 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         } else {
             // WIDE (MPC_B200_WIDE=1, one sample per thread only): the 32-warp whole-tile flavour at 64 registers
             if (const char *e = getenv("MPC_B200_WIDE"))
-                if (atoi(e) != 0 && lanes == 1 && cfg->dtype == MPC_F32 && !(cfg->model_noise_std > 0)) g.variant |= 16;
+                if (atoi(e) != 0 && lanes == 1 && cfg->dtype == MPC_F32 && !(cfg->model_noise_std > 0) && !h->ep.generic)
+                    g.variant |= 16;
             maxW = mppi_max_warps(cfg->dtype, NOISE_TENSOR, g.variant);
             if (maxW > 16) {  // recount the stages next to 32 warps' records
                 s_cap = 0;
@@ -560,6 +592,7 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
             bool stream = s_cap < 8 || (h->prefer_stream && stream_maxW > W);
             if (const char *e = getenv("MPC_B200_STREAM")) stream = atoi(e) != 0;
             if (cfg->model_noise_std > 0) stream = false;  // the noisy-model flavour exists for whole tiles only
+            if (h->ep.generic) stream = false;  // the generic-cost flavour exists for whole tiles only (fewer warps at long H)
             if (stream) {
                 g.variant &= ~16;
                 g.stream_rows = 8;

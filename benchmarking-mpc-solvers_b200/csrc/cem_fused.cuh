@@ -170,6 +170,8 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
                 double reward = 0.0;
 #pragma unroll 2
                 for (int t = 0; t < H; ++t) {
+                    if constexpr (Env::GENERIC != 0)
+                        if (a.per_step_goal) Env::prep_goal(ec, g_z + (size_t)t * NZ, gs);
                     reward += -(double)Env::step(ec, x, su[t * 32 + tid], gs);
                     if (a.model_noise > 0.0)
                         add_model_noise<Env>(x, a.model_noise, a.seed, PHILOX_MODEL_CEM, fa.noise_draw0 + (uint32_t)it, kglob,
@@ -193,6 +195,8 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
                         const int t = t4 + i;
                         if (t < H) {
                             const R u = vclip(sample_value(ssdR[t], (R)z[i], smuR[t]), lo, hi);
+                            if constexpr (Env::GENERIC != 0)
+                                if (a.per_step_goal) Env::prep_goal(ec, g_z + (size_t)t * NZ, gs);
                             reward += -(double)Env::step(ec, x, u, gs);
                             if (a.model_noise > 0.0)
                                 add_model_noise<Env>(x, a.model_noise, a.seed, PHILOX_MODEL_CEM,

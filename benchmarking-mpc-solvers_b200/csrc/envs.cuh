@@ -37,6 +37,8 @@ enum { ENV_PENDULUM = 0, ENV_CARTPOLE = 1, ENV_ACROBOT = 2 };
 template <typename V>
 struct EnvConst {
     V c[24];
+    V w[15];  // generic-cost flavour (GEN = 1): upper triangle, row major, of the symmetrised effective cost matrix
+              // (w_ii = s W_ii, w_ij = s (W_ij + W_ji), s = -1 for CartPole whose _state_cost returns -costs)
 };
 
 // the one-sample view of the constants (lane 0 of every packed pair)
@@ -45,6 +47,8 @@ __device__ __forceinline__ EnvConst<typename VT<V>::S> scalar_consts(const EnvCo
     EnvConst<typename VT<V>::S> o;
 #pragma unroll
     for (int i = 0; i < 24; ++i) o.c[i] = lane(k.c[i], 0);
+#pragma unroll
+    for (int i = 0; i < 15; ++i) o.w[i] = lane(k.w[i], 0);
     return o;
 }
 
@@ -54,18 +58,36 @@ __device__ __forceinline__ typename VT<V>::S k0(const EnvConst<V> &k, int i) {
 }
 
 __device__ __forceinline__ double clipd(double a, double lo, double hi) { return fmin(fmax(a, lo), hi); }
+
+// zd^T W zd for a full (non-diagonal) W, as einsum("bi,ij,bj->b") of the models' _state_cost
+// (pendulum_model.py:46-50, cartpole_swingup_model.py:95-104, acrobot_model.py:172-176), through the symmetrised
+// upper triangle k.w: sum_i zd_i (sum_{j >= i} w_ij zd_j)
+template <int NZ, typename V>
+__device__ __forceinline__ V quad_form(const EnvConst<V> &k, const V (&zd)[NZ]) {
+    V cost = V((typename VT<V>::S)0);
+    int idx = 0;
+#pragma unroll
+    for (int i = 0; i < NZ; ++i) {
+        V row = k.w[idx++] * zd[i];
+#pragma unroll
+        for (int j = i + 1; j < NZ; ++j) row = vfma(k.w[idx++], zd[j], row);
+        cost = vfma(zd[i], row, cost);
+    }
+    return cost;
+}
 constexpr double D_PI = 3.14159265358979323846;
 
 // ------------------------------------------------------------------------------------------------ Pendulum
 // float layout f: 0 A = -c_sin*dt  1 B = c_u*dt  2 dt  3 max_speed  4 max_torque  5..7 sqrt(W0..W2)
 //   with c_sin = -3g/(2l), c_u = 3/(m l^2)
-template <typename V, int TRIG>
+template <typename V, int TRIG, int GEN = 0>  // GEN: generic cost (full W, goal rows in z units; envs.cuh header)
 struct Pendulum {
     static constexpr int NS = 2, NG = 3, CHUNK = 4;
     static constexpr int ENV = ENV_PENDULUM;
+    static constexpr int GENERIC = GEN;
     typedef typename VT<V>::S S;
     typedef V Vec;
-    typedef Pendulum<S, 0> Scalar;  // one sample per thread, accurate trig: nominal rollouts
+    typedef Pendulum<S, 0, GEN> Scalar;  // one sample per thread, accurate trig: nominal rollouts
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<V> &, S *) {}
     static __device__ __forceinline__ void leave(const EnvConst<V> &, const S *x, double *out) {
@@ -75,7 +97,7 @@ struct Pendulum {
     // cost = sum W_i (z_i - g_i)^2 with z = -[thn, om, u]  ==  sum (sW_i*[thn, om, u]_i + sW_i*g_i)^2
     static __device__ __forceinline__ void prep_goal(const EnvConst<V> &k, const double *g, S *gs) {
 #pragma unroll
-        for (int i = 0; i < 3; ++i) gs[i] = k0(k, 5 + i) * (S)g[i];
+        for (int i = 0; i < 3; ++i) gs[i] = GEN ? (S)g[i] : k0(k, 5 + i) * (S)g[i];
     }
     static __device__ __forceinline__ V step(const EnvConst<V> &k, V (&x)[NS], const V &u, const S *gs) {
         const V th = x[0], om = x[1];
@@ -83,8 +105,14 @@ struct Pendulum {
         // floor differs only when th is an odd multiple of pi exactly (+pi instead of -pi): same cost (thn^2) and
         // |sin| < 1e-7 either way, and it needs no compare/select on the ALU pipe.
         const V thn = vwrap_pi(th);
-        const V d0 = vfma(k.c[5], thn, V(gs[0])), d1 = vfma(k.c[6], om, V(gs[1])), d2 = vfma(k.c[7], u, V(gs[2]));
-        const V cost = vfma(d0, d0, vfma(d1, d1, d2 * d2));   // u NOT clipped in the cost   pendulum_model.py:40-50
+        V cost;
+        if constexpr (GEN) {
+            const V zd[3] = {-thn - V(gs[0]), -om - V(gs[1]), -u - V(gs[2])};  // z = -[thn, om, u]; zd = z - g
+            cost = quad_form<3>(k, zd);
+        } else {
+            const V d0 = vfma(k.c[5], thn, V(gs[0])), d1 = vfma(k.c[6], om, V(gs[1])), d2 = vfma(k.c[7], u, V(gs[2]));
+            cost = vfma(d0, d0, vfma(d1, d1, d2 * d2));   // u NOT clipped in the cost   pendulum_model.py:40-50
+        }
         // dynamics: sin(th + pi) = -sin(th) = -sin(thn)                                      pendulum_model.py:28-38
         const V uc = vclip(u, -k.c[4], k.c[4]);
         const V s = vsin_wrapped<(TRIG != 0)>(thn);
@@ -96,13 +124,14 @@ struct Pendulum {
 };
 
 // parity layout c: 0 c_sin=-3g/(2l)  1 c_u=3/(m l^2)  2 dt  3 max_speed  4 max_torque  5..7 W0..W2
-template <int TRIG>
-struct Pendulum<double, TRIG> {
+template <int TRIG, int GEN>
+struct Pendulum<double, TRIG, GEN> {
     static constexpr int NS = 2, NG = 3, CHUNK = 1;
     static constexpr int ENV = ENV_PENDULUM;
+    static constexpr int GENERIC = GEN;
     typedef double S;
     typedef double Vec;
-    typedef Pendulum<double, TRIG> Scalar;
+    typedef Pendulum<double, TRIG, GEN> Scalar;
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<double> &, double *) {}
     static __device__ __forceinline__ void leave(const EnvConst<double> &, const double *x, double *out) {
@@ -125,7 +154,13 @@ struct Pendulum<double, TRIG> {
         }
         const double thn = r - D_PI;
         const double d0 = -thn - g[0], d1 = -om - g[1], d2 = -u - g[2];
-        const double cost = (d0 * k.c[5]) * d0 + (d1 * k.c[6]) * d1 + (d2 * k.c[7]) * d2;
+        double cost;
+        if constexpr (GEN) {
+            const double zd[3] = {d0, d1, d2};
+            cost = quad_form<3>(k, zd);
+        } else {
+            cost = (d0 * k.c[5]) * d0 + (d1 * k.c[6]) * d1 + (d2 * k.c[7]) * d2;
+        }
         const double uc = clipd(u, -k.c[4], k.c[4]);
         double om2 = om + (k.c[0] * sin(th + D_PI) + k.c[1] * uc) * k.c[2];
         x[0] = th + om2 * k.c[2];
@@ -139,13 +174,14 @@ struct Pendulum<double, TRIG> {
 //    4 A1=-2 m_p l  5 A2=3 m_p g  6 A4=4 b  7 D1=4 M  8 D2=3 m_p
 //    9 B1/l=-3 m_p  10 B2/l=6 M g/l  11 6 b/l  12 u clip (1)   13..17 sqrt(-W_i)
 //   (theta_acc's denominator 4 l M - 3 m_p l c^2 is l times x_acc's, so one reciprocal serves both)
-template <typename V, int TRIG>
+template <typename V, int TRIG, int GEN = 0>
 struct CartPole {
     static constexpr int NS = 4, NG = 5, CHUNK = 4;
     static constexpr int ENV = ENV_CARTPOLE;
+    static constexpr int GENERIC = GEN;
     typedef typename VT<V>::S S;
     typedef V Vec;
-    typedef CartPole<S, 0> Scalar;  // one sample per thread, accurate trig: nominal rollouts
+    typedef CartPole<S, 0, GEN> Scalar;  // one sample per thread, accurate trig: nominal rollouts
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<V> &, S *) {}
     static __device__ __forceinline__ void leave(const EnvConst<V> &, const S *x, double *out) {
@@ -154,11 +190,16 @@ struct CartPole {
     }
     // z = [xc, pd, 1 - cos th, thd, u]; residual_i = sW_i (z_i - g_i)
     static __device__ __forceinline__ void prep_goal(const EnvConst<V> &k, const double *g, S *gs) {
-        gs[0] = -k0(k, 13) * (S)g[0];
-        gs[1] = -k0(k, 14) * (S)g[1];
-        gs[2] = k0(k, 15) * (S)(1.0 - g[2]);
-        gs[3] = -k0(k, 16) * (S)g[3];
-        gs[4] = -k0(k, 17) * (S)g[4];
+        if constexpr (GEN) {
+#pragma unroll
+            for (int i = 0; i < 5; ++i) gs[i] = (S)g[i];
+        } else {
+            gs[0] = -k0(k, 13) * (S)g[0];
+            gs[1] = -k0(k, 14) * (S)g[1];
+            gs[2] = k0(k, 15) * (S)(1.0 - g[2]);
+            gs[3] = -k0(k, 16) * (S)g[3];
+            gs[4] = -k0(k, 17) * (S)g[4];
+        }
     }
     static __device__ __forceinline__ V step(const EnvConst<V> &k, V (&x)[NS], const V &u, const S *gs) {
         const V p = x[0], pd = x[1], th = x[2], thd = x[3];
@@ -168,9 +209,15 @@ struct CartPole {
         const V q = p * k.c[0];
         const V q2 = q * q, q4 = q2 * q2, q8 = q4 * q4;
         const V xc = vfma(q8, q2, q2);
-        const V d0 = vfma(k.c[13], xc, V(gs[0])), d1 = vfma(k.c[14], pd, V(gs[1])), d2 = vfma(-k.c[15], c, V(gs[2])),
-                d3 = vfma(k.c[16], thd, V(gs[3])), d4 = vfma(k.c[17], u, V(gs[4]));
-        const V cost = vfma(d0, d0, vfma(d1, d1, vfma(d2, d2, vfma(d3, d3, d4 * d4))));
+        V cost;
+        if constexpr (GEN) {
+            const V zd[5] = {xc - V(gs[0]), pd - V(gs[1]), (V(1.0f) - c) - V(gs[2]), thd - V(gs[3]), u - V(gs[4])};
+            cost = quad_form<5>(k, zd);
+        } else {
+            const V d0 = vfma(k.c[13], xc, V(gs[0])), d1 = vfma(k.c[14], pd, V(gs[1])), d2 = vfma(-k.c[15], c, V(gs[2])),
+                    d3 = vfma(k.c[16], thd, V(gs[3])), d4 = vfma(k.c[17], u, V(gs[4]));
+            cost = vfma(d0, d0, vfma(d1, d1, vfma(d2, d2, vfma(d3, d3, d4 * d4))));
+        }
         // _dynamics (explicit Euler, old velocities)                          cartpole_swingup_model.py:63-85
         const V uc = vclip(u, -k.c[12], k.c[12]);
         const V t1 = (thd * thd) * s, sc = s * c;
@@ -193,13 +240,14 @@ struct CartPole {
 //    4 A1=-2 m_p l  5 A2=3 m_p g  6 A4=4 b  7 D1=4 M  8 D2=3 m_p
 //    9 B1=-3 m_p l 10 B2=6 M g   11 E1=4 l M 12 E2=3 m_p l
 //   13..17 Wc_i = -W_i  (cost = -(zd W zd), W negative diagonal)   18 x_threshold
-template <int TRIG>
-struct CartPole<double, TRIG> {
+template <int TRIG, int GEN>
+struct CartPole<double, TRIG, GEN> {
     static constexpr int NS = 4, NG = 5, CHUNK = 1;
     static constexpr int ENV = ENV_CARTPOLE;
+    static constexpr int GENERIC = GEN;
     typedef double S;
     typedef double Vec;
-    typedef CartPole<double, TRIG> Scalar;
+    typedef CartPole<double, TRIG, GEN> Scalar;
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<double> &, double *) {}
     static __device__ __forceinline__ void leave(const EnvConst<double> &, const double *x, double *out) {
@@ -218,10 +266,17 @@ struct CartPole<double, TRIG> {
         const double q2 = q * q, q4 = q2 * q2, q8 = q4 * q4;
         const double z[5] = {q2 + q8 * q2, pd, 1 - c, thd, u};
         double acc = 0.0;
+        if constexpr (GEN) {
+            double zd[5];
 #pragma unroll
-        for (int i = 0; i < 5; ++i) {
-            const double d = z[i] - g[i];
-            acc += (d * k.c[13 + i]) * d;
+            for (int i = 0; i < 5; ++i) zd[i] = z[i] - g[i];
+            acc = quad_form<5>(k, zd);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 5; ++i) {
+                const double d = z[i] - g[i];
+                acc += (d * k.c[13 + i]) * d;
+            }
         }
         const double a = clipd(u, -1.0, 1.0) * k.c[1];
         const double thd2 = thd * thd, c2 = c * c;
@@ -241,13 +296,14 @@ struct CartPole<double, TRIG> {
 //    3 C = m2 lc2^2 + I2   4 D = m2 l1 lc2                                                    (d2 = C + D cos th2)
 //    5 P1 = (m1 lc1 + m2 l1) g   6 P2 = m2 lc2 g   7 max_vel1  8 max_vel2   9 h/2  10 h/6  11 sqrt(W0)  12 sqrt(W4)
 //    13..15 W1..W3 (their residuals are constants of the solve)   16 h/(2 pi)  17 h/pi  18 h/(6 pi)
-template <typename V, int TRIG>
+template <typename V, int TRIG, int GEN = 0>
 struct Acrobot {
-    static constexpr int NS = 4, NG = 3, CHUNK = 2;
+    static constexpr int NS = 4, NG = GEN ? 5 : 3, CHUNK = 2;
     static constexpr int ENV = ENV_ACROBOT;
+    static constexpr int GENERIC = GEN;
     typedef typename VT<V>::S S;
     typedef V Vec;
-    typedef Acrobot<S, 0> Scalar;  // one sample per thread, accurate trig: nominal rollouts
+    typedef Acrobot<S, 0, GEN> Scalar;  // one sample per thread, accurate trig: nominal rollouts
     // step() keeps the two angles in HALF-TURNS (theta / pi): range reductions become exact additions (vec.cuh)
     static __device__ __forceinline__ void enter(const EnvConst<V> &, S *x) {
         x[0] *= 0.318309886f;
@@ -261,9 +317,14 @@ struct Acrobot {
     }
     // z = [-cos th1 - cos(th1+th2) - 2, 0, 0, 0, u]                                   acrobot_model.py:162-176
     static __device__ __forceinline__ void prep_goal(const EnvConst<V> &k, const double *g, S *gs) {
-        gs[0] = k0(k, 11) * (S)(2.0 + g[0]);  // residual_0 = -(sW0 (c1 + c12) + gs0)
-        gs[1] = -k0(k, 12) * (S)g[4];
-        gs[2] = k0(k, 13) * (S)(g[1] * g[1]) + k0(k, 14) * (S)(g[2] * g[2]) + k0(k, 15) * (S)(g[3] * g[3]);
+        if constexpr (GEN) {
+#pragma unroll
+            for (int i = 0; i < 5; ++i) gs[i] = (S)g[i];
+        } else {
+            gs[0] = k0(k, 11) * (S)(2.0 + g[0]);  // residual_0 = -(sW0 (c1 + c12) + gs0)
+            gs[1] = -k0(k, 12) * (S)g[4];
+            gs[2] = k0(k, 13) * (S)(g[1] * g[1]) + k0(k, 14) * (S)(g[2] * g[2]) + k0(k, 15) * (S)(g[3] * g[3]);
+        }
     }
 
     // sin/cos of RK4 stage STAGE's angle (half-turns).  TRIG picks, per stage, the polynomial sincospi (FMA pipe, 1.5e-7
@@ -311,8 +372,14 @@ struct Acrobot {
         stage_sincos<1>(p1, &s1, &c1);
         stage_sincos<1>(p2, &s2, &c2);
         const V c12 = vfma(c1, c2, -(s1 * s2));
-        const V d0 = vfma(k.c[11], c1 + c12, V(gs[0])), d4 = vfma(k.c[12], u, V(gs[1]));
-        const V cost = vfma(d0, d0, vfma(d4, d4, V(gs[2])));
+        V cost;
+        if constexpr (GEN) {  // z = [-c1 - c12 - 2, 0, 0, 0, u]
+            const V zd[5] = {(-(c1 + c12) - V(2.0f)) - V(gs[0]), -V(gs[1]), -V(gs[2]), -V(gs[3]), u - V(gs[4])};
+            cost = quad_form<5>(k, zd);
+        } else {
+            const V d0 = vfma(k.c[11], c1 + c12, V(gs[0])), d4 = vfma(k.c[12], u, V(gs[1]));
+            cost = vfma(d0, d0, vfma(d4, d4, V(gs[2])));
+        }
         // one classical RK4 step, torque u (unclipped) held constant            acrobot_model.py:134-160,270-282
         V k1a, k1b, k2a, k2b, k3a, k3b, k4a, k4b;
         accel(k, s1, c1, s2, c2, w1, w2, u, &k1a, &k1b);
@@ -344,13 +411,14 @@ struct Acrobot {
 
 // parity layout c: 0 dt  1 A  2 B  3 C  4 D  5 P1  6 P2  7 max_vel1  8 max_vel2   9..13 W0..W4
 //   14 m1 lc1^2  15 l1^2 + lc2^2  16 2 l1 lc2  17 m2  18 I1  19 I2  20 lc2^2  21 l1 lc2  22 D ("book") or 0 ("nips")
-template <int TRIG>
-struct Acrobot<double, TRIG> {
+template <int TRIG, int GEN>
+struct Acrobot<double, TRIG, GEN> {
     static constexpr int NS = 4, NG = 5, CHUNK = 1;
     static constexpr int ENV = ENV_ACROBOT;
+    static constexpr int GENERIC = GEN;
     typedef double S;
     typedef double Vec;
-    typedef Acrobot<double, TRIG> Scalar;
+    typedef Acrobot<double, TRIG, GEN> Scalar;
     // reference units <-> the units step() keeps the state in (identity here)
     static __device__ __forceinline__ void enter(const EnvConst<double> &, double *) {}
     static __device__ __forceinline__ void leave(const EnvConst<double> &, const double *x, double *out) {
@@ -394,10 +462,17 @@ struct Acrobot<double, TRIG> {
         const double z0 = -cos(x[0]) - cos(x[1] + x[0]) - 2;
         const double zz[5] = {z0, 0.0, 0.0, 0.0, u};
         double acc = 0.0;
+        if constexpr (GEN) {
+            double zd[5];
 #pragma unroll
-        for (int i = 0; i < 5; ++i) {
-            const double d = zz[i] - g[i];
-            acc += (d * k.c[9 + i]) * d;
+            for (int i = 0; i < 5; ++i) zd[i] = zz[i] - g[i];
+            acc = quad_form<5>(k, zd);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 5; ++i) {
+                const double d = zz[i] - g[i];
+                acc += (d * k.c[9 + i]) * d;
+            }
         }
         const double dt = k.c[0] - 0.0, dt2 = dt / 2.0;
         const double y0[4] = {x[0], x[1], x[2], x[3]};
@@ -429,8 +504,8 @@ template <class Env>
 struct NoiseUnit {
     static __device__ __forceinline__ typename Env::S unit(int) { return (typename Env::S)1; }
 };
-template <int TRIG>
-struct NoiseUnit<Acrobot<float, TRIG>> {  // angles in half-turns
+template <int TRIG, int GEN>
+struct NoiseUnit<Acrobot<float, TRIG, GEN>> {  // angles in half-turns
     static __device__ __forceinline__ float unit(int i) { return i < 2 ? 0.318309886f : 1.0f; }
 };
 // One sample per thread (float or double lanes).  Philox counter = (sample, step, draw, stream).

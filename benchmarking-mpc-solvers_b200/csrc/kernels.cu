@@ -92,6 +92,12 @@ static EnvConst<V> make_env(const EnvParamsHost &ep) {
         else
             ec.c[i] = V((float)ep.f[i]);
     }
+    for (int i = 0; i < 15; ++i) {
+        if constexpr (std::is_same<V, double>::value)
+            ec.w[i] = ep.w[i];
+        else
+            ec.w[i] = V((float)ep.w[i]);
+    }
     return ec;
 }
 
@@ -231,6 +237,8 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
         for (int t = 0; t < H; ++t) {
             const R z = zt[(size_t)t * a.z_stride + a.z_off + k];
             const R u = vclip(sample_value(ssd[t], z, smu[t]), lo, hi);
+            if constexpr (Env::GENERIC != 0)
+                if (a.per_step_goal) Env::prep_goal(ec, g_z + (size_t)t * (NS + 1), gs);
             reward += -(double)Env::step(ec, x, u, gs);
             if (a.model_noise > 0.0)
                 add_model_noise<Env>(x, a.model_noise, a.seed, PHILOX_MODEL_CEM, a.noise_draw, (uint32_t)(a.g.k_begin + k), (uint32_t)t);
@@ -245,6 +253,8 @@ __global__ void __launch_bounds__(TILE) cem_rollout_kernel(const CemArgs a, cons
                 const int t = t4 + i;
                 if (t < H) {
                     const R u = vclip(sample_value(ssd[t], (R)z[i], smu[t]), lo, hi);
+                    if constexpr (Env::GENERIC != 0)
+                        if (a.per_step_goal) Env::prep_goal(ec, g_z + (size_t)t * (NS + 1), gs);
                     reward += -(double)Env::step(ec, x, u, gs);
                     if (a.model_noise > 0.0)
                         add_model_noise<Env>(x, a.model_noise, a.seed, PHILOX_MODEL_CEM, a.noise_draw, kglob, (uint32_t)t);
@@ -469,20 +479,21 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float *sink, int iters) {
 typedef MPC_REAL R_;
 
 #if MPC_ENV_ONLY == 0
-template <typename V, int TRIG>
-using TheEnv = Pendulum<V, TRIG>;
+template <typename V, int TRIG, int GEN = 0>
+using TheEnv = Pendulum<V, TRIG, GEN>;
 #elif MPC_ENV_ONLY == 1
-template <typename V, int TRIG>
-using TheEnv = CartPole<V, TRIG>;
+template <typename V, int TRIG, int GEN = 0>
+using TheEnv = CartPole<V, TRIG, GEN>;
 #else
-template <typename V, int TRIG>
-using TheEnv = Acrobot<V, TRIG>;
+template <typename V, int TRIG, int GEN = 0>
+using TheEnv = Acrobot<V, TRIG, GEN>;
 #endif
 constexpr bool IS_ACROBOT = MPC_ENV_ONLY == 2;
 
 // variant: bits 0-2 = trig flavour (0 polynomial, 1 MUFU; Acrobot 2..5: per-stage splits, envs.cuh), bit 3 = two samples
 // per thread (packed f32x2), bit 4 = WIDE (32-warp whole-tile blocks, one sample per thread).  float64 has one flavour.
-enum { VAR_TRIG_MASK = 7, VAR_PACK2 = 8, VAR_WIDE = 16 };
+// bit 5 = generic cost (full W / per-step goals): one sample per thread, polynomial trig, whole tiles or Philox.
+enum { VAR_TRIG_MASK = 7, VAR_PACK2 = 8, VAR_WIDE = 16, VAR_GEN = 32 };
 
 // trig flavours this unit instantiates; everything else collapses to 0 / 1
 static int unit_trig(int variant) {
@@ -496,8 +507,17 @@ static int unit_trig(int variant) {
 template <class F>
 static void with_rollout_env(int variant, bool splits, F &&f) {
     if constexpr (std::is_same<R_, double>::value) {
-        f(TheEnv<double, 0>{});
+        if (variant & VAR_GEN)
+            f(TheEnv<double, 0, 1>{});
+        else
+            f(TheEnv<double, 0>{});
     } else {
+#if MPC_TRIG_GROUP == 0
+        if (variant & VAR_GEN) {
+            f(TheEnv<float, 0, 1>{});
+            return;
+        }
+#endif
         int trig = unit_trig(variant);
         if (trig > 1 && !splits) trig = 1;
         const bool pack = (variant & VAR_PACK2) != 0;
@@ -519,15 +539,25 @@ static void with_rollout_env(int variant, bool splits, F &&f) {
 
 // One sample per thread: CEM rollouts (accurate or fast trig), nominal rollouts and single steps (always accurate).
 template <class F>
-static void with_scalar_env(bool fast, F &&f) {
+static void with_scalar_env(bool fast, F &&f, bool gen = false) {
     if constexpr (std::is_same<R_, double>::value) {
-        f(TheEnv<double, 0>{});
+        if (gen)
+            f(TheEnv<double, 0, 1>{});
+        else
+            f(TheEnv<double, 0>{});
     } else {
-        if (fast)
+        if (gen)
+            f(TheEnv<float, 0, 1>{});
+        else if (fast)
             f(TheEnv<float, 1>{});
         else
             f(TheEnv<float, 0>{});
     }
+}
+
+template <class F>
+static void with_scalar_env_gen(const EnvParamsHost &ep, bool fast, F &&f) {
+    with_scalar_env(fast, f, ep.generic != 0);
 }
 
 template <class Env, int NOISE, bool NOISY = false, bool WIDE = false>
@@ -618,6 +648,17 @@ cudaError_t FN(launch_mppi_solve)(int noise, int variant, const EnvParamsHost &e
     with_rollout_env(variant, stream, [&](auto env) {
         typedef decltype(env) E;
         typedef typename E::Vec V;
+        if constexpr (E::GENERIC != 0) {  // generic cost: whole tiles or Philox only (capi.cu refuses STREAM shapes)
+#if MPC_TRIG_GROUP == 0
+            if (stream)
+                e = cudaErrorInvalidConfiguration;
+            else if (noise == NOISE_PHILOX)
+                e = mppi_solve_go<E, NOISE_PHILOX>(a, ep, b, s);
+            else
+                e = mppi_solve_go<E, NOISE_TENSOR>(a, ep, b, s);
+#endif
+            return;
+        }
         if (noise == NOISE_PHILOX) {
 #if MPC_TRIG_GROUP == 0
             e = mppi_solve_go<E, NOISE_PHILOX>(a, ep, b, s);
@@ -643,7 +684,7 @@ cudaError_t FN(launch_mppi_solve)(int noise, int variant, const EnvParamsHost &e
 cudaError_t FN(launch_mppi_rank_merge)(const EnvParamsHost &ep, const MppiArgs &a, const MppiBuffers &b,
                                        cudaStream_t s) {
     cudaError_t e = cudaSuccess;
-    with_scalar_env(false, [&](auto env) {
+    with_scalar_env_gen(ep, false, [&](auto env) {
         typedef decltype(env) E;
         auto kern = mppi_rank_merge_kernel<E>;
         const int H = a.g.H, nw = 256 / 32;
@@ -693,7 +734,7 @@ cudaError_t FN(launch_cem_rollout)(int noise, int variant, const EnvParamsHost &
                                    const CemBuffers &b, cudaStream_t s) {
     const size_t smem = 2 * (size_t)a.g.H * sizeof(double);
     const int grid = a.g.Kpad / TILE;
-    with_scalar_env(unit_trig(variant) != 0, [&](auto env) {
+    with_scalar_env_gen(ep, unit_trig(variant) != 0, [&](auto env) {
         typedef decltype(env) E;
         typedef typename E::Vec V;
         if (noise == NOISE_TENSOR)
@@ -709,7 +750,7 @@ cudaError_t FN(launch_cem_rollout)(int noise, int variant, const EnvParamsHost &
 cudaError_t FN(launch_cem_fused)(int variant, const EnvParamsHost &ep, const CemFusedArgs &fa, const CemBuffers &b,
                                  const CemFusedScratch &sc, int grid, int coop, cudaStream_t s) {
     cudaError_t e = cudaErrorInvalidValue;
-    with_scalar_env(unit_trig(variant) != 0, [&](auto env) {
+    with_scalar_env_gen(ep, unit_trig(variant) != 0, [&](auto env) {
         typedef decltype(env) E;
         typedef typename E::Vec V;
         auto kern = cem_solve_kernel<E>;
@@ -767,7 +808,7 @@ cudaError_t FN(launch_cem_fused)(int variant, const EnvParamsHost &ep, const Cem
 
 cudaError_t FN(launch_cem_finish)(const EnvParamsHost &ep, const CemArgs &a, const CemBuffers &b, cudaStream_t s) {
     const size_t smem = (size_t)a.g.H * (2 + a.g.ns) * sizeof(double);
-    with_scalar_env(false, [&](auto env) {
+    with_scalar_env_gen(ep, false, [&](auto env) {
         typedef decltype(env) E;
         cem_finish_kernel<E><<<1, 128, smem, s>>>(a, make_env<typename E::Vec>(ep), b.x0, b.g_z, b.mu, b.sel, b.out);
     });
@@ -777,7 +818,7 @@ cudaError_t FN(launch_cem_finish)(const EnvParamsHost &ep, const CemArgs &a, con
 cudaError_t FN(launch_simulate)(const EnvParamsHost &ep, int H, double lo, double hi, int do_clip, const double *x0,
                                 const double *us, const double *g_z, double *xs, double *cost, cudaStream_t s) {
     const size_t smem = (size_t)H * 6 * sizeof(double);
-    with_scalar_env(false, [&](auto env) {
+    with_scalar_env_gen(ep, false, [&](auto env) {
         typedef decltype(env) E;
         simulate_kernel<E><<<1, 64, smem, s>>>(make_env<typename E::Vec>(ep), H, lo, hi, do_clip, x0, us, g_z, xs, cost);
     });
@@ -786,7 +827,7 @@ cudaError_t FN(launch_simulate)(const EnvParamsHost &ep, int H, double lo, doubl
 
 cudaError_t FN(launch_model_step)(const EnvParamsHost &ep, int n, const double *x, const double *u, const double *g,
                                   double *cost, double *xn, cudaStream_t s) {
-    with_scalar_env(false, [&](auto env) {
+    with_scalar_env_gen(ep, false, [&](auto env) {
         typedef decltype(env) E;
         model_step_kernel<E><<<(n + 127) / 128, 128, 0, s>>>(make_env<typename E::Vec>(ep), n, x, u, g, cost, xn);
     });
@@ -796,7 +837,10 @@ cudaError_t FN(launch_model_step)(const EnvParamsHost &ep, int n, const double *
 #ifdef MPC_IS_F64
 // always the float64 plant, whatever the rollout dtype
 cudaError_t FN(launch_episode_step)(const EnvParamsHost &ep, const EpisodeArgs &a, const EpisodeBuffers &b, cudaStream_t s) {
-    episode_step_kernel<TheEnv<double, 0>><<<1, 128, 0, s>>>(make_env<double>(ep), a, b);
+    if (ep.generic)
+        episode_step_kernel<TheEnv<double, 0, 1>><<<1, 128, 0, s>>>(make_env<double>(ep), a, b);
+    else
+        episode_step_kernel<TheEnv<double, 0>><<<1, 128, 0, s>>>(make_env<double>(ep), a, b);
     return cudaGetLastError();
 }
 #endif

@@ -18,6 +18,8 @@ struct EnvParamsHost {
     double c[24];  // folded constants, float64 parity layout (see fold_env_params)
     double f[24];  // folded constants, float32 throughput layout (narrowed when the kernel is launched)
     const char *f32_unsupported;  // null, or why these parameters have no float32 flavour
+    int generic;   // generic-cost flavour: full (non-diagonal) W and / or per-step goal rows in the sample rollouts
+    double w[15];  // its cost matrix: upper triangle (row major) of the symmetrised effective matrix (envs.cuh)
 };
 
 // Geometry of one handle's shard; identical for every solve.  MPPI tiles are WARP tiles of wt samples (mppi.cuh).
@@ -69,6 +71,8 @@ struct MppiArgs {
     int want_traj;        // compute the clipped plan's nominal rollout in the tail of the solve kernel
     int store_costs;      // write the per-sample costs S[k] (agent.sample_costs before mppi.py:73 zeroes them)
     int goal_zero;        // the goal trajectory is all zeros (what every reference script passes)
+    int per_step_goal;    // generic-cost flavour only: sample rollouts use goal row t at step t (an extension: the
+                          // reference's rollouts only ever see row 0, model.py:34,38)
     int record_only;      // the tail publishes this rank's (beta, eta, E) record instead of applying it
     int p2p;              // multi-GPU: all-gather the rank records inside the kernel over peer memory, then apply
     unsigned long long epoch;  // p2p: flag value of this solve (monotonic per handle, equal on all ranks)
@@ -100,6 +104,7 @@ struct CemArgs {
     unsigned long long epoch;  // flag value of this iteration's candidate exchange
     double model_noise;   // as MppiArgs
     uint32_t noise_draw;  // solve counter * max_iter + iteration
+    int per_step_goal;    // as MppiArgs
 };
 
 // CEM as one persistent cooperative launch (cem_fused.cuh): single GPU, Philox noise

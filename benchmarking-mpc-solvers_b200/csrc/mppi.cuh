@@ -560,6 +560,8 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
         // one rollout step: u = U_t + eps (mppi.py:39), cost + step (mppi.py:43-44), lam * u * eps / sigma^2 (:45-46)
         auto one = [&](int t, const V &e, V &acc) {
             const V u = V(sU[t]) + e;
+            if constexpr (Env::GENERIC != 0)  // opt-in extension: goal row t at step t (the reference's rollouts: row 0)
+                if (a.per_step_goal) Env::prep_goal(ec, g_z + ((size_t)b * H + t) * NZ, gs);
             const V c = Env::step(ec, x, u, gs);
             if constexpr (NOISY) {  // newstate += N(0, sensor_std)   model.py:42-43
                 static_assert(PACK == 1, "the noisy-model flavour rolls out one sample per thread");

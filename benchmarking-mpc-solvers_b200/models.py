@@ -50,11 +50,16 @@ class Model:
         self.name = self.name.replace("No Noise", "With Noise std=" + str(sensor_std))
 
     def _solver(self):
+        # rebuilt when model.W was replaced: the handle folds the cost matrix at creation
+        Wkey = np.asarray(self.W, dtype=np.float64).tobytes() if hasattr(self, "W") else None
+        if self._stepper is not None and Wkey != getattr(self, "_stepper_W", None):
+            self.close()
         if self._stepper is None:
             env, params = env_spec(self)
             self._stepper = capi.Solver("MPPI", env, params, K=1, H=1, dtype="f64", noise="philox",
                                         bounds=(float(np.ravel(self.bounds_low)[0]), float(np.ravel(self.bounds_high)[0])),
-                                        device=self._device)
+                                        device=self._device, W=cost_matrix(self))
+            self._stepper_W = Wkey
         return self._stepper
 
     # model.py:26-44: cost of (x, u) against goal row 0, then the step
@@ -165,12 +170,23 @@ class AcrobotModel(Model):
 
 
 def _diag(W, n, what):
+    """The diagonal of model.W for the parameter vector.  A non-diagonal W (or, in float32, a negative weight) is
+    carried by `cost_matrix` instead and selects the generic-cost flavour of the kernels."""
     W = np.asarray(W, dtype=np.float64)
     if W.shape != (n, n):
         raise ValueError("%s.W must be %dx%d" % (what, n, n))
-    if np.count_nonzero(W - np.diag(np.diag(W))):
-        raise ValueError("%s.W must be diagonal (the three reference models are)" % what)
     return [float(v) for v in np.diag(W)]
+
+
+def cost_matrix(model):
+    """None when model.W is one of the reference's own cost matrices in kind (diagonal: the fast, folded cost of the
+    kernels applies), else the full nz x nz matrix to hand to capi.Solver(W=...) — einsum("bi,ij,bj->b") over any W
+    (pendulum_model.py:46-50, cartpole_swingup_model.py:95-104, acrobot_model.py:172-176)."""
+    W = np.asarray(model.W, dtype=np.float64)
+    sign = -1.0 if "CartPoleSwingUpModel" in {c.__name__ for c in type(model).__mro__} else 1.0  # its cost is -zd W zd
+    if np.count_nonzero(W - np.diag(np.diag(W))) == 0 and np.all(sign * np.diag(W) >= 0):
+        return None  # (a negative weight cannot be folded as sqrt(W_i) by the float32 kernels either)
+    return W
 
 
 def env_spec(model):

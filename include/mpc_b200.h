@@ -94,6 +94,16 @@ typedef struct {
                              nominal rollout) adds N(0, std) to each component of the new state (model.py:42-43).  0 = off.
                              The draws are Philox (fresh per solve): statistically the reference's, not its numpy stream
                              (which is not reproducible there either: forked workers share one RNG state). */
+    /* Generic cost.  full_W != 0: W holds the model's whole cost matrix self.W, row major nz x nz
+     * (nz = state_size + 1), used as einsum("bi,ij,bj->b") does (pendulum_model.py:46-50,
+     * cartpole_swingup_model.py:95-104, acrobot_model.py:172-176) — any matrix, negative or non-symmetric; the W_i
+     * entries of env_params are then ignored.  per_step_goal != 0: the sample rollouts use goal row t at step t (an
+     * extension: the reference's rollouts only ever see row 0, model.py:34,38; its nominal rollout already uses row t,
+     * agent.py:103-104, and so does this library's).  Either switch selects the generic flavour of the kernels: one
+     * sample per thread, polynomial trig, whole-tile or Philox noise. */
+    int32_t full_W;
+    int32_t per_step_goal;
+    double W[25];
 } mpc_config;
 
 /* ---- lifetime ------------------------------------------------------------------------------------------ */

@@ -117,6 +117,53 @@ def gen_step_kat_nips():
         int(np.any(xn != d["acrobot_xn"], axis=1).sum()), len(xs)))
 
 
+def gen_fullw_cases():
+    """A full (non-diagonal, non-symmetric, indefinite) cost matrix self.W — einsum("bi,ij,bj->b") in _state_cost
+    (pendulum_model.py:46-50, cartpole_swingup_model.py:95-104, acrobot_model.py:172-176): single predicts, MPPI.f
+    per-sample costs (mppi.py:35-48), CEM.f rewards (cem.py:42-48) and Agent.simulate_trajectory with a per-step goal
+    trajectory (agent.py:97-108), all from the unmodified reference with only model.W replaced."""
+    out = {}
+    for ei, (env, cls) in enumerate(ENVS.items()):
+        rng = np.random.RandomState(500 + ei)
+        model = cls()
+        ns = model.state_size
+        nz = ns + 1
+        W = np.array(model.W, dtype=np.float64) + rng.normal(0, 0.3, (nz, nz))
+        model.W = W
+        n = 64
+        xs = rand_state(env, rng, n)
+        us = rng.uniform(-2, 2, (n, 1))
+        gs = rng.uniform(-1, 1, (n, nz))
+        cost, xn = np.zeros(n), np.zeros_like(xs)
+        for i in range(n):
+            xn[i] = model.predict(xs[i].copy(), us[i].copy(), goal=gs[i][None, :])
+            cost[i] = -model.get_reward()
+        K, H, lam, std = 48, 15, 0.5, 1.0
+        x = START[env] + rng.normal(0, 0.3, ns)
+        U = rng.uniform(-0.5, 0.5, (H, 1))
+        delta_u = rng.normal(0, std, (K, H, 1))
+        g = rng.uniform(-0.5, 0.5, nz)
+        g_z = np.repeat(g[None, :], H, axis=0)
+        S = np.array([MPPI.f(model, x.copy(), U, delta_u[k], g_z, H, lam, np.ones((1, 1)) * std) for k in range(K)],
+                     dtype=np.float64).reshape(K)
+        lo, hi = model.bounds_low, model.bounds_high
+        samples = np.clip(rng.normal(0, 1.0, (K, H, 1)), lo, hi)
+        R = np.array([CEM.f(model, x.copy(), samples[k], g_z) for k in range(K)], dtype=np.float64).reshape(K)
+        # nominal rollout against a goal TRAJECTORY (row t at step t): Agent.simulate_trajectory
+        agent = make_agent(MPPI, model, {"K": 2, "T": H, "std": 1.0, "lam": 1.0})
+        g_traj = rng.uniform(-0.5, 0.5, (H, nz))
+        us_nom = np.clip(rng.uniform(-1.5, 1.5, (H, 1)), lo, hi)
+        xs_nom, c_nom = agent.simulate_trajectory(x.copy(), us_nom, g_traj)
+        agent.close()
+        out.update({env + "_W": W, env + "_x": xs, env + "_u": us, env + "_g": gs, env + "_cost": cost, env + "_xn": xn,
+                    env + "_x0": x, env + "_U": U, env + "_delta_u": delta_u, env + "_goal": g, env + "_S": S,
+                    env + "_samples": samples, env + "_R": R, env + "_g_traj": g_traj, env + "_us_nom": us_nom,
+                    env + "_xs_nom": xs_nom, env + "_c_nom": np.array(float(c_nom))})
+    out["meta"] = np.array(json.dumps(dict(K=48, H=15, lam=0.5, std=1.0)))
+    np.savez(os.path.join(OUT, "fullw_cases.npz"), **out)
+    print("fullw_cases: ok")
+
+
 def gen_mppi_cases():
     """MPPI._calc_action (mppi.py:54-75) with the agent's own delta_u; costs captured from the pool."""
     cases = [
@@ -280,11 +327,12 @@ def gen_episode_cases():
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    if len(sys.argv) > 1 and sys.argv[1] == "nips":  # only the added fixture; the others stay byte-identical
-        gen_step_kat_nips()
+    if len(sys.argv) > 1 and sys.argv[1] in ("nips", "fullw"):  # only an added fixture; the others stay byte-identical
+        {"nips": gen_step_kat_nips, "fullw": gen_fullw_cases}[sys.argv[1]]()
         sys.exit(0)
     gen_step_kat()
     gen_step_kat_nips()
+    gen_fullw_cases()
     gen_mppi_cases()
     gen_cem_cases()
     gen_episode_cases()

@@ -39,6 +39,10 @@ typedef struct {
     int env;
     int ns;
     double p[24];
+    int full_w;      /* != 0: W holds the model's whole cost matrix self.W (nz x nz, row major); the W_i of p are ignored */
+    int goal_stride; /* 0: one goal row for every rollout step (the reference: model.py:34,38 uses row 0);
+                        nz: row t at step t in the SAMPLE rollouts too (an extension of this repo, opt-in) */
+    double W[25];
 } orc_model;
 
 static double clipd(double a, double lo, double hi) { return fmin(fmax(a, lo), hi); }
@@ -54,15 +58,29 @@ static double np_mod(double a, double b) {
     return r;
 }
 
+/* _state_cost: einsum("bi,ij,bj->b", zd, W, zd) for one row   pendulum_model.py:46-50 (same in the other two models);
+ * diagonal W (the reference's three models): sum_i (zd_i W_ii) zd_i */
+static double state_cost(const orc_model *m, const double *zd, int nz, const double *wdiag) {
+    double acc = 0.0;
+    if (m->full_w) {
+        for (int i = 0; i < nz; ++i)
+            for (int j = 0; j < nz; ++j) acc += (zd[i] * m->W[i * nz + j]) * zd[j];
+    } else {
+        for (int i = 0; i < nz; ++i) acc += (zd[i] * wdiag[i]) * zd[i];
+    }
+    return acc;
+}
+
 /* ---------------------------------------------------------------- pendulum */
-static void pendulum_step(const double *p, const double *x, double u, const double *g, double *cost, double *xn) {
+static void pendulum_step(const orc_model *mdl, const double *x, double u, const double *g, double *cost, double *xn) {
+    const double *p = mdl->p;
     const double grav = p[0], m = p[1], l = p[2], dt = p[3], max_speed = p[4], max_torque = p[5];
     const double th = x[0], thdot = x[1];
     /* _transform: z = -[angle_normalize(th), thdot, u]   (u NOT clipped)          pendulum_model.py:40-44 */
     double thn = np_mod(th + M_PI, 2 * M_PI) - M_PI;
     double z0 = -thn, z1 = -thdot, z2 = -u;
-    double d0 = z0 - g[0], d1 = z1 - g[1], d2 = z2 - g[2];
-    *cost = (d0 * p[6]) * d0 + (d1 * p[7]) * d1 + (d2 * p[8]) * d2;
+    double zd[3] = {z0 - g[0], z1 - g[1], z2 - g[2]};
+    *cost = state_cost(mdl, zd, 3, p + 6);
     /* _dynamics                                                               pendulum_model.py:28-38 */
     double uc = clipd(u, -max_torque, max_torque);
     double newthdot = thdot + (-3 * grav / (2 * l) * sin(th + M_PI) + 3. / (m * (l * l)) * uc) * dt;
@@ -73,7 +91,8 @@ static void pendulum_step(const double *p, const double *x, double u, const doub
 }
 
 /* ---------------------------------------------------------------- cartpole */
-static void cartpole_step(const double *p, const double *x, double u, const double *g, double *cost, double *xn) {
+static void cartpole_step(const orc_model *mdl, const double *x, double u, const double *g, double *cost, double *xn) {
+    const double *p = mdl->p;
     const double grav = p[0], m_c = p[1], m_p = p[2], l = p[3], force_mag = p[4], dt = p[5], b = p[6],
                  x_threshold = p[7];
     const double total_m = m_p + m_c, m_p_l = m_p * l;
@@ -82,12 +101,9 @@ static void cartpole_step(const double *p, const double *x, double u, const doub
     double q = pos / x_threshold;
     double z[5] = {q * q + pow(q, 10.0), x_dot, 1 - cos(theta), theta_dot, u};
     /* _state_cost: -(einsum(zd W zd)) with W = self.W (negative diag)   cartpole_swingup_model.py:95-104 */
-    double acc = 0.0;
-    for (int i = 0; i < 5; ++i) {
-        double d = z[i] - g[i];
-        acc += (d * p[8 + i]) * d;
-    }
-    *cost = -acc;
+    double zd[5];
+    for (int i = 0; i < 5; ++i) zd[i] = z[i] - g[i];
+    *cost = -state_cost(mdl, zd, 5, p + 8);
     /* _dynamics                                                      cartpole_swingup_model.py:63-85 */
     double action = clipd(u, -1.0, 1.0);
     action *= force_mag;
@@ -137,14 +153,13 @@ static double wrap_angle(double x, double m, double M) { /* acrobot_model.py:185
     return x;
 }
 
-static void acrobot_step(const double *p, const double *x, double u, const double *g, double *cost, double *xn) {
+static void acrobot_step(const orc_model *mdl, const double *x, double u, const double *g, double *cost, double *xn) {
+    const double *p = mdl->p;
     /* _transform + _state_cost                                              acrobot_model.py:162-176 */
     double z[5] = {-cos(x[0]) - cos(x[1] + x[0]) - 2, 0.0, 0.0, 0.0, u};
-    double acc = 0.0;
-    for (int i = 0; i < 5; ++i) {
-        double d = z[i] - g[i];
-        acc += (d * p[11 + i]) * d;
-    }
+    double zd[5];
+    for (int i = 0; i < 5; ++i) zd[i] = z[i] - g[i];
+    double acc = state_cost(mdl, zd, 5, p + 11);
     *cost = acc;
     /* _dynamics: one rk4 step over t = [0, dt]                    acrobot_model.py:134-160,270-282 */
     const double dt = p[0] - 0.0, dt2 = dt / 2.0;
@@ -166,9 +181,9 @@ static void acrobot_step(const double *p, const double *x, double u, const doubl
 /* Model.predict + get_reward: cost of (x,u) against goal row 0, then next state. */
 void orc_step(const orc_model *m, const double *x, double u, const double *goal_nz, double *cost, double *xn) {
     switch (m->env) {
-    case ORC_PENDULUM: pendulum_step(m->p, x, u, goal_nz, cost, xn); break;
-    case ORC_CARTPOLE: cartpole_step(m->p, x, u, goal_nz, cost, xn); break;
-    default: acrobot_step(m->p, x, u, goal_nz, cost, xn); break;
+    case ORC_PENDULUM: pendulum_step(m, x, u, goal_nz, cost, xn); break;
+    case ORC_CARTPOLE: cartpole_step(m, x, u, goal_nz, cost, xn); break;
+    default: acrobot_step(m, x, u, goal_nz, cost, xn); break;
     }
 }
 
@@ -251,7 +266,7 @@ static void mppi_range(void *vctx, int k0, int k1) {
         for (int t = 0; t < H; ++t) {
             double e = c->eps[(long)k * H + t];
             double test_u = c->U[t] + e;                             /* mppi.py:39 */
-            orc_step(c->m, x, test_u, c->goal, &cost, xn);           /* mppi.py:43-44 */
+            orc_step(c->m, x, test_u, c->goal + (long)t * c->m->goal_stride, &cost, xn); /* mppi.py:43-44 */
             sample_cost += cost + ((c->lam * test_u) * c->pinv) * e; /* mppi.py:45-46 */
             for (int i = 0; i < ns; ++i) x[i] = xn[i];
             if (c->xnoise) /* newstate += np.random.normal(0, sensor_std, state_size)   model.py:42-43 */
@@ -322,7 +337,7 @@ static void cem_range(void *vctx, int k0, int k1) {
         double x[4], xn[4], reward = 0.0, cost;
         for (int i = 0; i < ns; ++i) x[i] = c->x0[i];
         for (int t = 0; t < H; ++t) {
-            orc_step(c->m, x, c->samples[(long)k * H + t], c->goal, &cost, xn);
+            orc_step(c->m, x, c->samples[(long)k * H + t], c->goal + (long)t * c->m->goal_stride, &cost, xn);
             reward += -cost; /* cem.py:46-47: reward += model.get_reward() */
             for (int i = 0; i < ns; ++i) x[i] = xn[i];
         }

@@ -18,7 +18,8 @@ BOUNDS = {"pendulum": (-2.0, 2.0), "cartpole": (-1.0, 1.0), "acrobot": (-1.0, 1.
 
 
 class OrcModel(C.Structure):
-    _fields_ = [("env", C.c_int), ("ns", C.c_int), ("p", C.c_double * 24)]
+    _fields_ = [("env", C.c_int), ("ns", C.c_int), ("p", C.c_double * 24), ("full_w", C.c_int),
+                ("goal_stride", C.c_int), ("W", C.c_double * 25)]
 
 
 def default_params(env, g=10.0):
@@ -77,13 +78,20 @@ def _d(a):
     return a, a.ctypes.data_as(C.POINTER(C.c_double))
 
 
-def model(env, params=None, **kw):
+def model(env, params=None, W=None, per_step_goal=False, **kw):
+    """W: the model's whole cost matrix self.W (any nz x nz matrix); per_step_goal: the sample rollouts use goal row t
+    at step t (callers then pass goal as [H][nz]) — an extension, the reference's rollouts use row 0."""
     m = OrcModel()
     m.env = ENV_IDS[env]
     m.ns = STATE_SIZE[env]
     p = list(params) if params is not None else default_params(env, **kw)
     for i, v in enumerate(p):
         m.p[i] = float(v)
+    if W is not None:
+        m.full_w = 1
+        for i, v in enumerate(np.asarray(W, dtype=np.float64).reshape(-1)):
+            m.W[i] = float(v)
+    m.goal_stride = (m.ns + 1) if per_step_goal else 0
     m._env_name = env
     return m
 

@@ -54,8 +54,17 @@ def test_env_spec_reads_parameters():
         pass
     with pytest.raises(TypeError):
         mpc_b200.env_spec(Other())
+    # a full (non-diagonal) cost matrix is carried next to the parameter vector and selects the generic-cost kernels
+    from mpc_b200.models import cost_matrix
     m = mpc_b200.PendulumModel()
+    assert cost_matrix(m) is None
     m.W = np.ones((3, 3))
+    assert mpc_b200.env_spec(m)[1][6:9] == [1.0, 1.0, 1.0] and np.array_equal(cost_matrix(m), np.ones((3, 3)))
+    c = mpc_b200.CartPoleSwingUpModel()
+    assert cost_matrix(c) is None          # W = -diag(...): its cost is -zd W zd, the effective weights are >= 0
+    c.W = -c.W
+    assert cost_matrix(c) is not None      # negative effective weights cannot be folded as sqrt(W_i)
+    m.W = np.ones((2, 2))
     with pytest.raises(ValueError):
         mpc_b200.env_spec(m)
 

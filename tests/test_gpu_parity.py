@@ -128,6 +128,123 @@ def test_model_step_kat_acrobot_nips(golden_dir):
         capi.Solver("MPPI", 2, params, K=64, H=5, bounds=orc.BOUNDS["acrobot"], dtype="f32", noise="philox")
 
 
+# ------------------------------------------------------------------------------------------- generic cost (§8 f4)
+@pytest.mark.parametrize("env", ENVS)
+@pytest.mark.parametrize("dtype", ["f64", "f32"])
+def test_full_cost_matrix_golden(golden_dir, env, dtype):
+    """model.W replaced by a full (non-diagonal, non-symmetric, indefinite) matrix — the generic-cost flavour of the
+    kernels against fixtures produced by the unmodified reference with only model.W changed: single predicts, MPPI.f
+    per-sample costs, CEM.f rewards, the nominal rollout against a goal TRAJECTORY (agent.py:97-108)."""
+    d, mt = _load(golden_dir, "fullw_cases.npz")
+    W = d[env + "_W"]
+    K, H = mt["K"], mt["H"]
+    rt, at = (1e-12, 1e-12) if dtype == "f64" else (2e-4, 2e-4)
+    s = _solver("MPPI", env, K, H, dtype=dtype, lam=mt["lam"], sigma=mt["std"], W=W)
+    cost, xn = s.model_step(d[env + "_x"], d[env + "_u"][:, 0], d[env + "_g"])
+    if dtype == "f64":
+        np.testing.assert_allclose(cost, d[env + "_cost"], rtol=rt, atol=at)
+        np.testing.assert_allclose(xn, d[env + "_xn"], rtol=rt, atol=at)
+    else:  # extreme random states: a few float32 ulps of terms ~ omega^2 (test_model_step_kat's reasoning)
+        err = np.abs(cost - d[env + "_cost"])
+        assert (err <= 1e-5 * np.abs(d[env + "_cost"]) + 1e-3).mean() >= 0.95
+    s.set_noise(d[env + "_delta_u"].reshape(K, H))
+    g_z = np.repeat(d[env + "_goal"][None, :], H, axis=0)
+    s.mppi_solve(d[env + "_x0"], g_z, d[env + "_U"].reshape(-1))
+    S = s.mppi_costs()[0]
+    if dtype == "f64":
+        np.testing.assert_allclose(S, d[env + "_S"], rtol=F64_COST_RTOL)
+    else:
+        f32_cost_bar(env, H, np.abs(S - d[env + "_S"]) / np.abs(d[env + "_S"]), "full W", energetic=True)
+    xs, c = s.simulate(d[env + "_x0"], d[env + "_us_nom"][:, 0], d[env + "_g_traj"])
+    if dtype == "f64":
+        np.testing.assert_allclose(xs, d[env + "_xs_nom"], rtol=1e-11, atol=1e-11)
+        assert c == pytest.approx(float(d[env + "_c_nom"]), rel=1e-11)
+    s.close()
+    # CEM.f rewards: iteration 0 of a CEM solve whose samples are the fixture's (mu = 0, sd = 1, z = samples, unclipped
+    # values inside the bounds only — so feed the clipped samples as z with wide bounds)
+    c2 = capi.Solver("CEM", ENV_ID[env], orc.default_params(env), K=K, H=H, bounds=(-1e9, 1e9), dtype=dtype, sigma=1.0,
+                     max_iter=1, n_elite=K // 4, epsilon=0.0, alpha=0.0, W=W)
+    c2.cem_begin(d[env + "_x0"], g_z, np.zeros(H))
+    c2.cem_iterate(d[env + "_samples"].reshape(K, H))
+    c2.cem_end()
+    R = c2.cem_rewards(0)
+    if dtype == "f64":
+        np.testing.assert_allclose(R, d[env + "_R"], rtol=F64_COST_RTOL)
+    else:
+        f32_cost_bar(env, H, np.abs(R - d[env + "_R"]) / np.abs(d[env + "_R"]), "full W CEM", energetic=True)
+    c2.close()
+
+
+@pytest.mark.parametrize("env", ENVS)
+@pytest.mark.parametrize("noise", ["tensor", "philox"])
+def test_generic_cost_vs_oracle_with_per_step_goals(env, noise):
+    """Larger than the fixtures, against the oracle (pinned on them): a full W, and the opt-in per-step goal rows in the
+    SAMPLE rollouts (row t at step t — an extension; with it off the rollouts see row 0 like the reference's,
+    model.py:34,38).  MPPI costs and plan, the single-launch CEM solve, float64."""
+    K, H, lam = 3000 + 11, 33, 0.7
+    rng = np.random.RandomState(8)
+    nz = orc.STATE_SIZE[env] + 1
+    W = np.diag(np.abs(rng.normal(1, 0.5, nz))) + rng.normal(0, 0.2, (nz, nz))
+    if env == "cartpole":
+        W = -W
+    x, U, eps = _rand_case(env, K, H, seed=21)
+    g_traj = rng.uniform(-0.4, 0.4, (H, nz))
+    for per_step in (False, True):
+        m = orc.model(env, W=W, per_step_goal=per_step)
+        kw = dict(dtype="f64", lam=lam, sigma=1.0, W=W, per_step_goal=per_step, noise=noise, seed=4)
+        s = _solver("MPPI", env, K, H, **kw)
+        if noise == "tensor":
+            s.set_noise(eps)
+            e = eps
+        else:
+            e = s.philox_noise(0)
+        u0, Un, xs, cost = s.mppi_solve(x, g_traj, U)
+        S_ref = orc.mppi_costs(m, x, U, e, lam, 1.0, g_traj if per_step else g_traj[0])
+        U_ref, _ = orc.mppi_update(S_ref, e, lam, U)
+        np.testing.assert_allclose(s.mppi_costs()[0], S_ref, rtol=F64_COST_RTOL)
+        tol = _plan_tol(S_ref, lam, F64_COST_RTOL)
+        np.testing.assert_allclose(Un[0], U_ref, rtol=tol, atol=tol)
+        xs_ref, c_ref = orc.simulate(m, x, np.clip(Un[0], *orc.BOUNDS[env]), g_traj)  # the nominal rollout: row t always
+        np.testing.assert_allclose(xs[0], xs_ref, rtol=1e-10, atol=1e-10)
+        s.close()
+    # CEM, one launch, per-step goals and full W
+    Kc, iters, n_elite = 1500, 3, 150
+    c = _solver("CEM", env, Kc, H, dtype="f64", noise="philox", sigma=1.0, max_iter=iters, n_elite=n_elite, epsilon=1e-5,
+                alpha=0.2, seed=6, W=W, per_step_goal=True)
+    u0, Uc, xs, cost, n = c.cem_solve(x, g_traj, np.zeros(H))
+    z = np.stack([c.philox_noise(it) for it in range(iters)])
+    ref = orc.cem_solve(orc.model(env, W=W, per_step_goal=True), x, np.zeros(H), z, n_elite, 1e-5, 0.2, 1.0, goal=g_traj)
+    for it in range(iters):
+        assert np.array_equal(np.sort(c.cem_elites(it)), ref["elites"][it])
+    np.testing.assert_allclose(Uc, ref["mu"], rtol=1e-10, atol=1e-12)
+    c.close()
+
+
+def test_agents_accept_a_full_cost_matrix():
+    """The drop-in classes with a model whose W is not diagonal (rejected in round 1): the agent's solve equals the
+    oracle's on the agent's own noise; a float32 agent runs the generic flavour too."""
+    np.random.seed(3)
+    model = mpc_b200.PendulumModel()
+    model.W = np.array([[1.0, 0.2, 0.0], [-0.1, 0.1, 0.05], [0.0, 0.0, 0.001]])
+    agent = mpc_b200.MPPI(model, {"K": 400, "T": 20, "std": 1.0, "lam": 0.5})
+    x = np.array([2.5, 0.3])
+    a = agent.predict_action(x, goal_state=np.zeros(3))
+    S_ref, U_ref, _ = orc.mppi_solve(orc.model("pendulum", W=model.W), x, np.zeros(20), agent.delta_u, 0.5, 1.0)
+    np.testing.assert_allclose(agent.last_sample_costs(), S_ref, rtol=1e-12)
+    assert a[0] == pytest.approx(np.clip(U_ref[0], -2, 2), rel=1e-9, abs=1e-12)
+    xn = model.predict(x, np.array([0.5]))  # the model object steps with the same matrix
+    c_ref, xn_ref = orc.step(orc.model("pendulum", W=model.W), x, 0.5)
+    assert -model.get_reward() == pytest.approx(c_ref, rel=1e-12)
+    agent.close()
+    model.close()
+    np.random.seed(3)
+    a32 = mpc_b200.MPPI(model, {"K": 400, "T": 20, "std": 1.0, "lam": 0.5, "dtype": "f32"})
+    b = a32.predict_action(x, goal_state=np.zeros(3))
+    assert b[0] == pytest.approx(a[0], abs=1e-4)
+    a32.close()
+    model.close()
+
+
 # ------------------------------------------------------------------------------------------- MPPI, golden
 @pytest.mark.parametrize("dtype", ["f64", "f32"])
 def test_mppi_golden_cases(golden_dir, dtype):
