@@ -461,11 +461,13 @@ def cem_extra(capi, dist, fma_peak, K=4096, reps=100, warm=10):
     out.update({tag + "_f32_philox_p50_ms": round(1e3 * p50, 4), tag + "_steps_per_s": K * H * n_it / p50,
                 tag + "_device_ms_per_solve": dev_ms, tag + "_launches_per_solve": launches})
     ach = K * H * n_it * ALG_FLOPS["cartpole"] / (dev_ms * 1e-3) / 1e12
-    out[tag + "_roofline"] = {"bound": "fp32_pipe", "kernel": "all kernels of one CEM solve", "achieved": ach,
+    out[tag + "_roofline"] = {"bound": "fp32_pipe", "kernel": "cem_solve_kernel (the whole solve: one persistent launch)"
+                              if launches == 1 else "all kernels of one CEM solve", "achieved": ach,
                               "peak": fma_peak, "unit": "TFLOP/s", "frac": ach / fma_peak if fma_peak else None,
-                              "kernel_ms": dev_ms,
-                              "note": "K*H*iters = %d rollout-steps per solve: a latency-bound solve, not a "
-                                      "throughput one" % (K * H * n_it)}
+                              "kernel_ms": dev_ms, "alg_flops_per_step": ALG_FLOPS["cartpole"],
+                              "note": "K*H*iters = %d rollout-steps per solve; at K = 4096 the solve is a chain of "
+                                      "latencies (one warp of rollouts per SM, two grid barriers per iteration), not "
+                                      "a throughput problem" % (K * H * n_it)}
     return out
 
 
@@ -707,7 +709,9 @@ def run_ours(args, dist):
                                           fma_peak=fma_peak["f32"], **common)
                     extra[args.workload + "_polynomial_trig"] = brief(w)
                 extra.update(latency_extras(capi, dist))
-                extra.update(cem_extra(capi, dist, fma_peak["f32"]))
+                extra.update(cem_extra(capi, dist, fma_peak["f32"]))                      # BASELINE configs[1]
+                extra.update(cem_extra(capi, dist, fma_peak["f32"], K=65536, reps=30, warm=5))
+                extra.update(cem_extra(capi, dist, fma_peak["f32"], K=1 << 20, reps=6, warm=2))
                 extra.update(temperature_extra(capi, dist))
                 extra.update(episode_extra(capi, dist))
         except Exception as e:  # extras must never take the headline line down
