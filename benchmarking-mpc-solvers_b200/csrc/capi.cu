@@ -545,11 +545,12 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         }
         int max_smem = 0;
         CUC(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
-        max_smem -= 1024;  // the solve kernel's static shared memory (reduction scratch, profiling stamps) shares the limit
+        max_smem -= 640;  // the solve kernel's static shared memory (reduction scratch, profiling stamps: 532 B) shares the limit
+        const int uc = g.B < h->num_sms ? 1 : 0;  // fewer solves than SMs: a block works on ONE solve, one copy of its plan
         const int nblk_cap = h->num_sms > 32 ? h->num_sms : 32;  // records the last block may have to merge
         // does a block of W warps with a ring of S stages of `rows` time steps fit in shared memory?
         auto fits = [&](int W, int S, int rows) {
-            return mppi_solve_smem(cfg->dtype, g.variant, cfg->H, rows, S, W, W > nblk_cap ? W : nblk_cap, 1, h->nz) <=
+            return mppi_solve_smem(cfg->dtype, g.variant, cfg->H, rows, S, W, W > nblk_cap ? W : nblk_cap, 1, h->nz, uc) <=
                    (size_t)max_smem;
         };
         // whole [H][wt] tiles: the most stages that fit next to 16 warps' worth of records (more stages than warps
@@ -652,8 +653,9 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
         g.warps = W;
         g.stages = S;
         const int cap = g.max_parts > W ? g.max_parts : W;
+        g.u_copies = uc ? 1 : W;
         g.smem_rollout = mppi_solve_smem(cfg->dtype, g.variant, cfg->H, g.stream_rows ? g.stream_rows : cfg->H, S, W, cap,
-                                         g.fin_group, h->nz);
+                                         g.fin_group, h->nz, uc);
         if (g.smem_rollout > (size_t)max_smem) {
             int rc = fail(nullptr, MPC_EINVAL, "solve kernel needs %zu B of shared memory (limit %d)", g.smem_rollout,
                           max_smem);

@@ -255,7 +255,7 @@ __global__ void fill_kernel(float *p, size_t n, float v) {
     ret name##_f32_e0(__VA_ARGS__); ret name##_f32_e1(__VA_ARGS__); ret name##_f32_e2(__VA_ARGS__);   \
     ret name##_f64_e0(__VA_ARGS__); ret name##_f64_e1(__VA_ARGS__); ret name##_f64_e2(__VA_ARGS__);
 #define DECL_0(ret, name, ...) ret name##_f32_e0(__VA_ARGS__); ret name##_f64_e0(__VA_ARGS__);
-DECL_0(size_t, mppi_solve_smem, int, int, int, int, int, int, int, int)
+DECL_0(size_t, mppi_solve_smem, int, int, int, int, int, int, int, int, int)
 DECL_0(size_t, mppi_stage_bytes, int, int)
 DECL_0(int, mppi_max_warps, int, int)
 DECL_E(cudaError_t, launch_mppi_solve, int, int, const EnvParamsHost &, const MppiArgs &, const MppiBuffers &, cudaStream_t)
@@ -284,8 +284,8 @@ cudaError_t launch_episode_step_f64_e2(const EnvParamsHost &, const EpisodeArgs 
 #define BY_DTYPE_ENV(name, env, ...) \
     ((dtype) == DT_F32 ? BY_ENV_(name, _f32, env, __VA_ARGS__) : BY_ENV_(name, _f64, env, __VA_ARGS__))
 
-size_t mppi_solve_smem(int dtype, int variant, int H, int rows, int S, int W, int cap, int G, int nz) {
-    return BY_DTYPE(mppi_solve_smem, variant, H, rows, S, W, cap, G, nz);
+size_t mppi_solve_smem(int dtype, int variant, int H, int rows, int S, int W, int cap, int G, int nz, int uc) {
+    return BY_DTYPE(mppi_solve_smem, variant, H, rows, S, W, cap, G, nz, uc);
 }
 size_t mppi_stage_bytes(int dtype, int variant, int rows) { return BY_DTYPE(mppi_stage_bytes, variant, rows); }
 int mppi_max_warps(int dtype, int noise_kind, int variant) { return BY_DTYPE(mppi_max_warps, noise_kind, variant); }

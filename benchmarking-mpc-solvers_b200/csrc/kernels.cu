@@ -599,19 +599,19 @@ static cudaError_t mppi_solve_go(const MppiArgs &a, const EnvParamsHost &ep, con
 // shared-memory bytes of the solve kernel: records + ring (S stages of `rows` time steps, W warps) or records + the tail
 // arena, whichever is larger
 template <typename V>
-static size_t mppi_smem_bytes(int H, int rows, int S, int W, int cap, int G, int nz) {
-    const size_t ring = RingSmem<V>::ring_total(H, rows, S, W), tail = RingSmem<V>::tail_total(H, W, cap, G, nz);
+static size_t mppi_smem_bytes(int H, int rows, int S, int W, int cap, int G, int nz, int uc) {
+    const size_t ring = RingSmem<V>::ring_total(H, rows, S, W, uc ? uc : W), tail = RingSmem<V>::tail_total(H, W, cap, G, nz);
     return ring > tail ? ring : tail;
 }
 #endif
 
 #if MPC_ENV_ONLY == 0
-size_t FN(mppi_solve_smem)(int variant, int H, int rows, int S, int W, int cap, int G, int nz) {
+size_t FN(mppi_solve_smem)(int variant, int H, int rows, int S, int W, int cap, int G, int nz, int uc) {
     if constexpr (std::is_same<R_, double>::value)
-        return mppi_smem_bytes<double>(H, rows, S, W, cap, G, nz);
+        return mppi_smem_bytes<double>(H, rows, S, W, cap, G, nz, uc);
     else
-        return (variant & VAR_PACK2) ? mppi_smem_bytes<f2>(H, rows, S, W, cap, G, nz)
-                                     : mppi_smem_bytes<float>(H, rows, S, W, cap, G, nz);
+        return (variant & VAR_PACK2) ? mppi_smem_bytes<f2>(H, rows, S, W, cap, G, nz, uc)
+                                     : mppi_smem_bytes<float>(H, rows, S, W, cap, G, nz, uc);
 }
 
 size_t FN(mppi_stage_bytes)(int variant, int rows) {

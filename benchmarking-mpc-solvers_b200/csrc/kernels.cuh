@@ -44,6 +44,7 @@ struct Geometry {
     int fin_group;        // mode B: solves finalised together (one thread per nominal rollout)
     int stream_rows;      // 0 = whole [H][wt] tiles in the ring; > 0 = STREAM: time steps per chunk of a warp's private ring
     int stream_depth;     // STREAM: chunk stages per warp
+    int u_copies;         // copies of the plan in shared memory (rollout dtype): 1 when a block works on one solve, else W
     int variant;          // rollout flavour: bits 0-2 trig (0 polynomial, 1 MUFU, Acrobot 2/4/5 per-stage splits), bit 3 two
                           // samples per thread (f32x2), bit 4 WIDE (32-warp whole-tile blocks, one sample per thread)
     int ns;
@@ -217,7 +218,8 @@ cudaError_t launch_fill(float *p, size_t n, float v, cudaStream_t s);
 cudaError_t launch_episode_step(const EnvParamsHost &ep, const EpisodeArgs &a, const EpisodeBuffers &b, cudaStream_t s);
 
 // rows = time steps per ring stage (H, or the STREAM chunk); S = ring stages of the block (STREAM: W * depth)
-size_t mppi_solve_smem(int dtype, int variant, int H, int rows, int S, int W, int cap, int G, int nz);
+// uc = copies of the plan in the rollout dtype: 1, or 0 for "one per warp"
+size_t mppi_solve_smem(int dtype, int variant, int H, int rows, int S, int W, int cap, int G, int nz, int uc);
 size_t mppi_stage_bytes(int dtype, int variant, int rows);
 // warps per block the solve kernel of (dtype, noise kind, variant) is compiled for (SolveShape in mppi.cuh)
 int mppi_max_warps(int dtype, int noise_kind, int variant);

@@ -61,10 +61,12 @@ struct RingSmem {
     // a stage holds `rows` time steps of one warp tile: rows = H (whole tiles), or the STREAM chunk
     static __host__ __device__ size_t stage_bytes(int rows) { return (size_t)rows * WT * sizeof(R); }
     static __host__ __device__ size_t off_sU(int H, int rows, int S, int W) { return off_ring(H, W) + S * stage_bytes(rows); }
-    static __host__ __device__ size_t off_sw(int H, int rows, int S, int W) { return off_sU(H, rows, S, W) + a16((size_t)W * H * sizeof(R)); }
-    static __host__ __device__ size_t off_bar(int H, int rows, int S, int W) { return off_sw(H, rows, S, W) + (size_t)W * WT * sizeof(R); }
-    static __host__ __device__ size_t off_gen(int H, int rows, int S, int W) { return off_bar(H, rows, S, W) + (size_t)S * 8; }
-    static __host__ __device__ size_t ring_total(int H, int rows, int S, int W) { return off_gen(H, rows, S, W) + (size_t)S * 4 + 16; }
+    // uc = copies of the plan in the rollout dtype: 1 (a block works on one solve: fewer solves than SMs) or W (one
+    // per warp: a block may own several solves)
+    static __host__ __device__ size_t off_sw(int H, int rows, int S, int W, int uc) { return off_sU(H, rows, S, W) + a16((size_t)uc * H * sizeof(R)); }
+    static __host__ __device__ size_t off_bar(int H, int rows, int S, int W, int uc) { return off_sw(H, rows, S, W, uc) + (size_t)W * WT * sizeof(R); }
+    static __host__ __device__ size_t off_gen(int H, int rows, int S, int W, int uc) { return off_bar(H, rows, S, W, uc) + (size_t)S * 8; }
+    static __host__ __device__ size_t ring_total(int H, int rows, int S, int W, int uc) { return off_gen(H, rows, S, W, uc) + (size_t)S * 4 + 16; }
     // tail arena behind the records (doubles): scale[cap] | clipped plans [G][H] | goals [G][H*NZ] | group sums [W][H] | E
     static __host__ __device__ size_t tail_total(int H, int W, int cap, int G, int nz) {
         return off_ring(H, W) + ((size_t)cap + (size_t)G * H + (size_t)G * H * nz + (size_t)W * H + H + 64) * sizeof(double);
@@ -413,12 +415,13 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
     R *stages = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_ring(H, W));
     // the plan in the rollout dtype: one copy per block (mode A: one solve per block) or per warp (mode B)
     R *sU = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sU(H, rows, S, W)) + (mode_b ? (size_t)w * H : 0);
-    R *sw = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sw(H, rows, S, W)) + (size_t)w * WT;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + RingSmem<V>::off_bar(H, rows, S, W));
+    const int uc = a.g.u_copies;
+    R *sw = reinterpret_cast<R *>(smem_raw + RingSmem<V>::off_sw(H, rows, S, W, uc)) + (size_t)w * WT;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + RingSmem<V>::off_bar(H, rows, S, W, uc));
     // gen[st] = tile whose load the stage's mbarrier currently tracks.  An mbarrier carries one bit of phase: a
     // warp that ran a whole ring turn ahead of a slow warp would see the parity of an OLDER completed phase and
     // read a stale tile.  Waiting for gen[st] == j first makes the wait exact for any interleaving of the warps.
-    volatile int *gen = reinterpret_cast<volatile int *>(smem_raw + RingSmem<V>::off_gen(H, rows, S, W));
+    volatile int *gen = reinterpret_cast<volatile int *>(smem_raw + RingSmem<V>::off_gen(H, rows, S, W, uc));
 
     if (blockIdx.x == 0) stamp(a.trace, TR_START);
     // ---- this block's tile range ----------------------------------------------------------------------------

@@ -97,3 +97,30 @@ def test_noise_sweep_on_the_device_fills_the_sink(tmp_path):
     noisy = sink.find({"model_noise": True})
     assert len(noisy) == 2 and all(r["sensor_noise"] for r in noisy)
     assert all(np.isfinite(r["env_costs"]).all() and r["env_states"].shape == (20, 2) for r in res)
+
+
+def test_sample_and_temperature_sweeps_fill_the_sink(tmp_path):
+    """The other two sweep drivers (scripts/sample_test.py:28-51, scripts/mppi_temperature.py:21-32): every grid point
+    runs an episode (device-resident and through the reference-style host loop, `exp(warmstart)`), lands in the local
+    sink with the reference's dictionary schema, and can be queried back by its agent_config."""
+    sink = mpc_b200.ResultSink(str(tmp_path), "sweeps")
+    start = np.array([np.pi, 0.0])
+    base = {"std": 1.0, "lam": 0.5, "dtype": "f32"}
+    res = mpc_b200.sample_sweep(mpc_b200.PendulumEnv, mpc_b200.PendulumModel, mpc_b200.MPPI, base, start,
+                                samples=(64, 300), horizons=(5, 20), experiment_length=6, sink=sink, device=True)
+    assert len(res) == 4 and {(r["agent_config"]["K"], r["agent_config"]["T"]) for r in res} == {(64, 5), (300, 5), (64, 20), (300, 20)}
+    for r in res:
+        assert r["env_states"].shape == (6, 2) and r["env_costs"].shape == (6,) and np.isfinite(r["env_costs"]).all()
+        assert r["agent_planning_actions"].shape == (6 * r["agent_config"]["T"], 1)
+    res_t = mpc_b200.temperature_sweep(mpc_b200.PendulumEnv, mpc_b200.PendulumModel, mpc_b200.MPPI,
+                                       dict(base, K=128, T=10), start, lams=(0.01, 1.0), experiment_length=5, sink=sink,
+                                       device=False, warmstart=2)
+    assert [r["agent_config"]["lam"] for r in res_t] == [0.01, 1.0] and all(r["warmstart"] for r in res_t)
+    assert len(sink.find()) == 6 and len(sink.find({"agent_config": {"K": 300, "T": 20}})) == 1
+    hit = sink.find({"agent_config": {"lam": 0.01, "K": 128}})
+    assert len(hit) == 1 and np.array_equal(hit[0]["env_states"], res_t[0]["env_states"])
+    # Experiment.__call__ is what the reference scripts use
+    exp = mpc_b200.Experiment({"env": mpc_b200.PendulumEnv, "model": mpc_b200.PendulumModel, "agent": mpc_b200.MPPI,
+                               "agent_config": dict(base, K=64, T=8), "experiment_length": 4, "start_state": start})
+    out = exp(3)
+    assert out["env_states"].shape == (4, 2) and out["warmstart"] is True
