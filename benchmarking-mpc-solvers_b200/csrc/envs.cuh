@@ -304,14 +304,19 @@ struct Acrobot {
     typedef typename VT<V>::S S;
     typedef V Vec;
     typedef Acrobot<S, 0, GEN> Scalar;  // one sample per thread, accurate trig: nominal rollouts
-    // step() keeps the two angles in HALF-TURNS (theta / pi): range reductions become exact additions (vec.cuh)
+    // step() keeps the two angles in HALF-TURNS (theta / pi): range reductions become exact additions (vec.cuh).
+    // The all-MUFU flavour (TRIG == 1) keeps them in RADIANS instead: MUFU.SIN/COS take radians (one FMUL each for their
+    // own range scaling), so half-turns would cost a second multiply per stage angle — 8 instructions per step.
+    static constexpr bool RAD = TRIG == 1;
     static __device__ __forceinline__ void enter(const EnvConst<V> &, S *x) {
-        x[0] *= 0.318309886f;
-        x[1] *= 0.318309886f;
+        if constexpr (!RAD) {
+            x[0] *= 0.318309886f;
+            x[1] *= 0.318309886f;
+        }
     }
     static __device__ __forceinline__ void leave(const EnvConst<V> &, const S *x, double *out) {
-        out[0] = (double)x[0] * D_PI;
-        out[1] = (double)x[1] * D_PI;
+        out[0] = RAD ? (double)x[0] : (double)x[0] * D_PI;
+        out[1] = RAD ? (double)x[1] : (double)x[1] * D_PI;
         out[2] = (double)x[2];
         out[3] = (double)x[3];
     }
@@ -341,6 +346,8 @@ struct Acrobot {
             vsincospi<false>(p, s, c);
         else if constexpr (reduce)
             vsincospi<true>(vwrap_halfturns(p), s, c);
+        else if constexpr (RAD)
+            vsincos<true>(p, s, c);
         else
             vsincospi<true>(p, s, c);
     }
@@ -367,7 +374,9 @@ struct Acrobot {
 
     static __device__ __forceinline__ V step(const EnvConst<V> &k, V (&x)[NS], const V &u, const S *gs) {
         const V p1 = x[0], p2 = x[1], w1 = x[2], w2 = x[3];  // p = theta / pi
-        const V h = k.c[0], h2 = k.c[9], h6 = k.c[10], hp = k.c[17], h2p = k.c[16], h6p = k.c[18];
+        // angle increments: h / pi, h / (2 pi), h / (6 pi) in half-turns; h, h / 2, h / 6 in radians
+        const V h = k.c[0], h2 = k.c[9], h6 = k.c[10], hp = RAD ? k.c[0] : k.c[17], h2p = RAD ? k.c[9] : k.c[16],
+                h6p = RAD ? k.c[10] : k.c[18];
         V s1, c1, s2, c2;
         stage_sincos<1>(p1, &s1, &c1);
         stage_sincos<1>(p2, &s2, &c2);
@@ -401,8 +410,9 @@ struct Acrobot {
         const V n1 = vfma(h6p, vfma(V(2.0f), m2, w2) + k4w2, p2);
         const V n2 = vfma(h6, vfma(V(2.0f), ma, k1a) + k4a, w1);
         const V n3 = vfma(h6, vfma(V(2.0f), mb, k1b) + k4b, w2);
-        x[0] = vwrap_halfturns(n0);  // wrap(.., -pi, pi) by repeated -+2pi  ==  nearest multiple of 2pi removed
-        x[1] = vwrap_halfturns(n1);
+        // wrap(.., -pi, pi) by repeated -+2pi  ==  nearest multiple of 2pi removed
+        x[0] = RAD ? vwrap_pi(n0) : vwrap_halfturns(n0);
+        x[1] = RAD ? vwrap_pi(n1) : vwrap_halfturns(n1);
         x[2] = vclip(n2, -k.c[7], k.c[7]);
         x[3] = vclip(n3, -k.c[8], k.c[8]);
         return cost;
@@ -506,7 +516,7 @@ struct NoiseUnit {
 };
 template <int TRIG, int GEN>
 struct NoiseUnit<Acrobot<float, TRIG, GEN>> {  // angles in half-turns
-    static __device__ __forceinline__ float unit(int i) { return i < 2 ? 0.318309886f : 1.0f; }
+    static __device__ __forceinline__ float unit(int i) { return (i < 2 && TRIG != 1) ? 0.318309886f : 1.0f; }
 };
 // One sample per thread (float or double lanes).  Philox counter = (sample, step, draw, stream).
 template <class Env>
