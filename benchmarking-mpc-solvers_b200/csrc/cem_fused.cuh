@@ -116,6 +116,8 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
     __shared__ int s_want, s_stop;
 
     unsigned bar_gen = ld_acquire_gpu_u32(&sc.bar[1]);
+    // inline inputs: keep the device copy of the state current for device-resident solves enqueued later
+    if ((inl.on & 1) && blk == 0 && tid < NS) const_cast<double *>(x0g)[tid] = inl.x0[tid];
     // ---- start of the solve: std = self.std.copy() (cem.py:56), mean = planned_us
     for (int t = tid; t < H; t += nt) {
         smu[t] = (inl.on & 2) ? inl.U[t] : mu_g[t];

@@ -424,6 +424,9 @@ __global__ void __launch_bounds__(SolveShape<typename Env::Vec, NOISE, WIDE>::MA
     volatile int *gen = reinterpret_cast<volatile int *>(smem_raw + RingSmem<V>::off_gen(H, rows, S, W, uc));
 
     if (blockIdx.x == 0) stamp(a.trace, TR_START);
+    // inline inputs: keep the device copy of the state current (device-resident solves enqueued later read it; every
+    // block of THIS launch reads the parameters, so there is no race)
+    if ((inl.on & 1) && blockIdx.x == 0 && threadIdx.x < NS) const_cast<double *>(x0g)[threadIdx.x] = inl.x0[threadIdx.x];
     // ---- this block's tile range ----------------------------------------------------------------------------
     int tile0, tile1, b_lo, b_hi;
     if (!mode_b) {

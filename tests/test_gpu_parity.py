@@ -945,6 +945,31 @@ def test_simulate_and_model_predict_api():
     m.close()
 
 
+@pytest.mark.parametrize("kind", ["MPPI", "CEM"])
+def test_inline_inputs_equal_staged_inputs_and_keep_the_device_copy_current(kind, monkeypatch):
+    """Batch-1 host calls pass state and plan as kernel parameters (no host-to-device copy).  Same answers as the staged
+    path (MPC_B200_INLINE=0), and the device copies of state and plan stay current: a device-resident solve enqueued
+    afterwards continues from them."""
+    H = 20
+    kw = dict(dtype="f64", noise="philox", seed=2)
+    kw.update(dict(lam=0.5) if kind == "MPPI" else dict(sigma=1.0, max_iter=3, n_elite=50, epsilon=1e-6, alpha=0.2))
+    x, U = np.array([2.0, 0.3]), np.linspace(-0.3, 0.3, H)
+    res = {}
+    for inline in ("1", "0"):
+        monkeypatch.setenv("MPC_B200_INLINE", inline)
+        s = _solver(kind, "pendulum", 512, H, **kw)
+        out = s.mppi_solve(x, None, U) if kind == "MPPI" else s.cem_solve(x, None, U)
+        first = np.ravel(out[1]).copy()
+        s.solve_enqueue()                      # device-resident: reads the device copies of state and (updated) plan
+        second = np.ravel(s.download_outputs()[1]).copy()
+        res[inline] = (first, second, np.asarray(out[2]).copy())
+        s.close()
+    monkeypatch.delenv("MPC_B200_INLINE")
+    for a, b in zip(res["1"], res["0"]):
+        assert np.array_equal(a, b)
+    assert not np.array_equal(res["1"][0], res["1"][1])
+
+
 def test_errors_are_loud():
     with pytest.raises(capi.MpcError):
         _solver("MPPI", "pendulum", 64, 5000)           # H beyond the supported horizon
