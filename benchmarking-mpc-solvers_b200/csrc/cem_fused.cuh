@@ -139,13 +139,13 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
     };
     stamp(0, 0);
     int iters = 0, done = 0;
+    for (int t = tid; t < H; t += nt) {  // mean / std in the rollout dtype (kept current by the update below)
+        smuR[t] = (R)smu[t];
+        ssdR[t] = (R)ssd[t];
+    }
+    __syncthreads();
     for (int it = 0; it < fa.max_iter; ++it) {
         stamp(it, 1);
-        for (int t = tid; t < H; t += nt) {
-            smuR[t] = (R)smu[t];
-            ssdR[t] = (R)ssd[t];
-        }
-        __syncthreads();
         // ---------------------------------------------------------------- rollout of this block's samples
         if (fa.cached) {
             // one warp's worth of samples per block: all warps draw the normals (one Philox block per thread) and form
@@ -363,30 +363,8 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
         double s1 = 0.0, s2 = 0.0;
         const double cshift = tid < H ? smu[tid] : 0.0;
         int n_el = 0;
-        for (int c0 = k0; c0 < k1; c0 += nt) {
-            const int k = c0 + tid;
-            bool is_tie = false, elite = false;
-            if (k < k1) {
-                if (fa.all_pairs) {
-                    elite = shist[k - k0] < n_elite;
-                } else {
-                    const unsigned long long km = keys[k] & mask;
-                    elite = km > prefix || (km == prefix && !split_ties);
-                    is_tie = split_ties && km == prefix;
-                }
-            }
-            int tot;
-            if (split_ties) {  // uniform over the grid
-                const int r = block_excl_scan(is_tie ? 1 : 0, swarp, &tot);
-                if (is_tie && tie_base + r < want_ties) elite = true;
-                tie_base += tot;
-            }
-            const int pos = block_excl_scan(elite ? 1 : 0, swarp, &tot);
-            if (elite) {
-                clist[pos] = k;
-                sc.stage[k0 + n_el + pos] = k;
-            }
-            __syncthreads();
+        // E(t) partial sums over the elites listed in clist[0 .. tot)
+        auto sum_elites = [&](const int tot) {
             if (fa.cached) {
                 if (tid < H)
                     for (int e = 0; e < tot; ++e) {
@@ -418,7 +396,48 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
                     __syncthreads();
                 }
             }
-            n_el += tot;
+        };
+        if (fa.all_pairs) {
+            // one warp's worth of samples: warp 0 compacts the elites with a ballot (ascending index)
+            if (tid < 32) {
+                const int k = k0 + tid;
+                const bool elite = k < k1 && shist[tid] < n_elite;
+                const unsigned m = __ballot_sync(0xffffffffu, elite);
+                if (elite) {
+                    const int pos = __popc(m & ((1u << tid) - 1u));
+                    clist[pos] = k;
+                    sc.stage[k0 + pos] = k;
+                }
+                if (tid == 0) swarp[0] = __popc(m);
+            }
+            __syncthreads();
+            n_el = swarp[0];
+            sum_elites(n_el);
+        } else {
+            for (int c0 = k0; c0 < k1; c0 += nt) {
+                const int k = c0 + tid;
+                bool is_tie = false, elite = false;
+                if (k < k1) {
+                    const unsigned long long km = keys[k] & mask;
+                    elite = km > prefix || (km == prefix && !split_ties);
+                    is_tie = split_ties && km == prefix;
+                }
+                int tot;
+                if (split_ties) {  // uniform over the grid
+                    const int r = block_excl_scan(is_tie ? 1 : 0, swarp, &tot);
+                    if (is_tie && tie_base + r < want_ties) elite = true;
+                    tie_base += tot;
+                }
+                const int pos = block_excl_scan(elite ? 1 : 0, swarp, &tot);
+                if (elite) {
+                    clist[pos] = k;
+                    sc.stage[k0 + n_el + pos] = k;
+                }
+                __syncthreads();
+                sum_elites(tot);
+                __syncthreads();  // clist is rewritten by the next chunk
+                n_el += tot;
+            }
         }
         double *slot = sc.slots + (size_t)blk * (2 + 2 * H);
         if (tid == 0) slot[0] = (double)n_el;
@@ -442,7 +461,7 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
             double p1 = 0.0, p2 = 0.0;
             if (t < H && pp < P) {
                 const double *col = sc.slots + 2 + t;
-                constexpr int MAXR = 8;
+                constexpr int MAXR = 16;  // G <= 148 slots over P >= 2 partitions: one batch, every load in flight at once
                 double v1[MAXR], v2[MAXR];
                 for (int b0 = pp; b0 < G; b0 += P * MAXR) {
 #pragma unroll
@@ -478,6 +497,8 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
             const double new_sd = a.alpha * ssd[tid] + (1 - a.alpha) * sqrt(var); // cem.py:73
             smu[tid] = new_mu;
             ssd[tid] = new_sd;
+            smuR[tid] = (R)new_mu;
+            ssdR[tid] = (R)new_sd;
             notsmall = !(new_sd < a.epsilon);
             if (blk == 0) {
                 mu_g[tid] = new_mu;
