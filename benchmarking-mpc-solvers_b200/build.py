@@ -23,7 +23,7 @@ UNITS += [("kernels_f32_e2s.o", "kernels.cu", ["-DMPC_REAL=float", "-DMPC_ENV_ON
                                                "-DMPC_SUFFIX=_f32_e2s"])]
 UNITS += [("kernels_f64_e%d.o" % e, "kernels.cu", F64 + ["-DMPC_ENV_ONLY=%d" % e, "-DMPC_SUFFIX=_f64_e%d" % e])
           for e in (2, 1, 0)]
-UNITS += [("dispatch.o", "dispatch.cu", []), ("capi.o", "capi.cu", [])]
+UNITS += [("dispatch.o", "dispatch.cu", []), ("capi.o", "capi.cu", []), ("noalloc.o", "noalloc.cu", [])]
 
 
 def _nvcc():

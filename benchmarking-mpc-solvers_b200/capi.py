@@ -30,6 +30,7 @@ SYMBOLS = [
     "mpc_comm_create_id", "mpc_comm_init", "mpc_mppi_rollout_partial", "mpc_mppi_apply_partials", "mpc_upload_inputs", "mpc_solve_enqueue", "mpc_solve_enqueue_ex", "mpc_time_solves", "mpc_download_outputs",
     "mpc_timer_start", "mpc_timer_stop", "mpc_sync", "mpc_set_profiling", "mpc_get_rollout_ms", "mpc_launch_count", "mpc_get_geometry", "mpc_measure_fma_peak",
     "mpc_flush_l2", "mpc_debug_tickets", "mpc_pin_host_buffer", "mpc_unpin_host_buffer", "mpc_p2p_export", "mpc_p2p_import", "mpc_p2p_link", "mpc_get_trace", "mpc_episode_run", "mpc_philox_model_noise", "mpc_cem_get_iterations",
+    "mpc_mppi_update_static",
 ]
 
 
@@ -119,8 +120,19 @@ def load():
     L.mpc_debug_tickets.argtypes = [hp, C.POINTER(C.c_int32)]
     L.mpc_pin_host_buffer.argtypes = [C.c_void_p, C.c_size_t]
     L.mpc_unpin_host_buffer.argtypes = [C.c_void_p]
+    L.mpc_mppi_update_static.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_double] + [C.c_void_p] * 5 + \
+        [C.c_char_p, C.c_size_t]
     _lib = L
     return L
+
+
+def mppi_update_static(device, K, H, lam, S_dev, eps_dev, U_in_dev, U_out_dev, stream=None):
+    """mpc_mppi_update_static (include/mpc_b200.h): the MPPI control update on DEVICE addresses (ints), its scratch in a
+    static device array — no allocation.  Enqueues on `stream` (a cudaStream_t as int; None = default) and returns."""
+    err = C.create_string_buffer(512)
+    rc = load().mpc_mppi_update_static(device, K, H, lam, S_dev, eps_dev, U_in_dev, U_out_dev, stream, err, len(err))
+    if rc != 0:
+        raise MpcError(rc, err.value.decode())
 
 
 def _in(a, shape=None):

@@ -286,6 +286,34 @@ int mpc_unpin_host_buffer(void *p);
 /* Flush L2 by writing a buffer larger than it. */
 int mpc_flush_l2(mpc_handle *h);
 
+/* ---- allocation-free control update ------------------------------------------------------------------------ */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The arithmetic is the
+ * control update of MPPI._calc_action (mppi.py:59-71): beta = min S, w = exp(-(S - beta)/lam) / eta,
+ * U_out = U_in + sum_k w_k eps[k] — the same update mpc_mppi_solve fuses behind its rollout — as a variant of that
+ * kernel's block-record merge whose scratch (one record per block and the ticket word) lives in a file-scope
+ * `static __device__` array instead of memory allocated by mpc_create.  The call needs no handle and calls no
+ * cudaMalloc / cudaFree / allocating library routine; it enqueues one 256-byte memset and one kernel on `stream`
+ * and returns without synchronising.
+ *   device    CUDA device ordinal the pointers belong to
+ *   K, H      samples and horizon: 1 <= H <= MPC_STATIC_MAX_H, 1 <= K <= MPC_STATIC_MAX_K; anything larger is
+ *             rejected with MPC_EINVAL (the array cannot grow) — use mpc_mppi_solve for those
+ *   lam       MPPI temperature (mppi.py:17), > 0
+ *   S_dev     [K]     in   per-sample costs, float64, DEVICE memory
+ *   eps_dev   [K][H]  in   noise (delta_u, du = 1), float64, DEVICE memory
+ *   U_in_dev  [H]     in   planned_us before the update, float64, DEVICE memory
+ *   U_out_dev [H]     out  planned_us after the update (not clipped), DEVICE memory; may alias U_in_dev
+ *   stream    cudaStream_t (NULL = the legacy default stream)
+ *   err_out   receives the message of a failure (err_cap bytes, NUL-terminated); may be NULL
+ * Limits: the array is about 0.6 MB (296 block records of 2 + 256 doubles) and every GPU that loads the library holds
+ * it until the process exits.  Every call on a device shares it and it keeps the last call's contents (the ticket
+ * word is cleared on `stream` before each launch): calls that OVERLAP on one GPU — different streams or threads
+ * without an ordering between them — race on it and produce garbage; calls on one stream are safe. */
+#define MPC_STATIC_MAX_H 256
+#define MPC_STATIC_MAX_K (1 << 24)
+int mpc_mppi_update_static(int32_t device, int32_t K, int32_t H, double lam, const double *S_dev, const double *eps_dev,
+                           const double *U_in_dev, double *U_out_dev, void *stream, char *err_out, size_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif
