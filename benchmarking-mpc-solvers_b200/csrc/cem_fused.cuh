@@ -112,6 +112,7 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
     unsigned long long *smine = reinterpret_cast<unsigned long long *>(shist + 256);  // [32] all-pairs: this block's keys
     double *sred = reinterpret_cast<double *>(smine + 32);      // [2][nt] partial column sums of the update
     R *su = reinterpret_cast<R *>(sred + 2 * nt);               // [H][32] cached mode: this block's samples
+    R *sz = su + (size_t)H * 32;                                // [H][32] cached mode: standard normals of the NEXT iteration
     __shared__ unsigned long long s_prefix;
     __shared__ int s_want, s_stop;
 
@@ -143,26 +144,37 @@ __global__ void __launch_bounds__(CEMF_THREADS, 1)
         smuR[t] = (R)smu[t];
         ssdR[t] = (R)ssd[t];
     }
+    // cached mode: the standard normals of iteration `draw` for the block's 32 samples, one Philox block per task,
+    // drawn by threads first .. nt-1 (all of them before the first iteration; afterwards the 15 warps that have no
+    // rollout to do draw the NEXT iteration's normals while warp 0 walks down its dependency chain)
+    auto draw_normals = [&](const int draw, const int first) {
+        const int nq = (H + 3) >> 2;
+        for (int task = tid - first; task < 32 * nq; task += nt - first) {
+            const int sidx = task & 31, tq = task >> 5;
+            float z[4] = {0.f, 0.f, 0.f, 0.f};
+            if (k0 + sidx < k1) philox_normal4(a.seed, 1u, (uint32_t)draw, (uint32_t)(a.g.k_begin + k0 + sidx), (uint32_t)tq, z);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int t = 4 * tq + i;
+                if (t < H) sz[t * 32 + sidx] = (R)z[i];
+            }
+        }
+    };
+    if (fa.cached) draw_normals(0, 0);
     __syncthreads();
     for (int it = 0; it < fa.max_iter; ++it) {
         stamp(it, 1);
         // ---------------------------------------------------------------- rollout of this block's samples
         if (fa.cached) {
-            // one warp's worth of samples per block: all warps draw the normals (one Philox block per thread) and form
-            // the samples clip(mu + sd z) in shared memory; warp 0 rolls them out (a pure dependency chain from here),
-            // and the refit reads the elites' samples back from the same array
-            const int nq = (H + 3) >> 2;
-            for (int task = tid; task < 32 * nq; task += nt) {
-                const int sidx = task & 31, tq = task >> 5;
-                float z[4] = {0.f, 0.f, 0.f, 0.f};
-                if (k0 + sidx < k1) philox_normal4(a.seed, 1u, (uint32_t)it, (uint32_t)(a.g.k_begin + k0 + sidx), (uint32_t)tq, z);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int t = 4 * tq + i;
-                    if (t < H) su[t * 32 + sidx] = vclip(sample_value(ssdR[t], (R)z[i], smuR[t]), lo, hi);
-                }
+            // one warp's worth of samples per block: the samples clip(mu + sd z) are formed in shared memory from the
+            // normals drawn ahead; warp 0 rolls them out (a pure dependency chain from here) and the refit reads the
+            // elites' samples back from the same array
+            for (int i = tid; i < 32 * H; i += nt) {
+                const int t = i >> 5;
+                su[i] = vclip(sample_value(ssdR[t], sz[i], smuR[t]), lo, hi);
             }
             __syncthreads();
+            if (tid >= 32 && it + 1 < fa.max_iter) draw_normals(it + 1, 32);
             const int k = k0 + tid;
             if (tid < 32 && k < k1) {
                 const uint32_t kglob = (uint32_t)(a.g.k_begin + k);
@@ -563,7 +575,7 @@ static size_t cem_fused_smem(int H, int ns, bool cached) {
     b += (size_t)(CEMF_THREADS + 40 + 256) * sizeof(int);
     b = (b + 7) / 8 * 8;
     b += 32 * sizeof(unsigned long long) + 2 * (size_t)CEMF_THREADS * sizeof(double);
-    if (cached) b += (size_t)H * 32 * sizeof(R);
+    if (cached) b += 2 * (size_t)H * 32 * sizeof(R);
     return b + 16;
 }
 
