@@ -646,6 +646,8 @@ int mpc_create(const mpc_config *cfg, mpc_handle **out) {
             g.grid = g.B * nb;
             g.max_parts = nb;
             g.n_groups = nb > MERGE_GROUP ? (nb + MERGE_GROUP - 1) / MERGE_GROUP : 0;  // two-level merge (mppi.cuh tail)
+            if (const char *e = getenv("MPC_B200_MERGE_FLAT"))  // profiling: one ticket, the last block merges all records
+                if (atoi(e) != 0) g.n_groups = 0;
             g.fin_group = 1;
         }
         if (g.stream_rows) S = W * g.stream_depth;
