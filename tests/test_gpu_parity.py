@@ -834,6 +834,19 @@ def test_cem_philox_on_device_iterations():
     s2.close()
 
 
+@pytest.mark.parametrize("H", [80, 81, 82, 83, 84])
+def test_cem_single_launch_around_the_default_shared_memory_limit(H):
+    """The single-launch CEM kernel's dynamic shared memory crosses the 48 KB default between H = 82 and 83 (float32
+    CartPole, 32 samples per block): the opt-in attribute must be set on both sides of it (static shared memory counts
+    against the default as well) — every horizon solves in one launch."""
+    s = _solver("CEM", "cartpole", 4096, H, dtype="f32", noise="philox", sigma=1.0, max_iter=2, n_elite=100,
+                epsilon=1e-5, alpha=0.2, seed=5)
+    l0 = s.launch_count
+    u0, U, xs, cost, n = s.cem_solve(START["cartpole"] + 0.05, None, np.zeros(H))
+    assert s.launch_count - l0 == 1 and n == 2 and np.all(np.isfinite(U))
+    s.close()
+
+
 @pytest.mark.parametrize("env,K,H,n_elite,dtype", [
     ("cartpole", 4096, 50, 409, "f64"),      # BASELINE configs[1]: all-pairs rank counting, 128 blocks x 32 samples
     ("pendulum", 1000, 30, 100, "f64"),      # ragged last block
