@@ -460,6 +460,19 @@ def cem_extra(capi, dist, fma_peak, K=4096, reps=100, warm=10):
     s.close()
     out.update({tag + "_f32_philox_p50_ms": round(1e3 * p50, 4), tag + "_steps_per_s": K * H * n_it / p50,
                 tag + "_device_ms_per_solve": dev_ms, tag + "_launches_per_solve": launches})
+    if K == 4096:
+        # the same solve called from plain C (tools/cabi_latency.c, built by build.py next to the library): the C-ABI
+        # call with host buffers without the Python wrapper's ctypes / numpy time; with the logging trajectory (what
+        # Agent.predict_action needs) and without it (CEM._calc_action alone, cem.py:54-78)
+        exe = os.path.join(os.path.dirname(capi.LIB_PATH), "build", "cabi_latency")
+        if os.path.exists(exe):
+            import subprocess
+            for traj, key in ((1, "_c_abi_p50_ms"), (0, "_c_abi_calc_action_only_p50_ms")):
+                try:
+                    r = subprocess.run([exe, "500", str(traj)], capture_output=True, text=True, timeout=60)
+                    out[tag + key] = round(json.loads(r.stdout.strip().splitlines()[-1])["p50_us"] / 1e3, 4)
+                except Exception as e:  # a probe, not the product: report and carry on
+                    out[tag + key] = "unavailable: %r" % (e,)
     ach = K * H * n_it * ALG_FLOPS["cartpole"] / (dev_ms * 1e-3) / 1e12
     out[tag + "_roofline"] = {"bound": "fp32_pipe", "kernel": "cem_solve_kernel (the whole solve: one persistent launch)"
                               if launches == 1 else "all kernels of one CEM solve", "achieved": ach,

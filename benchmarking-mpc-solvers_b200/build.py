@@ -13,6 +13,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmpcb200.so")
+# plain-C latency probe of the C ABI (tools/cabi_latency.c): bench.py runs it beside the Python wrapper's p50
+CABI_SRC = os.path.join(HERE, "..", "tools", "cabi_latency.c")
+CABI_BIN = os.path.join(OBJ, "cabi_latency")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
 # (object name, source, extra flags)
@@ -40,6 +43,10 @@ def needs_build():
     # every source and header of the library (globbed: a new .cuh can never be forgotten here)
     deps = glob.glob(os.path.join(CSRC, "*.cu")) + glob.glob(os.path.join(CSRC, "*.cuh")) + \
         glob.glob(os.path.join(HERE, "..", "include", "*.h")) + [os.path.abspath(__file__)]
+    if shutil.which("gcc") and os.path.exists(CABI_SRC):
+        if not os.path.exists(CABI_BIN):
+            return True
+        deps.append(CABI_SRC)
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -67,6 +74,10 @@ def build(force=False, verbose=False):
         if rc != 0:
             raise RuntimeError("nvcc failed on %s" % obj)
     subprocess.check_call([nvcc] + ARCH + ["-shared", "-o", LIB] + [os.path.join(OBJ, u[0]) for u in UNITS] + ["-ldl"])
+    gcc = shutil.which("gcc")
+    if gcc and os.path.exists(CABI_SRC):  # a consumer of the C ABI in plain C; found next to the library by $ORIGIN
+        subprocess.check_call([gcc, "-O2", "-std=c99", "-I", os.path.join(HERE, "..", "include"), CABI_SRC, "-o", CABI_BIN,
+                               "-L", HERE, "-lmpcb200", "-Wl,-rpath,$ORIGIN/..", "-lm"])
     return LIB
 
 
