@@ -692,6 +692,39 @@ def test_mppi_full_size_properties():
     small.close()
 
 
+def test_mppi_headline_full_size_properties():
+    """The HEADLINE workload at its full size and in the benchmarked flavour (Acrobot, K = 2^20, H = 100, float32, MUFU
+    trig, one sample per thread, resident noise tensor filled on the device): size-independent properties.
+       (1) sample k's cost depends only on (seed, k), not on K or the tiling: the first 8192 costs equal a K = 8192
+           solve's bit for bit;
+       (2) those 8192 costs against the CPU oracle (float64, the pinned restatement of the reference) on the identical
+           noise: the float32 bar of (acrobot, H = 100);
+       (3) the plan equals the oracle's softmin update (float64, CPU) of the GPU's own 2^20 costs and noise;
+       (4) two consecutive identical solves are bit-identical."""
+    env, K, H, lam, n = "acrobot", 1 << 20, 100, 0.5, 8192
+    x = START[env] + 0.01
+    U = np.zeros(H)
+    kw = dict(dtype="f32", noise="tensor", lam=lam, sigma=1.0, seed=7, fast_math=1, lanes=1)
+    big = _solver("MPPI", env, K, H, **kw)
+    small = _solver("MPPI", env, n, H, **kw)
+    big.fill_noise()
+    small.fill_noise()
+    u0, Ub, _, _ = big.mppi_solve(x, None, U)
+    Sb = big.mppi_costs()[0]
+    small.mppi_solve(x, None, U)
+    assert np.array_equal(Sb[:n], small.mppi_costs()[0])
+    eps = big.philox_noise(0).astype(np.float32).astype(np.float64)  # the tensor's values (sigma = 1)
+    S_ref, _, _ = orc.mppi_solve(orc.model(env), x, U, eps[:n], lam, 1.0, nthreads=0)
+    f32_cost_bar(env, H, np.abs(Sb[:n] - S_ref) / np.abs(S_ref), "headline flavour, first %d of 2^20 samples" % n)
+    U_ref, w = orc.mppi_update(Sb, eps, lam, U)
+    assert abs(w.sum() - 1) < 1e-9
+    np.testing.assert_allclose(Ub[0], U_ref, atol=2e-6, rtol=0)  # float32 weights/products inside a tile
+    _, Ub2, _, _ = big.mppi_solve(x, None, U)
+    assert np.array_equal(Ub, Ub2)
+    big.close()
+    small.close()
+
+
 # ------------------------------------------------------------------------------------------- CEM
 def _cem_f32_iteration(s, it, Rref, el_ref, env, H, n_elite):
     """One float32 CEM iteration against the reference's: rewards on the env's float32 bar, elite set >= 99 % identical
