@@ -525,6 +525,35 @@ def test_mppi_batch_block_owns_solves():
     one.close()
 
 
+def test_mppi_batch_config4_full_size():
+    """BASELINE configs[4] at its own size and dtype: 4096 independent CartPole solves, K = 1024, H = 50, float32,
+    one launch (a block owns whole solves).  Solves across the batch (first / last of a block, first / last of the
+    batch) against the CPU oracle on the identical noise: costs on the float32 bar, plan = the oracle's softmin update
+    of the GPU's own costs; and the whole batch again: bit-identical."""
+    env, B, K, H, lam = "cartpole", 4096, 1024, 50, 0.5
+    rng = np.random.RandomState(0)
+    xs0 = START[env] + rng.normal(0, 0.2, (B, 4))  # cartpole_swingup_model.py:50-51
+    U0 = np.zeros((B, H))
+    sb = _solver("MPPI", env, K, H, dtype="f32", noise="philox", lam=lam, sigma=1.0, seed=3, batch=B)
+    u0b, Ub, xsb, cb = sb.mppi_solve(xs0, None, U0)
+    Sb = sb.mppi_costs()
+    eps = sb.philox_noise(0).astype(np.float32).astype(np.float64)  # every solve of the batch sees the same draw
+    m = orc.model(env)
+    for b in (0, 1, 27, 28, 2047, 4094, 4095):
+        S_ref, _, _ = orc.mppi_solve(m, xs0[b], U0[b], eps, lam, 1.0)
+        f32_cost_bar(env, H, np.abs(Sb[b] - S_ref) / np.abs(S_ref), "configs[4] solve %d" % b)
+        U_ref, w = orc.mppi_update(Sb[b], eps, lam, U0[b])
+        np.testing.assert_allclose(Ub[b], U_ref, atol=2e-6, rtol=0)
+        xs_ref, c_ref = orc.simulate(m, xs0[b], np.clip(Ub[b], *orc.BOUNDS[env]))
+        # the float32 nominal rollout of a swing-up from a random state: 50 steps amplify float32 rounding to ~4e-3
+        # in the state (measured), far below anything the logged trajectory is used for
+        np.testing.assert_allclose(xsb[b], xs_ref, rtol=0, atol=2e-2)
+        assert abs(cb[b] - c_ref) <= 2e-3 * abs(c_ref)
+    u0c, Uc, _, _ = sb.mppi_solve(xs0, None, U0)
+    assert np.array_equal(Ub, Uc)
+    sb.close()
+
+
 def _device_count():
     try:
         import torch
