@@ -341,6 +341,33 @@ def test_mppi_float32_flavours_meet_the_same_bar(env, H, K, seed, fast_math, lan
     s.close()
 
 
+@pytest.mark.parametrize("lam", [0.001, 0.01, 0.1, 1.0, 10.0])
+def test_mppi_temperature_grid_config3(lam):
+    """BASELINE configs[3] at its own size: Pendulum, K = 65536, H = 50 over the temperature grid of
+    scripts/mppi_temperature.py.  The action is a softmin of the costs: at lambda = 0.001 a handful of samples carry all
+    the weight.  float64: costs 1e-12, plan on the conditioning bound of 1e-12 costs.  float32 (the benchmarked
+    flavour): every cost within 1e-5, and the plan equal to the oracle's softmin update of the GPU's OWN costs (which
+    separates the update's arithmetic from the conditioning of the softmin at small temperatures)."""
+    env, K, H = "pendulum", 65536, 50
+    x, U, eps = _rand_case(env, K, H, seed=3)
+    S_ref, U_ref, _ = orc.mppi_solve(orc.model(env), x, U, eps, lam, 1.0, nthreads=0)
+    s = _solver("MPPI", env, K, H, dtype="f64", lam=lam, sigma=1.0)
+    s.set_noise(eps)
+    _, U64, _, _ = s.mppi_solve(x, None, U)
+    np.testing.assert_allclose(s.mppi_costs()[0], S_ref, rtol=F64_COST_RTOL)
+    tol = _plan_tol(S_ref, lam, F64_COST_RTOL)
+    np.testing.assert_allclose(U64[0], U_ref, rtol=tol, atol=tol)
+    s.close()
+    s = _solver("MPPI", env, K, H, dtype="f32", lam=lam, sigma=1.0, fast_math=1, lanes=2)
+    s.set_noise(eps)
+    _, U32, _, _ = s.mppi_solve(x, None, U)
+    S32 = s.mppi_costs()[0]
+    f32_cost_bar(env, H, np.abs(S32 - S_ref) / np.abs(S_ref), "lambda = %g" % lam)
+    U_own, w = orc.mppi_update(S32, eps.astype(np.float32).astype(np.float64), lam, U)
+    np.testing.assert_allclose(U32[0], U_own, atol=5e-6, rtol=0)
+    s.close()
+
+
 @pytest.mark.parametrize("env,H", [("acrobot", 100), ("acrobot", 50), ("pendulum", 50)])
 def test_mppi_mufu_flavour_is_not_worse_in_kind(env, H):
     """Energetic regime (swing-up states, plans of amplitude 1.5): float32 follows the float64 oracle in the median
